@@ -1,0 +1,181 @@
+/*
+ * orbx.h — C ABI of liborbx: B200-native (sm_100a) ORB extraction + brute-force Hamming matching.
+ *
+ * Drop-in boundary for the `feature` module of MostlyKIGuess/slam-rs.  The reference has no FFI of
+ * its own on this path: the seam is the Rust API of src/feature/{detector,matcher}.rs, which today
+ * forwards to OpenCV's cv::ORB / cv::BFMatcher through the `opencv` crate.  Every entry point below
+ * names the reference call it replaces (paths are relative to the reference root).
+ *
+ * Conventions
+ *  - every `int` return: ORBX_OK (0) or a negative ORBX_E_* code; orbx_last_error() gives the text
+ *    (thread-local).  Empty inputs are not errors (matcher.rs:29-31, detector.rs:58-67).
+ *  - handles are not re-entrant (mirrors `&mut self` on every reference method); distinct handles are
+ *    independent and own their CUDA stream and device scratch.
+ *  - image / descriptor / result pointers may be HOST or DEVICE memory (detected with
+ *    cudaPointerGetAttributes).  Host pointers: the call copies in/out and returns when results are
+ *    ready.  Device pointers: work is enqueued on the handle's stream and the call returns without
+ *    synchronising (use orbx_*_sync).  Count outputs (`int*`) follow the same rule.
+ *  - descriptors are u8 rows of exactly 32 bytes, row pitch 32 (cv::Mat K x 32 CV_8U, contiguous).
+ *  - there is no CPU fallback: without a CUDA device every create call fails with ORBX_E_CUDA.
+ */
+#ifndef ORBX_H
+#define ORBX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_E_BADARG (-1)
+#define ORBX_E_CAPACITY (-2) /* result larger than the caller's buffer; count outputs hold the needed size */
+#define ORBX_E_CUDA (-3)
+#define ORBX_E_NOMEM (-4)
+
+#define ORBX_HARRIS_SCORE 0
+
+/* == cv::KeyPoint (28 B): consumed at src/odometry/pose.rs:36-41 (`kp.get(i).pt()`) */
+typedef struct {
+  float x, y;      /* level coordinates x level scale (fp32) */
+  float size;      /* 31 * level scale */
+  float angle;     /* degrees, [0,360) */
+  float response;  /* Harris response */
+  int32_t octave;  /* pyramid level */
+  int32_t class_id; /* -1 */
+} orbx_keypoint;
+
+/* == cv::DMatch (16 B): consumed at src/odometry/pose.rs:36-41, src/mapping/map.rs:111-115 */
+typedef struct {
+  int32_t query_idx, train_idx, img_idx; /* img_idx = 0 */
+  float distance;                        /* (float) Hamming distance */
+} orbx_dmatch;
+
+/* cv::ORB::create parameters.  orbx_default_params() = ORB::create_def() (detector.rs:16):
+ * 500, 1.2f, 8, 31, 0, 2, HARRIS_SCORE, 31, 20.  Only nfeatures and fast_threshold may differ
+ * from the defaults in this version (others -> ORBX_E_BADARG). */
+typedef struct {
+  int32_t nfeatures;
+  float scale_factor;
+  int32_t nlevels, edge_threshold, first_level, wta_k, score_type, patch_size, fast_threshold;
+} orbx_params;
+
+typedef struct orbx_detector orbx_detector;
+typedef struct orbx_matcher orbx_matcher;
+
+void orbx_default_params(orbx_params* p);
+
+/* ------------------------------------------------------------------ OrbDetector
+ * replaces OrbDetector::new (detector.rs:15-18).  Scratch is sized for images up to max_w x max_h
+ * and max_batch frames per call.  `params` may be NULL (defaults). */
+int orbx_detector_create(const orbx_params* params, int device, int max_w, int max_h, int max_batch,
+                         orbx_detector** out);
+void orbx_detector_destroy(orbx_detector* d);
+/* replaces OrbDetector::max_features (detector.rs:42-44) */
+int orbx_detector_max_features(const orbx_detector* d);
+
+/* replaces OrbDetector::detect (detector.rs:20-24): S1-S7, 8-bit single channel image, no mask.
+ * kps: cap entries.  *n = number of keypoints (if > cap: ORBX_E_CAPACITY, first cap are written). */
+int orbx_detect(orbx_detector* d, const uint8_t* img, int w, int h, size_t pitch, orbx_keypoint* kps,
+                int cap, int* n);
+/* replaces OrbDetector::detect_and_compute (detector.rs:26-40): S1-S9.  desc: cap x 32 bytes. */
+int orbx_detect_and_compute(orbx_detector* d, const uint8_t* img, int w, int h, size_t pitch,
+                            orbx_keypoint* kps, uint8_t* desc, int cap, int* n);
+/* the same over `batch` equally sized frames (frame i at imgs + i*frame_stride): the data-parallel
+ * form of the per-frame loop at examples/visual_odometry.rs:84-218.  kps: batch x cap, desc: batch x
+ * cap x 32 (may be NULL = detect only), n_per_frame: batch.  Keypoint order inside a frame: level
+ * major, then response descending, then (y, x) — OpenCV's intra-level order is a std::nth_element
+ * artefact, so parity is on sets keyed by (octave, x, y). */
+int orbx_detect_and_compute_batch(orbx_detector* d, const uint8_t* imgs, int w, int h, size_t pitch,
+                                  size_t frame_stride, int batch, orbx_keypoint* kps, uint8_t* desc,
+                                  int cap_per_frame, int* n_per_frame);
+int orbx_detector_sync(orbx_detector* d);
+/* run on a caller-owned CUDA stream (cudaStream_t as void*); NULL restores the handle's own stream */
+int orbx_detector_set_stream(orbx_detector* d, void* stream);
+
+/* Stage access for parity tests and profiling (device buffers owned by the handle, valid until
+ * the next call): level geometry and pointers of the pyramid (blurred=0) or of the blurred
+ * pyramid (blurred=1) of the last batch. */
+int orbx_detector_level_info(const orbx_detector* d, int level, int blurred, int* w, int* h, size_t* pitch,
+                             size_t* frame_stride, const uint8_t** dev_ptr);
+/* copies level `level` of frame `frame` of the last batch to host memory (rows of `w` bytes at out_pitch) */
+int orbx_detector_read_level(orbx_detector* d, int level, int blurred, int frame, uint8_t* host_out,
+                             size_t out_pitch);
+/* FAST+NMS candidates of the last batch: copies up to cap packed (score<<24|y<<12|x) entries of
+ * (frame, level) to host memory in unspecified order; *n = count. */
+int orbx_detector_candidates(orbx_detector* d, int frame, int level, uint32_t* out, int cap, int* n);
+
+/* Per-stage device timing (CUDA events on the handle's stream).  enable=1 makes every later call
+ * record events around each stage; orbx_detector_timing() synchronises and returns accumulated
+ * milliseconds and launch counts per stage since the last reset. */
+#define ORBX_STAGE_PYRAMID 0
+#define ORBX_STAGE_FAST 1
+#define ORBX_STAGE_HARRIS 2
+#define ORBX_STAGE_SELECT 3
+#define ORBX_STAGE_ORIENT 4
+#define ORBX_STAGE_BLUR 5
+#define ORBX_STAGE_BRIEF 6
+#define ORBX_STAGE_COUNT 7
+int orbx_detector_set_timing(orbx_detector* d, int enable);
+int orbx_detector_timing(orbx_detector* d, float* ms_per_stage, int* launches_per_stage, int reset);
+
+/* ------------------------------------------------------------------ FeatureMatcher
+ * replaces FeatureMatcher::new (matcher.rs:15-21) = BFMatcher::create(NORM_HAMMING, crossCheck).
+ * The reference always passes crossCheck=false. */
+int orbx_matcher_create(int device, int cross_check, orbx_matcher** out);
+void orbx_matcher_destroy(orbx_matcher* m);
+int orbx_matcher_sync(orbx_matcher* m);
+int orbx_matcher_set_stream(orbx_matcher* m, void* stream);
+
+/* replaces FeatureMatcher::match_descriptors (matcher.rs:24-37) = DescriptorMatcher::match, k=1:
+ * for each query row the train row of minimum Hamming distance, ties -> lowest train index.
+ * out: nq entries in query order; *n = nq (0 when either side is empty).  With cross_check=1 only
+ * mutual first-arg-min pairs survive, in ascending query_idx (cv::BFMatcher crossCheck). */
+int orbx_match(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out,
+               int* n);
+/* BFMatcher::knnMatch(k=2) (north_star stage 5): out: nq x 2, n_per_q[i] = min(2, nt).  With
+ * cross_check=1, n_per_q[i] is zeroed for queries failing the mutual-nearest test (OpenCV asserts
+ * on this combination). */
+int orbx_knn_match2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                    orbx_dmatch* out, int* n_per_q);
+/* Batched k=2 over `npairs` independent problems, device pointers only: problem p matches
+ * q + p*q_stride (nq_dev[p] rows) against t + p*t_stride (nt_dev[p] rows); strides in bytes; counts
+ * are device int arrays (clamped to max_rows).  out: npairs x max_rows x 2, n_per_q: npairs x max_rows.
+ * This is the frame-to-frame loop of examples/visual_odometry.rs:106 over a whole sequence. */
+int orbx_knn_match2_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const int* nq_dev,
+                          const uint8_t* t, size_t t_stride, const int* nt_dev, int npairs, int max_rows,
+                          orbx_dmatch* out, int* n_per_q);
+/* Lowe ratio test on a k=2 result: keeps knn2[2i] iff n_per_q[i] == 2 and d1 < ratio*d2 (fp32,
+ * strict).  Host or device arrays; order preserved. */
+int orbx_ratio_test(orbx_matcher* m, const orbx_dmatch* knn2, const int* n_per_q, int nq, float ratio,
+                    orbx_dmatch* out, int* n);
+/* replaces FeatureMatcher::filter_good_matches (matcher.rs:40-66): thr = max(ratio*min_dist, 30);
+ * keep distance < thr (strict), order preserved.  Host or device arrays. */
+int orbx_filter_good_matches(orbx_matcher* m, const orbx_dmatch* in, int n, float ratio, orbx_dmatch* out,
+                             int* n_out);
+/* batched device form: problem p has n_dev[p] matches at in + p*max_rows; out likewise. */
+int orbx_filter_good_matches_batch(orbx_matcher* m, const orbx_dmatch* in, const int* n_dev, int npairs,
+                                   int max_rows, float ratio, orbx_dmatch* out, int* n_out_dev);
+/* k=1 batched (device pointers), same addressing as orbx_knn_match2_batch; out: npairs x max_rows */
+int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const int* nq_dev,
+                     const uint8_t* t, size_t t_stride, const int* nt_dev, int npairs, int max_rows,
+                     orbx_dmatch* out, int* n_out_dev);
+
+/* matcher timing: accumulated ms / launches of the Hamming kernel */
+int orbx_matcher_set_timing(orbx_matcher* m, int enable);
+int orbx_matcher_timing(orbx_matcher* m, float* ms, int* launches, int reset);
+
+/* ------------------------------------------------------------------ misc */
+const char* orbx_last_error(void);
+const char* orbx_version(void);
+/* number of CUDA kernels this library has launched in this process */
+uint64_t orbx_launch_count(void);
+/* POPC-pipe microbenchmark (roofline denominator for S10): returns measured 32-bit POPC/s of
+ * `device` for mode 0 (POPC only) or 1 (POPC interleaved with the XOR/add mix of the match loop) */
+int orbx_popc_microbench(int device, int mode, double* popc_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H */

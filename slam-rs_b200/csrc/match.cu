@@ -1,0 +1,766 @@
+// S10 — brute-force NORM_HAMMING matcher (k=1 / k=2, cross-check, Lowe ratio, min-distance filter).
+//
+// Replaces cv::BFMatcher::knnMatchImpl -> cv::batchDistance reached from
+// /root/reference/src/feature/matcher.rs:34 (train_match) and the pure-Rust post filter at
+// matcher.rs:40-66.  Semantics: dist = popcount(q XOR t) over 256 bits;
+// K best in ascending (distance, trainIdx) order, i.e. ties go to the lowest train index.
+//
+// Kernel shape: one thread owns one query descriptor (8 x u32 in registers); the train set is streamed
+// through shared memory in 256-row tiles (cp.async double buffer) and every lane reads the same train
+// row (LDS.128 broadcast, conflict free).  Per (query, train) pair: 8 LOP3(xor) + 8 POPC + adds +
+// a packed-key min/max update of the running best-2: key = dist << 16 | local_train_idx, so the
+// lexicographic (distance, index) order is one unsigned compare and the lowest index wins ties.
+// This is POPC-pipe bound integer work; tensor cores are deliberately not used.
+#include <cooperative_groups.h>
+#include <cuda_pipeline.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+namespace orbx {
+
+constexpr int kQPB = 128;        // queries (= threads) per block
+constexpr int kTile = 256;       // train rows per shared-memory tile (8 KB)
+constexpr int kMaxSplitRows = 65536;  // local train index must fit 16 bits
+
+}  // namespace orbx
+
+struct orbx_matcher {
+  int device = 0;
+  int cross_check = 0;
+  int num_sms = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  // staging for host-pointer calls and partial results; grown on demand
+  void* buf[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  orbx::EventTimer timer;
+};
+
+namespace orbx {
+
+enum { B_Q = 0, B_T, B_OUT, B_CNT, B_PART, B_REV, B_OUT2, B_CNT2 };
+
+static int ensure(orbx_matcher* m, int which, size_t bytes) {
+  if (bytes <= m->cap[which]) return ORBX_OK;
+  if (m->buf[which]) {
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+    ORBX_CUDA(cudaFree(m->buf[which]));
+    m->buf[which] = nullptr;
+    m->cap[which] = 0;
+  }
+  size_t want = align_up(bytes + bytes / 4, 256);
+  cudaError_t e = cudaMalloc(&m->buf[which], want);
+  if (e != cudaSuccess) {
+    set_error("cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+    return ORBX_E_NOMEM;
+  }
+  m->cap[which] = want;
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Hamming k-best kernel
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+struct MatchArgs {
+  const uint8_t* q;
+  const uint8_t* t;
+  size_t q_stride, t_stride;  // bytes between problems
+  const int* nq_dev;          // per problem counts (device) or nullptr
+  const int* nt_dev;
+  int nq_fixed, nt_fixed;  // used when the pointers are null
+  int max_rows;            // clamp for device counts; output row pitch
+  int rows_per_split;      // multiple of kTile, <= kMaxSplitRows
+  int nsplits;
+  unsigned long long* part;  // [problem][split][max_rows][K] packed (dist<<32 | train_idx)
+  orbx_dmatch* out;          // used when nsplits == 1: [problem][max_rows][K]
+  int* n_per_q;              // optional [problem][max_rows] (K=2) ; for K=1: unused
+  int* n_out;                // optional per problem count (K=1 batch): nq or 0
+};
+
+template <int K>
+__device__ __forceinline__ void best_update(unsigned& b1, unsigned& b2, unsigned key) {
+  if (K == 1) {
+    b1 = min(b1, key);
+  } else {
+    unsigned hi = max(b1, key);
+    b1 = min(b1, key);
+    b2 = min(b2, hi);
+  }
+}
+
+template <int K>
+__global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
+  __shared__ uint4 tile[2][kTile * 2];
+  const int prob = blockIdx.z;
+  const int split = blockIdx.y;
+  int nq = a.nq_dev ? min(a.nq_dev[prob], a.max_rows) : a.nq_fixed;
+  int nt = a.nt_dev ? min(a.nt_dev[prob], a.max_rows) : a.nt_fixed;
+  const int q0 = blockIdx.x * kQPB;
+  if (q0 >= nq) return;
+  const int qi = q0 + threadIdx.x;
+  const bool active = qi < nq;
+
+  const int t_begin = split * a.rows_per_split;
+  const int t_end = min(nt, t_begin + a.rows_per_split);
+
+  const uint4* qp = reinterpret_cast<const uint4*>(a.q + (size_t)prob * a.q_stride);
+  const uint4* tp = reinterpret_cast<const uint4*>(a.t + (size_t)prob * a.t_stride);
+
+  uint4 qa = make_uint4(0, 0, 0, 0), qb = qa;
+  if (active) {
+    qa = __ldg(qp + (size_t)qi * 2);
+    qb = __ldg(qp + (size_t)qi * 2 + 1);
+  }
+  unsigned b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;
+
+  const int ntiles = t_end > t_begin ? (t_end - t_begin + kTile - 1) / kTile : 0;
+  auto issue = [&](int tl, int bufi) {
+    const int base = t_begin + tl * kTile;
+    const int rows = min(kTile, t_end - base);
+    const uint4* src = tp + (size_t)base * 2;
+    for (int i = threadIdx.x; i < rows * 2; i += kQPB) cp_async16(&tile[bufi][i], src + i);
+    cp_async_commit();
+  };
+  if (ntiles > 0) issue(0, 0);
+  for (int tl = 0; tl < ntiles; ++tl) {
+    const int cur = tl & 1;
+    if (tl + 1 < ntiles) {
+      issue(tl + 1, cur ^ 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    const int base_local = tl * kTile;
+    const int rows = min(kTile, t_end - (t_begin + base_local));
+    const uint4* tt = tile[cur];
+    int j = 0;
+#pragma unroll 4
+    for (; j + 4 <= rows; j += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        uint4 x = tt[(j + u) * 2], y = tt[(j + u) * 2 + 1];
+        unsigned d = __popc(qa.x ^ x.x) + __popc(qa.y ^ x.y) + __popc(qa.z ^ x.z) + __popc(qa.w ^ x.w) +
+                     __popc(qb.x ^ y.x) + __popc(qb.y ^ y.y) + __popc(qb.z ^ y.z) + __popc(qb.w ^ y.w);
+        best_update<K>(b1, b2, (d << 16) | (unsigned)(base_local + j + u));
+      }
+    }
+    for (; j < rows; ++j) {
+      uint4 x = tt[j * 2], y = tt[j * 2 + 1];
+      unsigned d = __popc(qa.x ^ x.x) + __popc(qa.y ^ x.y) + __popc(qa.z ^ x.z) + __popc(qa.w ^ x.w) +
+                   __popc(qb.x ^ y.x) + __popc(qb.y ^ y.y) + __popc(qb.z ^ y.z) + __popc(qb.w ^ y.w);
+      best_update<K>(b1, b2, (d << 16) | (unsigned)(base_local + j));
+    }
+    __syncthreads();
+  }
+  if (!active) return;
+
+  if (a.nsplits == 1) {
+    // fused epilogue: DMatch records straight from registers
+    orbx_dmatch* o = a.out + ((size_t)prob * a.max_rows + qi) * K;
+    int cnt = 0;
+    if (b1 != 0xFFFFFFFFu) {
+      o[0] = orbx_dmatch{qi, (int)(b1 & 0xFFFF), 0, (float)(b1 >> 16)};
+      cnt = 1;
+    }
+    if (K == 2 && b2 != 0xFFFFFFFFu) {
+      o[1] = orbx_dmatch{qi, (int)(b2 & 0xFFFF), 0, (float)(b2 >> 16)};
+      cnt = 2;
+    }
+    if (a.n_per_q) a.n_per_q[(size_t)prob * a.max_rows + qi] = cnt;
+    if (a.n_out && qi == 0) a.n_out[prob] = (nt > 0) ? nq : 0;
+  } else {
+    unsigned long long* p = a.part + (((size_t)prob * a.nsplits + split) * a.max_rows + qi) * K;
+    auto widen = [&](unsigned k) -> unsigned long long {
+      if (k == 0xFFFFFFFFu) return ~0ull;
+      return ((unsigned long long)(k >> 16) << 32) | (unsigned long long)(t_begin + (int)(k & 0xFFFF));
+    };
+    p[0] = widen(b1);
+    if (K == 2) p[1] = widen(b2);
+  }
+}
+
+// merge per-split partial best-K into DMatch records
+template <int K>
+__global__ void merge_splits_kernel(MatchArgs a) {
+  const int prob = blockIdx.y;
+  int nq = a.nq_dev ? min(a.nq_dev[prob], a.max_rows) : a.nq_fixed;
+  int nt = a.nt_dev ? min(a.nt_dev[prob], a.max_rows) : a.nt_fixed;
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi == 0 && a.n_out) a.n_out[prob] = (nt > 0) ? nq : 0;
+  if (qi >= nq) return;
+  unsigned long long b1 = ~0ull, b2 = ~0ull;
+  const int used = min(a.nsplits, (nt + a.rows_per_split - 1) / a.rows_per_split);
+  for (int s = 0; s < used; ++s) {
+    const unsigned long long* p = a.part + (((size_t)prob * a.nsplits + s) * a.max_rows + qi) * K;
+    for (int k = 0; k < K; ++k) {
+      unsigned long long key = p[k];
+      unsigned long long hi = max(b1, key);
+      b1 = min(b1, key);
+      b2 = min(b2, hi);
+    }
+  }
+  orbx_dmatch* o = a.out + ((size_t)prob * a.max_rows + qi) * K;
+  int cnt = 0;
+  if (b1 != ~0ull) {
+    o[0] = orbx_dmatch{qi, (int)(b1 & 0xFFFFFFFFu), 0, (float)(unsigned)(b1 >> 32)};
+    cnt = 1;
+  }
+  if (K == 2 && b2 != ~0ull) {
+    o[1] = orbx_dmatch{qi, (int)(b2 & 0xFFFFFFFFu), 0, (float)(unsigned)(b2 >> 32)};
+    cnt = 2;
+  }
+  if (a.n_per_q) a.n_per_q[(size_t)prob * a.max_rows + qi] = cnt;
+}
+
+// ------------------------------------------------------------------------------------------------
+// ordered compaction helpers (one block per problem; order preserved = ascending query index)
+// ------------------------------------------------------------------------------------------------
+constexpr int kCompactThreads = 1024;
+
+// returns the exclusive offset of this thread's flag within the block, and the block total
+__device__ __forceinline__ int block_excl_scan_flag(bool flag, int* warp_sums, int& total) {
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned bal = __ballot_sync(0xFFFFFFFFu, flag);
+  int within = __popc(bal & ((1u << lane) - 1));
+  if (lane == 0) warp_sums[warp] = __popc(bal);
+  __syncthreads();
+  if (warp == 0) {
+    int v = (lane < (blockDim.x >> 5)) ? warp_sums[lane] : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    warp_sums[lane] = incl - v;
+    if (lane == 31) warp_sums[32] = incl;
+  }
+  __syncthreads();
+  int off = warp_sums[warp] + within;
+  total = warp_sums[32];
+  __syncthreads();
+  return off;
+}
+
+// mode 0: Lowe ratio on knn2 (in: [rows][2], cnt: [rows]);  mode 1: min-distance filter on k=1 list
+// mode 2: cross-check of forward k=1 (in) against reverse k=1 (rev)
+__global__ void __launch_bounds__(kCompactThreads)
+compact_kernel(int mode, const orbx_dmatch* in, const int* cnt, const orbx_dmatch* rev, const int* n_dev,
+               int n_fixed, int max_rows, float ratio, orbx_dmatch* out, int* n_out) {
+  __shared__ int warp_sums[33];
+  __shared__ float s_min[32];
+  __shared__ float s_thr;
+  const int prob = blockIdx.x;
+  int n = n_dev ? min(n_dev[prob], max_rows) : n_fixed;
+  const size_t rowbase = (size_t)prob * max_rows;
+  const int stride_in = (mode == 0) ? 2 : 1;
+  in += rowbase * stride_in;
+  if (cnt) cnt += rowbase;
+  if (rev) rev += rowbase;
+  out += rowbase;
+
+  if (mode == 1) {
+    float mn = 3.402823466e+38f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) mn = fminf(mn, in[i].distance);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mn = fminf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+    if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = mn;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float m2 = s_min[0];
+      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m2 = fminf(m2, s_min[w]);
+      s_thr = fmaxf(__fmul_rn(ratio, m2), 30.0f);  // matcher.rs:58
+    }
+    __syncthreads();
+  }
+  int written = 0;
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int i = base + threadIdx.x;
+    bool keep = false;
+    orbx_dmatch m;
+    if (i < n) {
+      m = in[(size_t)i * stride_in];
+      if (mode == 0) {
+        keep = cnt[i] >= 2 && m.distance < __fmul_rn(ratio, in[(size_t)i * 2 + 1].distance);
+      } else if (mode == 1) {
+        keep = m.distance < s_thr;
+      } else {
+        keep = rev[m.train_idx].train_idx == i;
+      }
+    }
+    int total;
+    int off = block_excl_scan_flag(keep, warp_sums, total);
+    if (keep) out[written + off] = m;
+    written += total;
+  }
+  if (threadIdx.x == 0) n_out[prob] = written;
+}
+
+// zero n_per_q for queries failing the mutual-nearest test (k=2 + cross-check composition)
+__global__ void knn2_cross_mask_kernel(const orbx_dmatch* knn2, const orbx_dmatch* rev, int nq, int* n_per_q) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  if (n_per_q[i] == 0) return;
+  const int j = knn2[(size_t)i * 2].train_idx;
+  if (rev[j].train_idx != i) n_per_q[i] = 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side launch logic
+// ------------------------------------------------------------------------------------------------
+template <int K>
+static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs) {
+  const int rows_q = a.nq_dev ? a.max_rows : a.nq_fixed;
+  const int rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
+  if (rows_q <= 0 || npairs <= 0) return ORBX_OK;
+  const int qtiles = div_up(rows_q, kQPB);
+  // enough blocks for ~16 warps per SM over two waves, but never split below one tile
+  const long target = (long)m->num_sms * 8;
+  int splits = (int)std::min<long>(std::max<long>(1, target / std::max<long>(1, (long)qtiles * npairs)),
+                                   std::max(1, div_up(rows_t, kTile)));
+  int rps = (int)align_up((size_t)div_up(std::max(rows_t, 1), splits), kTile);
+  if (rps > kMaxSplitRows) rps = kMaxSplitRows;
+  splits = std::max(1, div_up(std::max(rows_t, 1), rps));
+  a.rows_per_split = rps;
+  a.nsplits = splits;
+  if (splits > 1) {
+    int rc = ensure(m, B_PART, (size_t)npairs * splits * a.max_rows * K * sizeof(unsigned long long));
+    if (rc) return rc;
+    a.part = (unsigned long long*)m->buf[B_PART];
+  }
+  dim3 grid(qtiles, splits, npairs);
+  m->timer.begin(0, m->stream);
+  hamming_knn_kernel<K><<<grid, kQPB, 0, m->stream>>>(a);
+  m->timer.end(m->stream);
+  ORBX_LAUNCH_CHECK();
+  if (splits > 1) {
+    dim3 g2(div_up(rows_q, 256), npairs);
+    merge_splits_kernel<K><<<g2, 256, 0, m->stream>>>(a);
+    ORBX_LAUNCH_CHECK();
+  }
+  return ORBX_OK;
+}
+
+}  // namespace orbx
+
+using namespace orbx;
+
+extern "C" {
+
+int orbx_matcher_create(int device, int cross_check, orbx_matcher** out) {
+  if (!out) {
+    set_error("orbx_matcher_create: out is NULL");
+    return ORBX_E_BADARG;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    set_error("orbx_matcher_create: CUDA device %d unavailable (%s); liborbx has no CPU fallback", device,
+              e != cudaSuccess ? cudaGetErrorString(e) : "index out of range");
+    return ORBX_E_CUDA;
+  }
+  ORBX_CUDA(cudaSetDevice(device));
+  orbx_matcher* m = new orbx_matcher();
+  m->device = device;
+  m->cross_check = cross_check ? 1 : 0;
+  cudaDeviceGetAttribute(&m->num_sms, cudaDevAttrMultiProcessorCount, device);
+  e = cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    set_error("cudaStreamCreate: %s", cudaGetErrorString(e));
+    delete m;
+    return ORBX_E_CUDA;
+  }
+  m->stream = m->own_stream;
+  *out = m;
+  return ORBX_OK;
+}
+
+void orbx_matcher_destroy(orbx_matcher* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  cudaStreamSynchronize(m->stream);
+  m->timer.destroy();
+  for (int i = 0; i < 8; ++i)
+    if (m->buf[i]) cudaFree(m->buf[i]);
+  if (m->own_stream) cudaStreamDestroy(m->own_stream);
+  delete m;
+}
+
+int orbx_matcher_sync(orbx_matcher* m) {
+  if (!m) return ORBX_E_BADARG;
+  ORBX_CUDA(cudaSetDevice(m->device));
+  ORBX_CUDA(cudaStreamSynchronize(m->stream));
+  return ORBX_OK;
+}
+
+int orbx_matcher_set_stream(orbx_matcher* m, void* stream) {
+  if (!m) return ORBX_E_BADARG;
+  m->stream = stream ? (cudaStream_t)stream : m->own_stream;
+  return ORBX_OK;
+}
+
+int orbx_matcher_set_timing(orbx_matcher* m, int enable) {
+  if (!m) return ORBX_E_BADARG;
+  m->timer.enabled = enable != 0;
+  return ORBX_OK;
+}
+
+int orbx_matcher_timing(orbx_matcher* m, float* ms, int* launches, int reset) {
+  if (!m) return ORBX_E_BADARG;
+  ORBX_CUDA(cudaSetDevice(m->device));
+  m->timer.collect();
+  if (ms) *ms = (float)m->timer.ms[0];
+  if (launches) *launches = m->timer.launches[0];
+  if (reset) m->timer.reset();
+  return ORBX_OK;
+}
+
+// stage a host array on the device if needed; returns the device pointer to use
+static int stage_in(orbx_matcher* m, int which, const void* p, size_t bytes, const void** dev) {
+  if (bytes == 0 || is_device_ptr(p)) {
+    *dev = p;
+    return ORBX_OK;
+  }
+  int rc = ensure(m, which, bytes);
+  if (rc) return rc;
+  ORBX_CUDA(cudaMemcpyAsync(m->buf[which], p, bytes, cudaMemcpyHostToDevice, m->stream));
+  *dev = m->buf[which];
+  return ORBX_OK;
+}
+
+static int set_count(orbx_matcher* m, int* n, int value) {
+  if (!n) return ORBX_OK;
+  if (is_device_ptr(n)) {
+    ORBX_CUDA(cudaMemcpyAsync(n, &value, sizeof(int), cudaMemcpyHostToDevice, m->stream));
+    ORBX_CUDA(cudaStreamSynchronize(m->stream));
+  } else {
+    *n = value;
+  }
+  return ORBX_OK;
+}
+
+// shared implementation of orbx_match / orbx_knn_match2 for one problem
+static int match_one(orbx_matcher* m, int K, const uint8_t* q, int nq, const uint8_t* t, int nt,
+                     orbx_dmatch* out, int* n_or_counts) {
+  if (!m || nq < 0 || nt < 0 || (nq > 0 && !q) || (nt > 0 && !t)) {
+    set_error("orbx match: bad argument");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  // empty guard == matcher.rs:29-31
+  if (nq == 0 || nt == 0) {
+    if (K == 1) return set_count(m, n_or_counts, 0);
+    if (nq > 0 && n_or_counts) {
+      if (is_device_ptr(n_or_counts))
+        ORBX_CUDA(cudaMemsetAsync(n_or_counts, 0, sizeof(int) * nq, m->stream));
+      else
+        for (int i = 0; i < nq; ++i) n_or_counts[i] = 0;
+    }
+    return ORBX_OK;
+  }
+  if (!out) {
+    set_error("orbx match: out is NULL");
+    return ORBX_E_BADARG;
+  }
+  const void *dq, *dt;
+  int rc;
+  if ((rc = stage_in(m, B_Q, q, (size_t)nq * 32, &dq))) return rc;
+  if ((rc = stage_in(m, B_T, t, (size_t)nt * 32, &dt))) return rc;
+  const bool out_dev = is_device_ptr(out);
+  const bool cnt_dev = n_or_counts && is_device_ptr(n_or_counts);
+  const bool cross = m->cross_check != 0;
+
+  // forward pass
+  orbx_dmatch* fwd;
+  const bool direct = out_dev && !(K == 1 && cross);
+  if (direct) {
+    fwd = out;
+  } else {
+    if ((rc = ensure(m, B_OUT, (size_t)nq * K * sizeof(orbx_dmatch)))) return rc;
+    fwd = (orbx_dmatch*)m->buf[B_OUT];
+  }
+  int* counts = nullptr;
+  if (K == 2) {
+    if (cnt_dev) {
+      counts = n_or_counts;
+    } else {
+      if ((rc = ensure(m, B_CNT, (size_t)nq * sizeof(int)))) return rc;
+      counts = (int*)m->buf[B_CNT];
+    }
+  }
+  MatchArgs a{};
+  a.q = (const uint8_t*)dq;
+  a.t = (const uint8_t*)dt;
+  a.nq_fixed = nq;
+  a.nt_fixed = nt;
+  a.max_rows = nq;
+  a.out = fwd;
+  a.n_per_q = counts;
+  if (K == 1)
+    rc = launch_knn<1>(m, a, 1);
+  else
+    rc = launch_knn<2>(m, a, 1);
+  if (rc) return rc;
+
+  int n_final = nq;
+  if (cross) {
+    // reverse k=1: train -> query
+    if ((rc = ensure(m, B_REV, (size_t)nt * sizeof(orbx_dmatch)))) return rc;
+    MatchArgs r{};
+    r.q = (const uint8_t*)dt;
+    r.t = (const uint8_t*)dq;
+    r.nq_fixed = nt;
+    r.nt_fixed = nq;
+    r.max_rows = nt;
+    r.out = (orbx_dmatch*)m->buf[B_REV];
+    if ((rc = launch_knn<1>(m, r, 1))) return rc;
+    if (K == 1) {
+      if ((rc = ensure(m, B_OUT2, (size_t)nq * sizeof(orbx_dmatch)))) return rc;
+      if ((rc = ensure(m, B_CNT2, sizeof(int)))) return rc;
+      orbx_dmatch* dst = out_dev ? out : (orbx_dmatch*)m->buf[B_OUT2];
+      compact_kernel<<<1, kCompactThreads, 0, m->stream>>>(2, fwd, nullptr, (orbx_dmatch*)m->buf[B_REV], nullptr,
+                                                          nq, nq, 0.f, dst, (int*)m->buf[B_CNT2]);
+      ORBX_LAUNCH_CHECK();
+      ORBX_CUDA(cudaMemcpyAsync(&n_final, m->buf[B_CNT2], sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+      ORBX_CUDA(cudaStreamSynchronize(m->stream));
+      fwd = dst;
+    } else {
+      knn2_cross_mask_kernel<<<div_up(nq, 256), 256, 0, m->stream>>>(fwd, (orbx_dmatch*)m->buf[B_REV], nq, counts);
+      ORBX_LAUNCH_CHECK();
+    }
+  }
+  if (!out_dev) {
+    const size_t rows = (K == 1) ? (size_t)n_final : (size_t)nq * 2;
+    if (rows)
+      ORBX_CUDA(cudaMemcpyAsync(out, fwd, rows * sizeof(orbx_dmatch), cudaMemcpyDeviceToHost, m->stream));
+  }
+  if (K == 2 && n_or_counts && !cnt_dev)
+    ORBX_CUDA(cudaMemcpyAsync(n_or_counts, counts, (size_t)nq * sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+  if (!out_dev || (n_or_counts && !cnt_dev)) ORBX_CUDA(cudaStreamSynchronize(m->stream));
+  if (K == 1) return set_count(m, n_or_counts, n_final);
+  return ORBX_OK;
+}
+
+int orbx_match(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* n) {
+  return match_one(m, 1, q, nq, t, nt, out, n);
+}
+
+int orbx_knn_match2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out,
+                    int* n_per_q) {
+  return match_one(m, 2, q, nq, t, nt, out, n_per_q);
+}
+
+static int batch_args_ok(orbx_matcher* m, const void* q, const void* t, const void* out, int npairs, int max_rows) {
+  if (!m || npairs < 0 || max_rows < 0) {
+    set_error("orbx batch match: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (npairs == 0 || max_rows == 0) return ORBX_OK;
+  if (!is_device_ptr(q) || !is_device_ptr(t) || !is_device_ptr(out)) {
+    set_error("orbx batch match: q, t and out must be device pointers");
+    return ORBX_E_BADARG;
+  }
+  return ORBX_OK;
+}
+
+int orbx_knn_match2_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const int* nq_dev, const uint8_t* t,
+                          size_t t_stride, const int* nt_dev, int npairs, int max_rows, orbx_dmatch* out,
+                          int* n_per_q) {
+  int rc = batch_args_ok(m, q, t, out, npairs, max_rows);
+  if (rc || npairs == 0 || max_rows == 0) return rc;
+  if (!nq_dev || !nt_dev || !is_device_ptr(nq_dev) || !is_device_ptr(nt_dev)) {
+    set_error("orbx_knn_match2_batch: counts must be device arrays");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  MatchArgs a{};
+  a.q = q;
+  a.t = t;
+  a.q_stride = q_stride;
+  a.t_stride = t_stride;
+  a.nq_dev = nq_dev;
+  a.nt_dev = nt_dev;
+  a.max_rows = max_rows;
+  a.out = out;
+  a.n_per_q = n_per_q;
+  if (n_per_q)
+    ORBX_CUDA(cudaMemsetAsync(n_per_q, 0, (size_t)npairs * max_rows * sizeof(int), m->stream));
+  return launch_knn<2>(m, a, npairs);
+}
+
+int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const int* nq_dev, const uint8_t* t,
+                     size_t t_stride, const int* nt_dev, int npairs, int max_rows, orbx_dmatch* out,
+                     int* n_out_dev) {
+  int rc = batch_args_ok(m, q, t, out, npairs, max_rows);
+  if (rc || npairs == 0 || max_rows == 0) return rc;
+  if (!nq_dev || !nt_dev || !is_device_ptr(nq_dev) || !is_device_ptr(nt_dev) || !n_out_dev ||
+      !is_device_ptr(n_out_dev)) {
+    set_error("orbx_match_batch: counts must be device arrays");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  ORBX_CUDA(cudaMemsetAsync(n_out_dev, 0, (size_t)npairs * sizeof(int), m->stream));
+  MatchArgs a{};
+  a.q = q;
+  a.t = t;
+  a.q_stride = q_stride;
+  a.t_stride = t_stride;
+  a.nq_dev = nq_dev;
+  a.nt_dev = nt_dev;
+  a.max_rows = max_rows;
+  a.out = out;
+  a.n_out = n_out_dev;
+  return launch_knn<1>(m, a, npairs);
+}
+
+// one-problem compaction for host or device arrays
+static int compact_one(orbx_matcher* m, int mode, const orbx_dmatch* in, const int* cnt, int n, float ratio,
+                       orbx_dmatch* out, int* n_out) {
+  if (!m || n < 0 || !n_out) {
+    set_error("orbx filter: bad argument");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  if (n == 0) return set_count(m, n_out, 0);
+  if (!in || !out || (mode == 0 && !cnt)) {
+    set_error("orbx filter: NULL array");
+    return ORBX_E_BADARG;
+  }
+  const size_t in_rows = (mode == 0) ? (size_t)n * 2 : (size_t)n;
+  const void *din, *dcnt = nullptr;
+  int rc;
+  if ((rc = stage_in(m, B_OUT, in, in_rows * sizeof(orbx_dmatch), &din))) return rc;
+  if (mode == 0 && (rc = stage_in(m, B_CNT, cnt, (size_t)n * sizeof(int), &dcnt))) return rc;
+  const bool out_dev = is_device_ptr(out);
+  orbx_dmatch* dout = out;
+  if (!out_dev) {
+    if ((rc = ensure(m, B_OUT2, (size_t)n * sizeof(orbx_dmatch)))) return rc;
+    dout = (orbx_dmatch*)m->buf[B_OUT2];
+  }
+  if ((rc = ensure(m, B_CNT2, sizeof(int)))) return rc;
+  compact_kernel<<<1, kCompactThreads, 0, m->stream>>>(mode, (const orbx_dmatch*)din, (const int*)dcnt, nullptr,
+                                                      nullptr, n, n, ratio, dout, (int*)m->buf[B_CNT2]);
+  ORBX_LAUNCH_CHECK();
+  int cnt_h = 0;
+  ORBX_CUDA(cudaMemcpyAsync(&cnt_h, m->buf[B_CNT2], sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+  ORBX_CUDA(cudaStreamSynchronize(m->stream));
+  if (!out_dev && cnt_h)
+    ORBX_CUDA(cudaMemcpy(out, dout, (size_t)cnt_h * sizeof(orbx_dmatch), cudaMemcpyDeviceToHost));
+  return set_count(m, n_out, cnt_h);
+}
+
+int orbx_ratio_test(orbx_matcher* m, const orbx_dmatch* knn2, const int* n_per_q, int nq, float ratio,
+                    orbx_dmatch* out, int* n) {
+  return compact_one(m, 0, knn2, n_per_q, nq, ratio, out, n);
+}
+
+int orbx_filter_good_matches(orbx_matcher* m, const orbx_dmatch* in, int n, float ratio, orbx_dmatch* out,
+                             int* n_out) {
+  return compact_one(m, 1, in, nullptr, n, ratio, out, n_out);
+}
+
+int orbx_filter_good_matches_batch(orbx_matcher* m, const orbx_dmatch* in, const int* n_dev, int npairs,
+                                   int max_rows, float ratio, orbx_dmatch* out, int* n_out_dev) {
+  if (!m || npairs < 0 || max_rows < 0) {
+    set_error("orbx_filter_good_matches_batch: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (npairs == 0) return ORBX_OK;
+  if (!is_device_ptr(in) || !is_device_ptr(out) || !is_device_ptr(n_dev) || !is_device_ptr(n_out_dev)) {
+    set_error("orbx_filter_good_matches_batch: device pointers required");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  compact_kernel<<<npairs, kCompactThreads, 0, m->stream>>>(1, in, nullptr, nullptr, n_dev, 0, max_rows, ratio, out,
+                                                           n_out_dev);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// POPC-pipe microbenchmark: the denominator of the S10 roofline
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+template <int MODE>
+__global__ void popc_bench_kernel(unsigned* out, int iters, unsigned seed) {
+  unsigned v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
+  unsigned acc = 0, b1 = ~0u, b2 = ~0u;
+  for (int it = 0; it < iters; ++it) {
+    if (MODE == 0) {
+      // 8 independent POPC per iteration; operands change every iteration through a cheap add
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        unsigned p = __popc(v[i]);
+        v[i] = v[i] + p + 0x01010101u;
+      }
+    } else {
+      unsigned d = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d += __popc(v[i] ^ (acc + i));
+      unsigned key = (d << 16) | (unsigned)(it & 0xFFFF);
+      unsigned hi = max(b1, key);
+      b1 = min(b1, key);
+      b2 = min(b2, hi);
+      acc += 0x9E3779B9u;
+    }
+  }
+  unsigned r = acc ^ b1 ^ b2;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r ^= v[i];
+  if (r == 0x12345678u) out[0] = r;  // keep the work alive
+}
+
+extern "C" {
+
+int orbx_popc_microbench(int device, int mode, double* popc_per_s) {
+  if (!popc_per_s) return ORBX_E_BADARG;
+  ORBX_CUDA(cudaSetDevice(device));
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  unsigned* d = nullptr;
+  ORBX_CUDA(cudaMalloc(&d, 4));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  const int iters = 1 << 14, threads = 256, blocks = sms * 8;
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    cudaEventRecord(e0);
+    if (mode == 0)
+      popc_bench_kernel<0><<<blocks, threads>>>(d, iters, 12345u + rep);
+    else
+      popc_bench_kernel<1><<<blocks, threads>>>(d, iters, 12345u + rep);
+    g_launches.fetch_add(1);
+    cudaEventRecord(e1);
+    ORBX_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep > 0 && ms < best) best = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *popc_per_s = (double)blocks * threads * (double)iters * 8.0 / (best * 1e-3);
+  return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,357 @@
+// S3-S7 — retainBest(2N_l) by FAST score, Harris response, retainBest(N_l) by Harris, intensity-
+// centroid orientation, keypoint assembly.
+//
+// Replaces KeyPointsFilter::retainBest, HarrisResponses, ICAngles and the pt*=scale loop of
+// cv::ORB_Impl::computeKeyPoints (reached from /root/reference/src/feature/detector.rs:22,32).
+// Arithmetic per SURVEY.md Appendix A S3-S7: both selections keep *all* entries >= the n-th best
+// (ties kept); Harris sums are int32 and the final expression is non-fused fp32; the angle is
+// cv::fastAtan2's polynomial in non-fused fp32.
+#include "detector.cuh"
+
+namespace orbx {
+
+// order-preserving float -> uint key; every real response maps to a key > 0 (0 = "not selected")
+__device__ __forceinline__ uint32_t float_key(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
+}
+
+// ------------------------------------------------------------------------------------------------
+// S3 + S4: threshold from the score histogram, Harris for the survivors
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float harris_at(const uint8_t* img, int pitch, int x, int y) {
+  // 9x9 window, rows y-4..y+4; rolling rows of horizontal difference / smoothing (7 columns each)
+  int hd[3][7], hs[3][7];
+  int a = 0, b = 0, c = 0;
+#pragma unroll
+  for (int r = 0; r < 9; ++r) {
+    const uint8_t* p = img + (size_t)(y - 4 + r) * pitch + (x - 4);
+    int v[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) v[i] = __ldg(p + i);
+    const int slot = r % 3;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      hd[slot][i] = v[i + 2] - v[i];
+      hs[slot][i] = v[i] + 2 * v[i + 1] + v[i + 2];
+    }
+    if (r >= 2) {
+      const int s0 = (r - 2) % 3, s1 = (r - 1) % 3, s2 = slot;
+#pragma unroll
+      for (int i = 0; i < 7; ++i) {
+        const int Ix = hd[s0][i] + 2 * hd[s1][i] + hd[s2][i];
+        const int Iy = hs[s2][i] - hs[s0][i];
+        a += Ix * Ix;
+        b += Iy * Iy;
+        c += Ix * Iy;
+      }
+    }
+  }
+  const float scale = 1.0f / (4.0f * 7.0f * 255.0f);
+  const float s4 = __fmul_rn(__fmul_rn(__fmul_rn(scale, scale), scale), scale);
+  const float fa = (float)a, fb = (float)b, fc = (float)c;
+  const float t1 = __fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc));
+  const float sum = __fadd_rn(fa, fb);
+  const float t2 = __fmul_rn(__fmul_rn(0.04f, sum), sum);
+  return __fmul_rn(__fsub_rn(t1, t2), s4);
+}
+
+constexpr int kHarrisBlocksPerLevel = 8;
+
+__global__ void __launch_bounds__(256) harris_kernel(DevGeom g) {
+  __shared__ uint32_t s_hist[256];
+  __shared__ int s_thr;
+  __shared__ uint32_t s_queue[512];
+  __shared__ uint32_t s_qn;
+  const int l = blockIdx.y, frame = blockIdx.z;
+  const DevLevel& L = g.lv[l];
+  const size_t fl = (size_t)frame * kMaxLevels + l;
+  const uint32_t count = min(g.cand_count[fl], (uint32_t)L.cand_cap);
+  if (count == 0) return;
+  const int tid = threadIdx.x;
+
+  // S3: thr = largest score s with #(score >= s) >= 2*N_l; everything if the list is short
+  s_hist[tid] = g.hist[fl * 256 + tid];
+  if (tid == 0) {
+    s_thr = 0;
+    s_qn = 0;
+  }
+  __syncthreads();
+  const uint32_t n_keep = 2u * (uint32_t)L.quota;
+  if (tid == 0) {
+    if (n_keep == 0) {
+      s_thr = 256;  // retainBest(0): nothing survives
+    } else if (count > n_keep) {
+      uint32_t acc = 0;
+      int s = 255;
+      for (; s > 0; --s) {
+        acc += s_hist[s];
+        if (acc >= n_keep) break;
+      }
+      s_thr = s;
+    }
+  }
+  __syncthreads();
+  const int thr = s_thr;
+  const uint32_t* cand = L.cand + (size_t)frame * L.cand_cap;
+  uint32_t* key = L.key + (size_t)frame * L.cand_cap;
+  const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
+
+  // block-compacted processing: gather survivors into a queue, run Harris on dense batches
+  const uint32_t per_block = (count + gridDim.x - 1) / gridDim.x;
+  const uint32_t begin = blockIdx.x * per_block;
+  const uint32_t end = min(count, begin + per_block);
+  for (uint32_t base = begin; base < end; base += 256) {
+    const uint32_t i = base + tid;
+    if (i < end) {
+      const uint32_t cw = cand[i];
+      if ((int)(cw >> 24) >= thr) {
+        s_queue[atomicAdd(&s_qn, 1u)] = i;
+      } else {
+        key[i] = 0;
+      }
+    }
+    __syncthreads();
+    const bool last = base + 256 >= end;
+    uint32_t qn = s_qn;
+    if (qn >= 256 || last) {
+      for (uint32_t off = 0; off < qn; off += 256) {
+        if (off + tid < qn) {
+          const uint32_t j = s_queue[off + tid];
+          const uint32_t cw = cand[j];
+          key[j] = float_key(harris_at(img, L.pitch, (int)(cw & 0xFFF), (int)((cw >> 12) & 0xFFF)));
+        }
+      }
+      __syncthreads();
+      if (tid == 0) s_qn = 0;
+    }
+    __syncthreads();
+  }
+}
+
+int launch_harris(const DevGeom& g, cudaStream_t s) {
+  if (g.batch == 0) return ORBX_OK;
+  dim3 grid(kHarrisBlocksPerLevel, g.nlevels, g.batch);
+  harris_kernel<<<grid, 256, 0, s>>>(g);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// S5: radix select of the N_l-th largest Harris key, compaction, bitonic sort (response desc, y, x)
+// ------------------------------------------------------------------------------------------------
+constexpr int kSelThreads = 512;
+
+__global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort_cap) {
+  extern __shared__ __align__(16) unsigned long long s_sort[];  // sort_cap entries
+  __shared__ uint32_t s_hist[256];
+  __shared__ uint32_t s_prefix, s_remaining, s_nvalid, s_nsel;
+  const int l = blockIdx.x, frame = blockIdx.y;
+  const DevLevel& L = g.lv[l];
+  const size_t fl = (size_t)frame * kMaxLevels + l;
+  const uint32_t count = min(g.cand_count[fl], (uint32_t)L.cand_cap);
+  const int tid = threadIdx.x;
+  if (count == 0 || L.quota == 0) {
+    if (tid == 0) g.sel_count[fl] = 0;
+    return;
+  }
+  const uint32_t* cand = L.cand + (size_t)frame * L.cand_cap;
+  const uint32_t* key = L.key + (size_t)frame * L.cand_cap;
+
+  if (tid == 0) {
+    s_nvalid = 0;
+    s_nsel = 0;
+  }
+  __syncthreads();
+  {
+    uint32_t nv = 0;
+    for (uint32_t i = tid; i < count; i += kSelThreads) nv += key[i] != 0;
+    for (int o = 16; o > 0; o >>= 1) nv += __shfl_xor_sync(0xFFFFFFFFu, nv, o);
+    if ((tid & 31) == 0 && nv) atomicAdd(&s_nvalid, nv);
+  }
+  __syncthreads();
+  const uint32_t nvalid = s_nvalid;
+  uint32_t thr = 1;  // keep every valid entry
+  if (nvalid > (uint32_t)L.quota) {
+    // MSB-first 8-bit radix select of the quota-th largest key
+    if (tid == 0) {
+      s_prefix = 0;
+      s_remaining = (uint32_t)L.quota;
+    }
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      if (tid < 256) s_hist[tid] = 0;
+      __syncthreads();
+      const uint32_t prefix = s_prefix;
+      const uint32_t mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
+      for (uint32_t i = tid; i < count; i += kSelThreads) {
+        const uint32_t k = key[i];
+        if (k != 0 && (k & mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 0xFF], 1u);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        uint32_t rem = s_remaining, acc = 0;
+        int b = 255;
+        for (; b > 0; --b) {
+          if (acc + s_hist[b] >= rem) break;
+          acc += s_hist[b];
+        }
+        s_prefix = prefix | ((uint32_t)b << shift);
+        s_remaining = rem - acc;
+      }
+      __syncthreads();
+    }
+    thr = s_prefix;
+  }
+  // compaction into the sort buffer
+  for (uint32_t i = tid; i < count; i += kSelThreads) {
+    const uint32_t k = key[i];
+    if (k != 0 && k >= thr) {
+      const uint32_t slot = atomicAdd(&s_nsel, 1u);
+      if (slot < (uint32_t)sort_cap)
+        s_sort[slot] = ((unsigned long long)k << 32) | (unsigned long long)(0xFFFFFFu - (cand[i] & 0xFFFFFFu));
+    }
+  }
+  __syncthreads();
+  uint32_t nsel = s_nsel;
+  if (nsel > (uint32_t)L.sel_cap || nsel > (uint32_t)sort_cap) {
+    if (tid == 0) atomicExch(g.flags, (int)nsel);
+    nsel = min(nsel, (uint32_t)min(L.sel_cap, sort_cap));
+  }
+  uint32_t n2 = 1;
+  while (n2 < nsel) n2 <<= 1;
+  for (uint32_t i = nsel + tid; i < n2; i += kSelThreads) s_sort[i] = 0ull;
+  __syncthreads();
+  // bitonic sort, descending
+  for (uint32_t k = 2; k <= n2; k <<= 1) {
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t i = tid; i < n2; i += kSelThreads) {
+        const uint32_t p = i ^ j;
+        if (p > i) {
+          const unsigned long long a = s_sort[i], b = s_sort[p];
+          const bool desc = (i & k) == 0;
+          if (desc ? (a < b) : (a > b)) {
+            s_sort[i] = b;
+            s_sort[p] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  unsigned long long* sel = L.sel + (size_t)frame * L.sel_cap;
+  for (uint32_t i = tid; i < nsel; i += kSelThreads) sel[i] = s_sort[i];
+  if (tid == 0) g.sel_count[fl] = nsel;
+}
+
+int launch_select(const DevGeom& g, int sort_cap, cudaStream_t s) {
+  if (g.batch == 0) return ORBX_OK;
+  const size_t smem = (size_t)sort_cap * sizeof(unsigned long long);
+  static int configured = 0;
+  if (smem > 48 * 1024 && configured < (int)smem) {
+    ORBX_CUDA(cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = (int)smem;
+  }
+  dim3 grid(g.nlevels, g.batch);
+  select_kernel<<<grid, kSelThreads, smem, s>>>(g, sort_cap);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// S6 + S7: one warp per keypoint — IC moments over the radius-15 disc, fastAtan2, keypoint record
+// ------------------------------------------------------------------------------------------------
+__constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  const float s = (float)(180.0 / 3.14159265358979323846);
+  const float P1 = __fmul_rn(0.9997878412794807f, s), P3 = __fmul_rn(-0.3258083974640975f, s);
+  const float P5 = __fmul_rn(0.1555786518463281f, s), P7 = __fmul_rn(-0.04432655554792128f, s);
+  const float eps = 2.220446049250313e-16f;
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(P7, c2), P5), c2), P3), c2), P1), c);
+  } else {
+    c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.0f,
+                  __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(P7, c2), P5), c2), P3), c2), P1), c));
+  }
+  if (x < 0.0f) a = __fsub_rn(180.0f, a);
+  if (y < 0.0f) a = __fsub_rn(360.0f, a);
+  return a;
+}
+
+constexpr int kOrientWarps = 8;
+
+__global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, OutArgs o) {
+  const int frame = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // level-major prefix over the per-level selections of this frame
+  uint32_t pre[kMaxLevels + 1];
+  pre[0] = 0;
+#pragma unroll
+  for (int l = 0; l < kMaxLevels; ++l)
+    pre[l + 1] = pre[l] + (l < g.nlevels ? g.sel_count[(size_t)frame * kMaxLevels + l] : 0u);
+  const uint32_t total = pre[kMaxLevels];
+  if (blockIdx.x == 0 && threadIdx.x == 0) o.n[frame] = (int)total;
+  const uint32_t limit = min(total, (uint32_t)min(o.cap, o.lvl_cap));
+  const uint32_t j = blockIdx.x * kOrientWarps + warp;
+  if (j >= limit) return;
+  int l = 0;
+#pragma unroll
+  for (int i = 1; i < kMaxLevels; ++i)
+    if (j >= pre[i]) l = i;
+  const DevLevel& L = g.lv[l];
+  const unsigned long long e = L.sel[(size_t)frame * L.sel_cap + (j - pre[l])];
+  const uint32_t pos = 0xFFFFFFu - (uint32_t)(e & 0xFFFFFFu);
+  const int x = (int)(pos & 0xFFF), y = (int)(pos >> 12);
+  const float response = key_float((uint32_t)(e >> 32));
+
+  const uint8_t* img = L.img + (size_t)frame * L.frame_stride + (size_t)y * L.pitch + x;
+  const int u = lane - 15;  // lanes 0..30 cover u = -15..15
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {
+    for (int v = -15; v <= 15; ++v) {
+      if (abs(u) <= c_umax[abs(v)]) {
+        const int p = __ldg(img + v * L.pitch + u);
+        m10 += u * p;
+        m01 += v * p;
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, s);
+    m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, s);
+  }
+  if (lane == 0) {
+    orbx_keypoint kp;
+    kp.x = __fmul_rn((float)x, L.scale);
+    kp.y = __fmul_rn((float)y, L.scale);
+    kp.size = __fmul_rn(31.0f, L.scale);
+    kp.angle = fast_atan2_deg((float)m01, (float)m10);
+    kp.response = response;
+    kp.octave = l;
+    kp.class_id = -1;
+    o.kps[(size_t)frame * o.cap + j] = kp;
+    o.kp_lvl[(size_t)frame * o.lvl_cap + j] = ((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+  }
+}
+
+int launch_orient(const DevGeom& g, const OutArgs& o, cudaStream_t s) {
+  if (g.batch == 0) return ORBX_OK;
+  const int lim = o.cap < o.lvl_cap ? o.cap : o.lvl_cap;
+  dim3 grid(div_up(lim > 0 ? lim : 1, kOrientWarps), g.batch);
+  orient_kernel<<<grid, kOrientWarps * 32, 0, s>>>(g, o);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
+}  // namespace orbx
