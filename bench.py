@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py — ORB extract + frame-to-frame Hamming match throughput (frames/s @1241x376).
+
+Workload (BASELINE.json configs[1]): a KITTI-shaped synthetic sequence of T=1000
+grayscale 1241x376 frames per GPU, nfeatures=2000.  One step = one pass of the hot path over the
+sequence: S1-S9 on every frame and the T-1 (t-1 -> t) matching problems (BFMatcher k=2 + cross-check
+mutual test + Lowe ratio 0.75).  N>1: every rank owns an independent sequence (weak scaling, no
+data-path collective — SURVEY.md §8e); value = all frames / max-over-ranks time.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          our arm (liborbx on B200)
+  python bench.py --impl reference ...                          reference arm: cv2 (= the OpenCV code the
+                                                                reference binds) on the host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W_IMG, H_IMG, NFEAT, T_SEQ = 1241, 376, 2000, 1000
+RATIO = 0.75
+METRIC = "ORB extract+match frames/s @1241x376"
+WORKLOAD = ("C2 KITTI-shaped synthetic sequence 1241x376 x %d frames/GPU, nfeatures=2000, 8 levels, "
+            "frame-to-frame BFMatcher Hamming k=2 + cross-check + Lowe 0.75")
+
+
+def load_synth():
+    import importlib.util as u
+    spec = u.spec_from_file_location("_orbx_synth", os.path.join(ROOT, "slam-rs_b200", "synth.py"))
+    m = u.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            j = json.load(open(p))
+            return float(j["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU reference: cv2 == the cv::ORB / cv::BFMatcher code the reference calls (detector.rs:32, matcher.rs:34)
+# ---------------------------------------------------------------------------------------------------
+def cpu_pass(frames, threads):
+    """One pass of the same hot path with OpenCV on the host: returns (seconds, frames_done)."""
+    import cv2
+    cv2.setNumThreads(threads)
+    orb = cv2.ORB_create(nfeatures=NFEAT)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING, False)
+    bfx = cv2.BFMatcher(cv2.NORM_HAMMING, True)
+    t0 = time.perf_counter()
+    prev = None
+    for img in frames:
+        _, desc = orb.detectAndCompute(img, None)
+        if prev is not None and desc is not None and len(prev) and len(desc):
+            knn = bf.knnMatch(prev, desc, k=2)
+            mutual = {m.queryIdx for m in bfx.match(prev, desc)}
+            _ = [p[0] for p in knn if len(p) == 2 and p[0].queryIdx in mutual
+                 and np.float32(p[0].distance) < np.float32(RATIO) * np.float32(p[1].distance)]
+        prev = desc
+    return time.perf_counter() - t0, len(frames)
+
+
+def cpu_baseline(frames_sample, threads):
+    import cv2
+    cpu_pass(frames_sample[:3], threads)  # warm-up
+    dt, n = cpu_pass(frames_sample, threads)
+    return {"value": n / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
+            "sample": "cv2 %s ORB_create(nfeatures=2000).detectAndCompute + BFMatcher knnMatch(k=2) + crossCheck match "
+                      "+ Lowe 0.75 on the first %d frames of the same sequence, %d OpenCV threads, %.1f s"
+                      % (cv2.__version__, n, threads, dt)}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    synth = load_synth()
+    threads = os.cpu_count() or 1
+    nsample = args.ref_frames
+    frames = synth.sequence(H_IMG, W_IMG, nsample)
+    import cv2
+    for _ in range(args.warmup):
+        cpu_pass(frames[:4], threads)
+    times = []
+    for _ in range(args.steps):
+        dt, n = cpu_pass(frames, threads)
+        times.append(dt)
+    tot = sum(times)
+    val = nsample * args.steps / tot
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD % T_SEQ, "sample_frames_per_step": nsample},
+        "cpu_baseline": {"value": val, "unit": "frames/s", "cores": threads, "kind": "reference",
+                         "sample": "cv2 %s (the OpenCV code the reference binds) on %d frames per step, %d threads"
+                                   % (cv2.__version__, nsample, threads)},
+        "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------
+def pyramid_pixels(h, w):
+    sf = np.float32(1.2)
+    tot = []
+    for l in range(8):
+        inv = np.float32(1.0) / np.float32(np.power(np.float64(sf), np.float64(l)))
+        tot.append(int(np.rint(np.float32(h) * inv)) * int(np.rint(np.float32(w) * inv)))
+    return tot
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — liborbx has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import slam_rs_b200 as orbx
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    synth = load_synth()
+
+    T = args.frames
+    # every rank owns an independent sequence (canvas seed differs): weak scaling, no collective
+    frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
+    fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
+                          ratio=RATIO, cross_check=True)
+    frames_pinned = torch.from_numpy(frames).pin_memory()
+    frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
+    frames_dev[:, :, :W_IMG].copy_(frames_pinned)
+    host_out = fe.alloc_host_outputs()
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident: warm-up, then K timed steps with per-stage event timers on
+    for _ in range(args.warmup):
+        fe.run_device(frames_dev)
+    barrier()
+    fe.det.set_timing(True)
+    fe.matcher.set_timing(True)
+    fe.det.timing(reset=True)
+    fe.matcher.timing(reset=True)
+    launches0 = orbx.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        fe.run_device(frames_dev)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = orbx.launch_count() - launches0
+    stage = fe.det.timing(reset=True)
+    match_ms, match_launches = fe.matcher.timing(reset=True)
+    fe.det.set_timing(False)
+    fe.matcher.set_timing(False)
+
+    # ---- end to end through the public API with HOST buffers (pinned): H2D + kernels + D2H per step
+    for _ in range(max(1, args.warmup // 2)):
+        fe.run_host(frames_pinned, host_out)
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        fe.run_host(frames_pinned, host_out)
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop()
+
+    # ---- work accounting
+    n_dev = fe.n[:T].cpu().numpy().astype(np.int64)
+    n_dev = np.minimum(n_dev, fe.cap)
+    pairs_fwd = int(np.sum(n_dev[:-1] * n_dev[1:]))
+    pairs_per_step = 2 * pairs_fwd  # forward k=2 + reverse k=1 (cross-check)
+    K_mean = float(n_dev.mean())
+    n_good = int(host_out["n_good"][1:T].numpy().astype(np.int64).sum())
+    cand0 = 0
+    try:
+        fe.det.detect_and_compute_device(frames_dev[:1], fe.kps[:1], fe.desc[:1], fe.n[:1], width=W_IMG)
+        cand0 = sum(len(fe.det.candidates(l, 0)[0]) for l in range(8))
+    except Exception:
+        pass
+
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    frames_all = T * world * args.steps
+    value = frames_all / (ms_total * 1e-3)
+    e2e_value = frames_all / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        hbm_peak, peak_kind = measured_peaks()
+        P = sum(pyramid_pixels(H_IMG, W_IMG))
+        frames_timed = T * args.steps
+        popc = None
+        import ctypes as C
+        v = C.c_double()
+        if orbx.lib.orbx_popc_microbench(local_rank, 0, C.byref(v)) == 0:
+            popc = v.value
+        alg = {
+            "pyramid": P, "fast": P + 8 * cand0, "brief": 2 * P + 572 * K_mean,
+        }
+        stages = {}
+        for name, (ms, ln) in stage.items():
+            stages[name] = {"ms_per_step": ms / args.steps, "launches_per_step": ln / args.steps}
+        stages["hamming"] = {"ms_per_step": match_ms / args.steps, "launches_per_step": match_launches / args.steps}
+        for name, nbytes in (("pyramid", alg["pyramid"]), ("fast", alg["fast"])):
+            gbs = nbytes * frames_timed / (stage[name][0] * 1e-3) / 1e9
+            stages[name].update({"bound": "hbm", "achieved_gbs": gbs, "frac": gbs / hbm_peak})
+        bb_ms = stage["blur"][0] + stage["brief"][0]
+        gbs = alg["brief"] * frames_timed / (bb_ms * 1e-3) / 1e9
+        stages["blur+brief"] = {"ms_per_step": bb_ms / args.steps, "bound": "hbm", "achieved_gbs": gbs,
+                                "frac": gbs / hbm_peak}
+        pairs_s = pairs_per_step * args.steps / (match_ms * 1e-3)
+        stages["hamming"].update({"bound": "popc", "pairs_per_s": pairs_s, "achieved_tpopc": pairs_s * 8 / 1e12,
+                                  "peak_tpopc": popc / 1e12 if popc else None,
+                                  "frac": (pairs_s * 8 / popc) if popc else None})
+        # dominant kernel of the step
+        dom = max(("pyramid", "fast", "harris", "select", "orient", "blur", "brief", "hamming"),
+                  key=lambda k: stages[k]["ms_per_step"])
+        if dom == "hamming":
+            launches_dom = match_launches
+            roof = {"kernel": "hamming_knn_kernel", "bound": "popc", "achieved": pairs_s * 8 / 1e12,
+                    "peak": popc / 1e12 if popc else None, "unit": "TPOPC/s",
+                    "frac": (pairs_s * 8 / popc) if popc else None, "traffic": None,
+                    "peak_source": "orbx_popc_microbench (measured in this run; POPC is 16 lanes/clk/SM)",
+                    "avg_launch_ms": match_ms / max(match_launches, 1),
+                    "note": "integer XOR+POPC work: neither HBM nor tensor bound (north_star stage 5)"}
+        else:
+            key = {"blur": "blur+brief", "brief": "blur+brief"}.get(dom, dom)
+            s = stages.get(key, {})
+            roof = {"kernel": dom, "bound": "hbm", "achieved": s.get("achieved_gbs"), "peak": hbm_peak, "unit": "GB/s",
+                    "frac": s.get("frac"), "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (%s)" % peak_kind,
+                    "avg_launch_ms": stage[dom][0] / max(stage[dom][1], 1)}
+        line = {
+            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk,
+                       "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (T * H_IMG * fe.pitch / 1e6),
+                       "keypoints_per_frame": K_mean, "fast_candidates_frame0": cand0,
+                       "good_matches_per_pair": n_good / max(T - 1, 1)},
+            "hamming_pairs_per_s": pairs_s * world, "hamming_pairs_per_step": pairs_per_step,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": fe.h2d_bytes(T),
+                    "d2h_bytes_per_step": fe.d2h_bytes(T), "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches), "roofline": roof, "stages": stages, "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline(frames[:args.cpu_frames], os.cpu_count() or 1)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=T_SEQ, help="frames per GPU per step")
+    ap.add_argument("--chunk", type=int, default=250, help="frames per extraction launch")
+    ap.add_argument("--cpu-frames", type=int, default=100, help="frames of the sequence timed for cpu_baseline")
+    ap.add_argument("--ref-frames", type=int, default=60, help="frames per step of the reference arm")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

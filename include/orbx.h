@@ -150,6 +150,9 @@ int orbx_knn_match2_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, co
  * strict).  Host or device arrays; order preserved. */
 int orbx_ratio_test(orbx_matcher* m, const orbx_dmatch* knn2, const int* n_per_q, int nq, float ratio,
                     orbx_dmatch* out, int* n);
+/* batched device form of orbx_ratio_test: problem p has nq_dev[p] queries at knn2 + p*max_rows*2 */
+int orbx_ratio_test_batch(orbx_matcher* m, const orbx_dmatch* knn2, const int* n_per_q, const int* nq_dev,
+                          int npairs, int max_rows, float ratio, orbx_dmatch* out, int* n_out_dev);
 /* replaces FeatureMatcher::filter_good_matches (matcher.rs:40-66): thr = max(ratio*min_dist, 30);
  * keep distance < thr (strict), order preserved.  Host or device arrays. */
 int orbx_filter_good_matches(orbx_matcher* m, const orbx_dmatch* in, int n, float ratio, orbx_dmatch* out,

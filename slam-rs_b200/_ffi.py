@@ -69,6 +69,7 @@ def _load():
         "orbx_knn_match2_batch": (i, [vp, vp, sz, vp, vp, sz, vp, i, i, vp, vp]),
         "orbx_match_batch": (i, [vp, vp, sz, vp, vp, sz, vp, i, i, vp, vp]),
         "orbx_ratio_test": (i, [vp, vp, vp, i, f, vp, vp]),
+        "orbx_ratio_test_batch": (i, [vp, vp, vp, vp, i, i, f, vp, vp]),
         "orbx_filter_good_matches": (i, [vp, vp, i, f, vp, vp]),
         "orbx_filter_good_matches_batch": (i, [vp, vp, vp, i, i, f, vp, vp]),
         "orbx_matcher_set_timing": (i, [vp, i]),

@@ -18,9 +18,8 @@ namespace orbx {
 
 constexpr int kScoreW = kFastTileW + 2;  // 64
 constexpr int kScoreH = kFastTileH + 2;  // 32
-constexpr int kSrcW = kScoreW + 6;       // 70
 constexpr int kSrcH = kScoreH + 6;       // 38
-constexpr int kSrcPitch = 80;            // 70 + up to 3 alignment bytes, rounded to words
+constexpr int kSrcPitch = 80;            // tile row pitch in bytes (72 used: 4 + 64 + 4)
 
 // ring offsets in the shared-memory tile (dy*kSrcPitch + dx); folds to immediates after unrolling
 __host__ __device__ constexpr int ring_off(int k) {
@@ -29,73 +28,107 @@ __host__ __device__ constexpr int ring_off(int k) {
   return dy[k] * kSrcPitch + dx[k];
 }
 
-// max over the 16 cyclic 9-arcs of the min over the arc (sliding-window min via 3-input min: DPX VIMNMX3)
-__device__ __forceinline__ int arc9_maxmin(const int (&d)[16]) {
-  int t3[16];
-#pragma unroll
-  for (int k = 0; k < 16; ++k) t3[k] = __vimin3_s32(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-  int best = -65536;
-#pragma unroll
-  for (int k = 0; k < 16; k += 2) {
-    const int a = __vimin3_s32(t3[k], t3[(k + 3) & 15], t3[(k + 6) & 15]);
-    const int b = __vimin3_s32(t3[k + 1], t3[(k + 4) & 15], t3[(k + 7) & 15]);
-    best = __vimax3_s32(best, a, b);
-  }
-  return best;
-}
+// ---- packed 16x2 arithmetic: two pixels per instruction (VIMNMX3.S16x2 / VIADD.16x2 are native) ----
+__device__ __forceinline__ unsigned min3x2(unsigned a, unsigned b, unsigned c) { return __vimin3_s16x2(a, b, c); }
+__device__ __forceinline__ unsigned max3x2(unsigned a, unsigned b, unsigned c) { return __vimax3_s16x2(a, b, c); }
 
-// 16-bit cyclic mask has a run of >= 9 set bits
-__device__ __forceinline__ bool has_run9(unsigned m) {
-  unsigned x = m | (m << 16);
-  x &= x >> 1;  // runs of 2
-  x &= x >> 2;  // runs of 4
-  x &= x >> 4;  // runs of 8
-  x &= (m | (m << 16)) >> 8;  // runs of 9
-  return (x & 0xFFFFu) != 0;
-}
-
-__device__ __forceinline__ int fast_score(const uint8_t* c, int t) {
-  const int v = *c;
-  const int hi = v + t, lo = v - t;
-  // quick reject: every opposite ring pair must contain a brighter (resp. darker) pixel
-  const int p0 = c[ring_off(0)], p8 = c[ring_off(8)];
-  bool br = max(p0, p8) > hi, dk = min(p0, p8) < lo;
-  if (!(br | dk)) return 0;
-  const int p4 = c[ring_off(4)], p12 = c[ring_off(12)];
-  br &= max(p4, p12) > hi;
-  dk &= min(p4, p12) < lo;
-  if (!(br | dk)) return 0;
-  int r[16];
-#pragma unroll
-  for (int k = 0; k < 16; ++k) r[k] = c[ring_off(k)];
-  unsigned mb = 0, md = 0;
+// D[k] = v - ring_k + 256 per 16-bit lane.  Returns m = max(dark, bright) per lane (signed 16x2), where
+//   dark   = max over the 16 cyclic 9-arcs of min over the arc of (v - ring)
+//   bright = max over arcs of min of (ring - v) = -(min over arcs of max over the arc of (v - ring))
+// Sliding-window min/max over 9 = 3-input ops over windows of 3, then over 3 windows of 3.
+__device__ __forceinline__ unsigned fast_m16x2(const unsigned (&D)[16]) {
+  unsigned lo3[16], hi3[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    mb |= (r[k] > hi ? 1u : 0u) << k;
-    md |= (r[k] < lo ? 1u : 0u) << k;
+    lo3[k] = min3x2(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
+    hi3[k] = max3x2(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
   }
-  const bool cb = br && has_run9(mb);
-  const bool cd = dk && has_run9(md);
-  if (!(cb | cd)) return 0;
-  int m = 0;
-  if (cd) {
-    int d[16];
+  unsigned dark = 0u, brightn = 0x7FFF7FFFu;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = v - r[k];
-    m = arc9_maxmin(d);
+  for (int k = 0; k < 16; k += 2) {
+    const unsigned a = min3x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+    const unsigned b = min3x2(lo3[k + 1], lo3[(k + 4) & 15], lo3[(k + 7) & 15]);
+    dark = max3x2(dark, a, b);
+    const unsigned c = max3x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+    const unsigned d = max3x2(hi3[k + 1], hi3[(k + 4) & 15], hi3[(k + 7) & 15]);
+    brightn = min3x2(brightn, c, d);
   }
-  if (cb) {
-    int d[16];
+  // dark - 256 and 256 - brightn per lane
+  const unsigned a = __vsub2(dark, 0x01000100u);
+  const unsigned b = __vsub2(0x01000100u, brightn);
+  return __vmaxs2(a, b);
+}
+
+// four horizontally adjacent bytes starting DX columns from the thread's first pixel, taken from the
+// three aligned words A (cols -4..-1), B (0..3), C (4..7) of one tile row
+template <int DX>
+__device__ __forceinline__ unsigned window4(unsigned A, unsigned B, unsigned C) {
+  if (DX == 0) return B;
+  if (DX < 0) return __funnelshift_r(A, B, 8 * (4 + DX));
+  return __funnelshift_r(B, C, 8 * DX);
+}
+__device__ __forceinline__ unsigned lo_pair(unsigned w) { return __byte_perm(w, 0u, 0x4140); }  // (b0, b1) -> 16x2
+__device__ __forceinline__ unsigned hi_pair(unsigned w) { return __byte_perm(w, 0u, 0x4342); }  // (b2, b3)
+
+// scores of 4 adjacent pixels; `row` points at the word holding the 4 centre pixels (tile row pitch in words)
+__device__ __forceinline__ unsigned fast_score4(const unsigned* row, int t) {
+  constexpr int P = kSrcPitch / 4;
+  unsigned Dl[16], Dh[16];
+  unsigned vl, vh;
+  {
+    const unsigned B = row[0];
+    vl = lo_pair(B) + 0x01000100u;
+    vh = hi_pair(B) + 0x01000100u;
+  }
+#define ORBX_RING(K, DX, DY)                                                         \
+  {                                                                                  \
+    const unsigned* r_ = row + (DY) * P;                                             \
+    const unsigned w_ = window4<DX>(r_[-1], r_[0], r_[1]);                           \
+    Dl[K] = vl - lo_pair(w_);                                                        \
+    Dh[K] = vh - hi_pair(w_);                                                        \
+  }
+  // compass points first: cheap necessary condition, evaluated for the whole warp
+  ORBX_RING(0, 0, 3)
+  ORBX_RING(8, 0, -3)
+  ORBX_RING(4, 3, 0)
+  ORBX_RING(12, -3, 0)
+  {
+    const unsigned thi = 0x01000100u + (unsigned)t * 0x00010001u;  // 256 + t
+    const unsigned tlo = 0x01000100u - (unsigned)t * 0x00010001u;  // 256 - t
+    unsigned possible = 0;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = r[k] - v;
-    m = max(m, arc9_maxmin(d));
+    for (int half = 0; half < 2; ++half) {
+      const unsigned* D = half ? Dh : Dl;
+      const unsigned pd = __vmins2(__vmaxs2(D[0], D[8]), __vmaxs2(D[4], D[12]));  // dark needs pd > 256+t
+      const unsigned pb = __vmaxs2(__vmins2(D[0], D[8]), __vmins2(D[4], D[12]));  // bright needs pb < 256-t
+      possible |= __vcmpgts2(pd, thi) | __vcmpgts2(tlo, pb);
+    }
+    if (!__any_sync(0xFFFFFFFFu, possible != 0)) return 0u;
   }
-  return m - 1;  // m > t >= 1 here
+  ORBX_RING(1, 1, 3)
+  ORBX_RING(2, 2, 2)
+  ORBX_RING(3, 3, 1)
+  ORBX_RING(5, 3, -1)
+  ORBX_RING(6, 2, -2)
+  ORBX_RING(7, 1, -3)
+  ORBX_RING(9, -1, -3)
+  ORBX_RING(10, -2, -2)
+  ORBX_RING(11, -3, -1)
+  ORBX_RING(13, -3, 1)
+  ORBX_RING(14, -2, 2)
+  ORBX_RING(15, -1, 3)
+#undef ORBX_RING
+  const unsigned ml = fast_m16x2(Dl), mh = fast_m16x2(Dh);
+  // score = m - 1 where m > t, else 0
+  const int m0 = (short)(ml & 0xFFFF), m1 = (short)(ml >> 16), m2 = (short)(mh & 0xFFFF), m3 = (short)(mh >> 16);
+  const unsigned s0 = m0 > t ? (unsigned)(m0 - 1) : 0u, s1 = m1 > t ? (unsigned)(m1 - 1) : 0u;
+  const unsigned s2 = m2 > t ? (unsigned)(m2 - 1) : 0u, s3 = m3 > t ? (unsigned)(m3 - 1) : 0u;
+  return s0 | (s1 << 8) | (s2 << 16) | (s3 << 24);
 }
 
 __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
-  __shared__ __align__(16) uint8_t s_src[kSrcH * kSrcPitch];
-  __shared__ uint8_t s_score[kScoreH][kScoreW];
+  __shared__ __align__(16) unsigned s_src[kSrcH * (kSrcPitch / 4)];
+  __shared__ __align__(16) uint8_t s_score[kScoreH][kScoreW];
   __shared__ uint32_t s_list[(kFastTileW / 2 + 1) * (kFastTileH / 2 + 1) + 32];
   __shared__ uint32_t s_hist[256];
   __shared__ uint32_t s_n, s_base;
@@ -112,46 +145,55 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   const int ty = lt / L.fast_tiles_x, tx = lt - ty * L.fast_tiles_x;
   const int x0 = kEdge + tx * kFastTileW;  // first interior pixel of the tile
   const int y0 = kEdge + ty * kFastTileH;
-  const int sx0 = x0 - 4, sy0 = y0 - 4;    // source footprint origin (ring 3 + NMS 1)
-  const int bx = sx0 & ~3;
-  const int shift = sx0 - bx;               // 0..3
+  // tile column c <-> image x = x0 - 5 + c (score column 0 = x0 - 1 sits at tile column 4, word aligned);
+  // tile row r <-> image y = y0 - 4 + r
+  const int gx0 = x0 - 5, gy0 = y0 - 4;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
   const int tid = threadIdx.x;
 
   s_hist[tid] = 0;
   if (tid == 0) s_n = 0;
 
+  constexpr int wpr = kSrcPitch / 4;  // 20 words per tile row, 18 used
   if (L.aligned4) {
-    constexpr int wpr = kSrcPitch / 4;  // 20 words cover shift + 70 bytes
-    for (int i = tid; i < wpr * kSrcH; i += 256) {
-      const int r = i / wpr, c = i - r * wpr;
-      const int gy = min(sy0 + r, L.h - 1);
-      const int gx = min(bx + c * 4, (L.pitch - 4));  // clamp inside the row pitch
-      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)gy * L.pitch + gx));
-      *reinterpret_cast<uint32_t*>(s_src + r * kSrcPitch + c * 4) = v;
+    const int sh = 8 * (gx0 & 3);
+    const int ga = gx0 & ~3;
+    for (int i = tid; i < 18 * kSrcH; i += 256) {
+      const int r = i / 18, c = i - r * 18;
+      const int gy = min(gy0 + r, L.h - 1);
+      const uint8_t* p = img + (size_t)gy * L.pitch;
+      const int a0 = min(ga + c * 4, L.pitch - 4), a1 = min(ga + c * 4 + 4, L.pitch - 4);
+      const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
+      const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
+      s_src[r * wpr + c] = __funnelshift_r(w0, w1, sh);
     }
   } else {
-    for (int i = tid; i < kSrcPitch * kSrcH; i += 256) {
-      const int r = i / kSrcPitch, c = i - r * kSrcPitch;
-      const int gy = min(sy0 + r, L.h - 1);
-      const int gx = min(bx + c, L.w - 1);
-      s_src[r * kSrcPitch + c] = __ldg(img + (size_t)gy * L.pitch + gx);
+    uint8_t* sb = reinterpret_cast<uint8_t*>(s_src);
+    for (int i = tid; i < 72 * kSrcH; i += 256) {
+      const int r = i / 72, c = i - r * 72;
+      const int gy = min(gy0 + r, L.h - 1);
+      const int gx = min(gx0 + c, L.w - 1);
+      sb[r * kSrcPitch + c] = __ldg(img + (size_t)gy * L.pitch + gx);
     }
   }
   __syncthreads();
 
-  // score region: (x0-1 .. x0+62) x (y0-1 .. y0+30); valid where 30 <= x <= w-31, 30 <= y <= h-31
+  // score region: columns x0-1 .. x0+62, rows y0-1 .. y0+30; 4 pixels per thread, 2 rows per thread
   {
-    const int cx = tid & 63;
-    const int gx = x0 - 1 + cx;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int cy = (tid >> 6) + k * 4;
+    const int c4 = tid & 15;          // group of 4 score columns
+    const int gx = x0 - 1 + c4 * 4;   // image x of the first of the 4 pixels
+#pragma unroll 1
+    for (int k = 0; k < 2; ++k) {
+      const int cy = (tid >> 4) + k * 16;
       const int gy = y0 - 1 + cy;
-      int sc = 0;
-      if (gx <= L.w - kEdge && gy <= L.h - kEdge)
-        sc = fast_score(s_src + (cy + 3) * kSrcPitch + shift + cx + 3, g.fast_threshold);
-      s_score[cy][cx] = (uint8_t)sc;
+      unsigned sc = 0;
+      // warp-uniform skip of rows/columns that are entirely outside the scored region is not needed:
+      // out-of-range pixels are masked below (their tile bytes are clamped copies, never out of bounds)
+      sc = fast_score4(s_src + (cy + 3) * wpr + c4 + 1, g.fast_threshold);
+      if (gy > L.h - kEdge) sc = 0;
+      const int over = gx + 3 - (L.w - kEdge);  // pixels with x > w-31 are not scored
+      if (over > 0) sc = over >= 4 ? 0u : (sc & (0xFFFFFFFFu >> (8 * over)));
+      *reinterpret_cast<unsigned*>(&s_score[cy][c4 * 4]) = sc;
     }
   }
   __syncthreads();

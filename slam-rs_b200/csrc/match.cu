@@ -319,6 +319,19 @@ __global__ void knn2_cross_mask_kernel(const orbx_dmatch* knn2, const orbx_dmatc
   if (rev[j].train_idx != i) n_per_q[i] = 0;
 }
 
+// batched form: problem p = blockIdx.y; rows at p*max_rows
+__global__ void knn2_cross_mask_batch_kernel(const orbx_dmatch* knn2, const orbx_dmatch* rev, const int* nq_dev,
+                                             int max_rows, int* n_per_q) {
+  const int prob = blockIdx.y;
+  const int nq = min(nq_dev[prob], max_rows);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  const size_t row = (size_t)prob * max_rows + i;
+  if (n_per_q[row] == 0) return;
+  const int j = knn2[row * 2].train_idx;
+  if (rev[(size_t)prob * max_rows + j].train_idx != i) n_per_q[row] = 0;
+}
+
 // ------------------------------------------------------------------------------------------------
 // host-side launch logic
 // ------------------------------------------------------------------------------------------------
@@ -601,7 +614,45 @@ int orbx_knn_match2_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, co
   a.n_per_q = n_per_q;
   if (n_per_q)
     ORBX_CUDA(cudaMemsetAsync(n_per_q, 0, (size_t)npairs * max_rows * sizeof(int), m->stream));
-  return launch_knn<2>(m, a, npairs);
+  if ((rc = launch_knn<2>(m, a, npairs))) return rc;
+  if (m->cross_check && n_per_q) {
+    // mutual-nearest composition: reverse k=1 pass, then zero n_per_q of non-mutual queries
+    if ((rc = ensure(m, B_REV, (size_t)npairs * max_rows * sizeof(orbx_dmatch)))) return rc;
+    MatchArgs r{};
+    r.q = t;
+    r.t = q;
+    r.q_stride = t_stride;
+    r.t_stride = q_stride;
+    r.nq_dev = nt_dev;
+    r.nt_dev = nq_dev;
+    r.max_rows = max_rows;
+    r.out = (orbx_dmatch*)m->buf[B_REV];
+    if ((rc = launch_knn<1>(m, r, npairs))) return rc;
+    dim3 g(div_up(max_rows, 256), npairs);
+    knn2_cross_mask_batch_kernel<<<g, 256, 0, m->stream>>>(out, (const orbx_dmatch*)m->buf[B_REV], nq_dev, max_rows,
+                                                          n_per_q);
+    ORBX_LAUNCH_CHECK();
+  }
+  return ORBX_OK;
+}
+
+int orbx_ratio_test_batch(orbx_matcher* m, const orbx_dmatch* knn2, const int* n_per_q, const int* nq_dev,
+                          int npairs, int max_rows, float ratio, orbx_dmatch* out, int* n_out_dev) {
+  if (!m || npairs < 0 || max_rows < 0) {
+    set_error("orbx_ratio_test_batch: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (npairs == 0) return ORBX_OK;
+  if (!is_device_ptr(knn2) || !is_device_ptr(n_per_q) || !is_device_ptr(nq_dev) || !is_device_ptr(out) ||
+      !is_device_ptr(n_out_dev)) {
+    set_error("orbx_ratio_test_batch: device pointers required");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  compact_kernel<<<npairs, kCompactThreads, 0, m->stream>>>(0, knn2, n_per_q, nullptr, nq_dev, 0, max_rows, ratio, out,
+                                                           n_out_dev);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
 }
 
 int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const int* nq_dev, const uint8_t* t,

@@ -234,6 +234,10 @@ class FeatureMatcher:
         check(lib.orbx_match_batch(self._h, _ptr(q), q_stride, _ptr(nq), _ptr(t), t_stride, _ptr(nt), npairs,
                                    max_rows, _ptr(out), _ptr(n_out)))
 
+    def ratio_test_batch_device(self, knn2, n_per_q, nq, npairs, max_rows, ratio, out, n_out):
+        check(lib.orbx_ratio_test_batch(self._h, _ptr(knn2), _ptr(n_per_q), _ptr(nq), npairs, max_rows, ratio,
+                                        _ptr(out), _ptr(n_out)))
+
     def filter_good_matches_batch_device(self, matches, n, npairs, max_rows, ratio, out, n_out):
         check(lib.orbx_filter_good_matches_batch(self._h, _ptr(matches), _ptr(n), npairs, max_rows, ratio, _ptr(out),
                                                  _ptr(n_out)))

@@ -1,0 +1,159 @@
+"""Sequence front end: the data-parallel form of the reference's per-frame loop.
+
+/root/reference/examples/visual_odometry.rs:84-218 does, per frame, ``detect_and_compute(gray)``
+(:102), ``match_descriptors(prev_desc, desc)`` (:106) and a match filter (:107), carrying one frame
+of state (:207-209).  Over a whole sequence the extractions are independent and the T-1
+frame-to-frame matching problems are independent once descriptors exist, so this class runs them as
+batched launches of liborbx: frames -> [B] keypoints/descriptors -> [B-1] (t-1 -> t) match problems.
+
+Matching follows the north_star composition: BFMatcher k=2 + Lowe ratio + cross-check (mutual
+nearest), plus the reference's own k=1 + ``filter_good_matches(2.0)`` when ``reference_filter=True``.
+
+torch is used only for device/pinned memory and streams; all computation is liborbx kernels.
+"""
+import numpy as np
+import torch
+
+from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
+
+
+class SequenceFrontEnd:
+    def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
+                 ratio=0.75, cross_check=True, reference_filter=False):
+        self.w, self.h = int(width), int(height)
+        self.device = int(device)
+        self.dev = torch.device("cuda", self.device)
+        self.max_frames = int(max_frames)
+        self.chunk = int(min(chunk, max_frames))
+        self.nfeatures = int(nfeatures)
+        self.cap = int(cap or (nfeatures + nfeatures // 8 + 64 + 31) // 32 * 32)
+        self.ratio = float(ratio)
+        self.reference_filter = bool(reference_filter)
+        self.pitch = (self.w + 127) // 128 * 128
+        torch.cuda.set_device(self.device)
+        self.det = OrbDetector(nfeatures, device=device, max_width=self.w, max_height=self.h, max_batch=self.chunk)
+        self.matcher = FeatureMatcher(device=device, cross_check=cross_check)
+        T, cap = self.max_frames, self.cap
+        u8, i32 = torch.uint8, torch.int32
+        # device-resident results of one pass
+        self.kps = torch.zeros((T, cap, 28), dtype=u8, device=self.dev)
+        self.desc = torch.zeros((T, cap, 32), dtype=u8, device=self.dev)
+        self.n = torch.zeros((T,), dtype=i32, device=self.dev)
+        self.knn = torch.zeros((T, cap, 2, 16), dtype=u8, device=self.dev)
+        self.n_per_q = torch.zeros((T, cap), dtype=i32, device=self.dev)
+        self.good = torch.zeros((T, cap, 16), dtype=u8, device=self.dev)
+        self.n_good = torch.zeros((T,), dtype=i32, device=self.dev)
+        if self.reference_filter:
+            self.m1 = torch.zeros((T, cap, 16), dtype=u8, device=self.dev)
+            self.n_m1 = torch.zeros((T,), dtype=i32, device=self.dev)
+            self.ref_good = torch.zeros((T, cap, 16), dtype=u8, device=self.dev)
+            self.n_ref_good = torch.zeros((T,), dtype=i32, device=self.dev)
+        # staging for the host path
+        self.frames_dev = torch.zeros((T, self.h, self.pitch), dtype=u8, device=self.dev)
+        self.copy_stream = torch.cuda.Stream(device=self.dev)
+        # liborbx runs on one explicit (non-default) stream; callers' streams are joined with events
+        self.stream = torch.cuda.Stream(device=self.dev)
+        self.det.set_stream(self.stream.cuda_stream)
+        self.matcher.set_stream(self.stream.cuda_stream)
+
+    # ------------------------------------------------------------------ stages
+    def extract(self, frames_dev, t0, t1):
+        """frames_dev: uint8 CUDA [T, h, pitch] (pitch >= w).  Extract frames t0..t1-1."""
+        for a in range(t0, t1, self.chunk):
+            b = min(a + self.chunk, t1)
+            self.det.detect_and_compute_device(frames_dev[a:b], self.kps[a:b], self.desc[a:b], self.n[a:b],
+                                               width=self.w)
+
+    def match(self, t0, t1):
+        """Match (t-1 -> t) for t in [max(t0,1), t1): result row t describes pair (t-1, t)."""
+        a = max(t0, 1)
+        if t1 <= a:
+            return
+        npairs = t1 - a
+        cap = self.cap
+        stride = cap * 32
+        m = self.matcher
+        m.knn_match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs, cap,
+                                 self.knn[a], self.n_per_q[a])
+        m.ratio_test_batch_device(self.knn[a], self.n_per_q[a], self.n[a - 1:], npairs, cap, self.ratio, self.good[a],
+                                  self.n_good[a:])
+        if self.reference_filter:
+            m.match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs,
+                                 cap, self.m1[a], self.n_m1[a:])
+            m.filter_good_matches_batch_device(self.m1[a], self.n_m1[a:], npairs, cap, 2.0, self.ref_good[a],
+                                               self.n_ref_good[a:])
+
+    # ------------------------------------------------------------------ whole passes
+    def run_device(self, frames_dev):
+        """One pass over device-resident frames; results stay in HBM.  Asynchronous on the current stream."""
+        T = int(frames_dev.shape[0])
+        cur = torch.cuda.current_stream(self.dev)
+        self.stream.wait_stream(cur)
+        self.extract(frames_dev, 0, T)
+        self.match(0, T)
+        cur.wait_stream(self.stream)
+        return T
+
+    def run_host(self, frames_pinned, out):
+        """End-to-end pass over HOST frames (pinned uint8 [T, h, w]) into the pinned host buffers of
+        ``out`` (see alloc_host_outputs).  H2D copies run chunk-wise on a copy stream and overlap the
+        kernels of the previous chunk; results come back with one D2H copy per array at the end."""
+        T = int(frames_pinned.shape[0])
+        cur = torch.cuda.current_stream(self.dev)
+        self.stream.wait_stream(cur)
+        self.copy_stream.wait_stream(cur)
+        events = []
+        with torch.cuda.stream(self.copy_stream):
+            for a in range(0, T, self.chunk):
+                b = min(a + self.chunk, T)
+                self.frames_dev[a:b, :, :self.w].copy_(frames_pinned[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.copy_stream)
+                events.append(ev)
+        for i, a in enumerate(range(0, T, self.chunk)):
+            b = min(a + self.chunk, T)
+            self.stream.wait_event(events[i])
+            self.extract(self.frames_dev, a, b)
+            self.match(a, b)
+        cur.wait_stream(self.stream)
+        out["n"][:T].copy_(self.n[:T], non_blocking=True)
+        out["kps"][:T].copy_(self.kps[:T], non_blocking=True)
+        out["desc"][:T].copy_(self.desc[:T], non_blocking=True)
+        out["good"][:T].copy_(self.good[:T], non_blocking=True)
+        out["n_good"][:T].copy_(self.n_good[:T], non_blocking=True)
+        return T
+
+    def alloc_host_outputs(self):
+        T, cap = self.max_frames, self.cap
+        pin = dict(pin_memory=True)
+        return {
+            "n": torch.zeros((T,), dtype=torch.int32, **pin),
+            "kps": torch.zeros((T, cap, 28), dtype=torch.uint8, **pin),
+            "desc": torch.zeros((T, cap, 32), dtype=torch.uint8, **pin),
+            "good": torch.zeros((T, cap, 16), dtype=torch.uint8, **pin),
+            "n_good": torch.zeros((T,), dtype=torch.int32, **pin),
+        }
+
+    def h2d_bytes(self, T):
+        return T * self.h * self.w
+
+    def d2h_bytes(self, T):
+        return T * (4 + self.cap * (28 + 32 + 16) + 4)
+
+    # ------------------------------------------------------------------ host views
+    def frame_result(self, t):
+        """(keypoints, descriptors) of frame t as numpy (synchronises)."""
+        n = int(self.n[t].item())
+        n = min(n, self.cap)
+        k = self.kps[t, :n].cpu().numpy().view(KEYPOINT_DTYPE).reshape(-1)
+        return k, self.desc[t, :n].cpu().numpy()
+
+    def pair_result(self, t):
+        """Good matches of pair (t-1, t) as a numpy DMatch array (synchronises)."""
+        n = int(self.n_good[t].item())
+        return self.good[t, :n].cpu().numpy().view(DMATCH_DTYPE).reshape(-1)
+
+    def pair_knn(self, t):
+        nq = min(int(self.n[t - 1].item()), self.cap)
+        k = self.knn[t, :nq].cpu().numpy().view(DMATCH_DTYPE).reshape(nq, 2)
+        return k, self.n_per_q[t, :nq].cpu().numpy()

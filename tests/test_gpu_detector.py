@@ -1,0 +1,180 @@
+"""GPU parity: OrbDetector through the C ABI vs the oracle (restatement, golden vectors, cv2 live)."""
+import ctypes
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import restated as R, synth, cv_ref
+from tests.util import compare_orb
+from tests.test_oracle_cpu import load_orb, GOLD
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def orbx():
+    import slam_rs_b200 as s
+    return s
+
+
+def assert_exact(st):
+    assert st["missing"] == 0 and st["extra"] == 0, st
+    if st["common"]:
+        assert st["resp_eq"] == st["common"], st
+        assert st["angle_eq"] == st["common"], st
+        assert st["pt_eq"] == st["common"] and st["size_eq"] == st["common"], st
+        assert st["desc_bits_diff"] == 0, st
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "orb_*.npz"))))
+def test_golden_vectors(orbx, path):
+    g, ref = load_orb(path)
+    h, w, nf = int(g["h"]), int(g["w"]), int(g["nfeatures"])
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h)
+    kps, desc = det.detect_and_compute(g["image"])
+    assert_exact(compare_orb(kps, desc, ref, h, w))
+    assert np.all(kps["class_id"] == -1)
+    assert np.array_equal(det.level(1), g["level1"])
+    assert np.array_equal(det.level(0, blurred=True), g["blur0"])
+
+
+@pytest.mark.parametrize("h,w,seed,nf,sparse", [
+    (376, 1241, 0, 2000, False),      # BASELINE config 0/1 frame
+    (376, 1241, 1, 500, False),       # reference-faithful nfeatures (detector.rs:16)
+    (1080, 1920, 200, 5000, False),   # BASELINE config 2 frame
+    (480, 640, 31, 1000, True),
+    (333, 517, 32, 700, False),       # odd sizes: unaligned rows everywhere
+])
+def test_vs_restated_all_stages(orbx, h, w, seed, nf, sparse):
+    img = synth.frame(h, w, seed, sparse)
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h)
+    kps, desc = det.detect_and_compute(img)
+    ref = R.orb_detect_and_compute(img, nf, return_stages=True)
+    assert_exact(compare_orb(kps, desc, ref, h, w))
+    stg = ref["stages"]
+    for l in range(8):
+        assert np.array_equal(det.level(l), stg["levels"][l]), "pyramid level %d" % l
+        assert np.array_equal(det.level(l, blurred=True), stg["blurred"][l]), "blurred level %d" % l
+        x, y, sc = det.candidates(l)
+        rx, ry, rs = stg["cand"][l]
+        hh, ww = stg["levels"][l].shape
+        inb = (rx >= 31) & (rx < ww - 31) & (ry >= 31) & (ry < hh - 31)
+        assert set(zip(x.tolist(), y.tolist(), sc.tolist())) == set(
+            zip(rx[inb].tolist(), ry[inb].tolist(), rs[inb].tolist())), "FAST/NMS level %d" % l
+    # library order: level major, response descending, then (y, x)
+    key = np.lexsort((kps["x"], kps["y"], -kps["response"].astype(np.float64), kps["octave"]))
+    assert np.array_equal(key, np.arange(len(kps)))
+    # detect() == keypoints of detect_and_compute()
+    k2 = det.detect(img)
+    assert np.array_equal(k2, kps)
+
+
+@pytest.mark.skipif(not cv_ref.HAVE_CV2, reason="cv2 not importable")
+@pytest.mark.parametrize("h,w,seed,nf", [(376, 1241, 7, 2000), (1080, 1920, 201, 5000), (240, 320, 8, 500)])
+def test_vs_cv2_live(orbx, h, w, seed, nf):
+    img = synth.frame(h, w, seed)
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h)
+    kps, desc = det.detect_and_compute(img)
+    assert_exact(compare_orb(kps, desc, cv_ref.orb_detect_and_compute(img, nf), h, w))
+
+
+@pytest.mark.skipif(not cv_ref.HAVE_CV2, reason="cv2 not importable")
+def test_fast_threshold_param_vs_cv2(orbx):
+    import cv2
+    img = synth.frame(300, 400, 40)
+    det = orbx.OrbDetector(600, max_width=400, max_height=300, fast_threshold=35)
+    kps, desc = det.detect_and_compute(img)
+    k, d = cv2.ORB_create(nfeatures=600, fastThreshold=35).detectAndCompute(img, None)
+    assert_exact(compare_orb(kps, desc, cv_ref._pack(k, d), 300, 400))
+
+
+def test_reference_invariants(orbx):
+    # detector.rs:51-80
+    det = orbx.OrbDetector(500, max_width=640, max_height=480, reference_faithful=True)
+    assert det.max_features() == 500
+    det100 = orbx.OrbDetector(100, max_width=640, max_height=480)
+    blank = np.zeros((480, 640), np.uint8)
+    assert len(det100.detect(blank)) == 0
+    kps, desc = det.detect_and_compute(blank)
+    assert len(kps) == 0 and desc.shape == (0, 32)
+    # reference_faithful keeps ORB::create_def(): nfeatures stays 500 whatever max_features says
+    d2 = orbx.OrbDetector(3000, max_width=640, max_height=480, reference_faithful=True)
+    assert d2.max_features() == 3000 and d2.nfeatures == 500
+    img = synth.frame(480, 640, 41)
+    k, _ = d2.detect_and_compute(img)
+    assert len(k) == len(R.orb_detect_and_compute(img, 500)["x"])
+
+
+def test_small_and_degenerate_images(orbx):
+    det = orbx.OrbDetector(100, max_width=640, max_height=480)
+    img = synth.frame(70, 200, 3)            # only level 0 can yield keypoints
+    kps, desc = det.detect_and_compute(img)
+    assert_exact(compare_orb(kps, desc, R.orb_detect_and_compute(img, 100), 70, 200))
+    assert np.all(kps["octave"] == 0)
+    for shape in [(16, 16), (63, 63), (62, 300)]:
+        z = synth.frame(shape[0], shape[1], 4)
+        k, d = det.detect_and_compute(z)
+        assert_exact(compare_orb(k, d, R.orb_detect_and_compute(z, 100), shape[0], shape[1]))
+    # saturated and checkerboard inputs: ties everywhere
+    sat = np.full((200, 300), 255, np.uint8)
+    assert len(det.detect(sat)) == 0
+    yy, xx = np.mgrid[0:240, 0:320]
+    chk = (((yy // 16) + (xx // 16)) % 2 * 200 + 20).astype(np.uint8)
+    try:
+        k, d = det.detect_and_compute(chk)
+        assert_exact(compare_orb(k, d, R.orb_detect_and_compute(chk, 100), 240, 320))
+    except orbx.OrbxError as e:              # tie flood beyond the selection capacity is a reported error
+        assert e.code == -2
+
+
+def test_batch_device_pointers_and_pitch(orbx):
+    import torch
+    h, w, nf, B = 200, 333, 400, 5
+    imgs = np.stack([synth.frame(h, w, 50 + i) for i in range(B)])
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h, max_batch=B)
+    host = det.detect_and_compute_batch(imgs)
+    single = [orbx.OrbDetector(nf, max_width=w, max_height=h).detect_and_compute(im) for im in imgs]
+    for (k1, d1), (k2, d2) in zip(host, single):
+        assert np.array_equal(k1, k2) and np.array_equal(d1, d2)
+    cap = 640
+    for pitch in (w, 384):                   # unaligned (odd) pitch and 128-aligned pitch
+        buf = torch.zeros((B, h, pitch), dtype=torch.uint8, device="cuda")
+        buf[:, :, :w] = torch.from_numpy(imgs).cuda()
+        kps = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda")
+        desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+        n = torch.zeros((B,), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        det.detect_and_compute_device(buf, kps, desc, n, width=w)
+        det.sync()
+        nn = n.cpu().numpy()
+        for i in range(B):
+            k = kps[i, :nn[i]].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+            assert np.array_equal(k, host[i][0]) and np.array_equal(desc[i, :nn[i]].cpu().numpy(), host[i][1])
+
+
+def test_capacity_error_reports_needed_size(orbx):
+    img = synth.frame(240, 320, 5)
+    det = orbx.OrbDetector(300, max_width=320, max_height=240)
+    kps = np.zeros(50, orbx.KEYPOINT_DTYPE)
+    desc = np.zeros((50, 32), np.uint8)
+    n = ctypes.c_int(0)
+    rc = orbx.lib.orbx_detect_and_compute(det._h, img.ctypes.data, 320, 240, 320, kps.ctypes.data, desc.ctypes.data,
+                                          50, ctypes.byref(n))
+    assert rc == -2 and n.value == 280
+    full, fd = det.detect_and_compute(img)
+    assert np.array_equal(kps, full[:50]) and np.array_equal(desc, fd[:50])
+    # too large for the handle
+    big = np.zeros((300, 400), np.uint8)
+    with pytest.raises(orbx.OrbxError):
+        det.detect(big)
+
+
+def test_determinism(orbx):
+    img = synth.frame(376, 1241, 60)
+    det = orbx.OrbDetector(2000, max_width=1241, max_height=376)
+    a = det.detect_and_compute(img)
+    for _ in range(3):
+        b = det.detect_and_compute(img)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])

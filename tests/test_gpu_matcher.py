@@ -1,0 +1,193 @@
+"""GPU parity: FeatureMatcher through the C ABI vs the oracle (bit-exact indices and distances)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import restated as R, synth, cv_ref, c_oracle
+from tests.test_oracle_cpu import GOLD
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def orbx():
+    import slam_rs_b200 as s
+    return s
+
+
+def check_knn(out, cnt, idx, dist, c, q0=0):
+    assert np.array_equal(cnt, c)
+    for j in range(out.shape[1]):
+        ok = cnt > j
+        assert np.array_equal(out["train_idx"][ok, j], idx[ok, j])
+        assert np.array_equal(out["distance"][ok, j], dist[ok, j].astype(np.float32))
+        assert np.array_equal(out["query_idx"][ok, j], np.nonzero(ok)[0] + q0)
+        assert np.all(out["img_idx"][ok, j] == 0)
+
+
+def test_golden_match_vectors(orbx):
+    g = np.load(os.path.join(GOLD, "match_700x900.npz"))
+    q, t = g["q"], g["t"]
+    m = orbx.FeatureMatcher()
+    out = m.match_descriptors(q, t)
+    assert np.array_equal(out["query_idx"], g["match"][:, 0].astype(np.int32))
+    assert np.array_equal(out["train_idx"], g["match"][:, 1].astype(np.int32))
+    assert np.array_equal(out["distance"], g["match"][:, 3].astype(np.float32))
+    knn, cnt = m.knn_match(q, t)
+    assert np.all(cnt == 2)
+    assert np.array_equal(knn["train_idx"], g["knn2"][:, :, 1].astype(np.int32))
+    assert np.array_equal(knn["distance"], g["knn2"][:, :, 3].astype(np.float32))
+    mx = orbx.FeatureMatcher(cross_check=True).match_descriptors(q, t)
+    assert np.array_equal(mx["query_idx"], g["cross"][:, 0].astype(np.int32))
+    assert np.array_equal(mx["train_idx"], g["cross"][:, 1].astype(np.int32))
+    assert np.array_equal(mx["distance"], g["cross"][:, 3].astype(np.float32))
+
+
+def test_empty_and_tiny(orbx):
+    # matcher.rs:79-86: empty x empty -> Ok, 0 matches; matcher.rs:29-31: either side empty -> empty
+    m = orbx.FeatureMatcher()
+    e = np.zeros((0, 32), np.uint8)
+    q = synth.random_descriptors(5, 1)
+    assert len(m.match_descriptors(e, e)) == 0
+    assert len(m.match_descriptors(q, e)) == 0
+    assert len(m.match_descriptors(e, q)) == 0
+    knn, cnt = m.knn_match(q, e)
+    assert np.all(cnt == 0)
+    # one train row: k=2 yields a single neighbour per query
+    t1 = synth.random_descriptors(1, 2)
+    knn, cnt = m.knn_match(q, t1)
+    assert np.all(cnt == 1) and np.all(knn["train_idx"][:, 0] == 0)
+    assert np.array_equal(knn["distance"][:, 0], R.hamming_matrix(q, t1)[:, 0].astype(np.float32))
+    # identical rows everywhere: every tie resolves to the lowest train index
+    t = np.repeat(synth.random_descriptors(1, 3), 300, axis=0)
+    knn, cnt = m.knn_match(q, t)
+    assert np.all(knn["train_idx"][:, 0] == 0) and np.all(knn["train_idx"][:, 1] == 1)
+    with pytest.raises(ValueError):
+        m.match_descriptors(np.zeros((3, 16), np.uint8), t)
+
+
+@pytest.mark.parametrize("nq,nt,seed", [(1, 1, 1), (127, 255, 2), (129, 257, 3), (2000, 2000, 4), (5000, 5000, 5),
+                                        (333, 70001, 6)])
+def test_knn_vs_oracle_sizes(orbx, nq, nt, seed):
+    q, t = synth.random_descriptors(nq, seed), synth.random_descriptors(nt, seed + 100)
+    if nt > 20:
+        t[nt // 2] = t[nt - 1] = t[3]
+        q[0] = t[3]
+    m = orbx.FeatureMatcher()
+    idx, dist, c = c_oracle.knn(q, t, 2)
+    knn, cnt = m.knn_match(q, t)
+    check_knn(knn, cnt, idx, dist, c)
+    out = m.match_descriptors(q, t)
+    assert np.array_equal(out["train_idx"], idx[:, 0]) and np.array_equal(out["distance"], dist[:, 0].astype(np.float32))
+
+
+def test_orb_descriptors_match_and_filters(orbx):
+    seq = synth.sequence(376, 1241, 2)
+    det = orbx.OrbDetector(2000, max_width=1241, max_height=376)
+    (k0, d0), (k1, d1) = det.detect_and_compute(seq[0]), det.detect_and_compute(seq[1])
+    m = orbx.FeatureMatcher()
+    # reference loop: match (k=1) + filter_good_matches(2.0)  (visual_odometry.rs:106-107)
+    raw = m.match_descriptors(d0, d1)
+    ref = R.match_k1(d0, d1)
+    assert np.array_equal(raw["train_idx"], ref[:, 1]) and np.array_equal(raw["distance"], ref[:, 2].astype(np.float32))
+    good = m.filter_good_matches(raw, 2.0)
+    rgood = R.filter_good_matches(ref, 2.0)
+    assert np.array_equal(good["query_idx"], rgood[:, 0]) and np.array_equal(good["train_idx"], rgood[:, 1])
+    assert len(good) > 300
+    # the true motion is a 3 px shift: filtered matches must agree with it
+    dx = k0["x"][good["query_idx"]] - k1["x"][good["train_idx"]]
+    assert np.mean(np.abs(dx - 3.0) < 2.5) > 0.9
+    # north_star composition: k=2 + Lowe ratio + cross-check
+    knn, cnt = m.knn_match(d0, d1)
+    idx, dist, c = R.knn(d0, d1, 2)
+    check_knn(knn, cnt, idx, dist, c)
+    kept = m.ratio_test(knn, cnt, 0.75)
+    rk = R.ratio_test(idx, dist, c, 0.75)
+    assert np.array_equal(kept["query_idx"], np.nonzero(rk)[0]) and np.array_equal(kept["train_idx"], idx[rk, 0])
+    mx = orbx.FeatureMatcher(cross_check=True)
+    knn_x, cnt_x = mx.knn_match(d0, d1)
+    mutual = np.zeros(len(d0), bool)
+    mutual[R.cross_check(d0, d1)[:, 0]] = True
+    assert np.array_equal(cnt_x, np.where(mutual, c, 0))
+    kept_x = mx.ratio_test(knn_x, cnt_x, 0.75)
+    assert np.array_equal(kept_x["query_idx"], np.nonzero(rk & mutual)[0])
+    if cv_ref.HAVE_CV2:
+        assert np.array_equal(cv_ref.match_k1(d0, d1), ref)
+        x = cv_ref.match_k1(d0, d1, cross_check=True)
+        assert np.array_equal(mx.match_descriptors(d0, d1)["query_idx"], x[:, 0])
+
+
+def test_map_to_frame_both_orientations(orbx):
+    """Config C4 shape, scaled to what the C oracle checks in seconds, in both orientations
+    (reference: query = map, train = frame — map.rs:107; north_star: query = frame, train = map)."""
+    mp, fr = synth.map_and_frame_descriptors(120000, 1000, f=0)
+    m = orbx.FeatureMatcher()
+    out = m.match_descriptors(mp, fr)
+    idx, dist, _ = c_oracle.knn(mp, fr, 1)
+    assert np.array_equal(out["train_idx"], idx[:, 0]) and np.array_equal(out["distance"], dist[:, 0].astype(np.float32))
+    knn, cnt = m.knn_match(fr, mp)              # > 65536 train rows: split + merge path
+    idx, dist, c = c_oracle.knn(fr, mp, 2)
+    check_knn(knn, cnt, idx, dist, c)
+
+
+def test_full_size_map_properties(orbx):
+    """1M map x 5000 frame descriptors (BASELINE config 3 per-frame problem): size-independent properties +
+    an oracle check on a slice of the queries."""
+    mp, fr = synth.map_and_frame_descriptors(1_000_000, 5000, f=1)
+    m = orbx.FeatureMatcher()
+    knn, cnt = m.knn_match(fr, mp)
+    assert np.all(cnt == 2)
+    assert np.all(knn["distance"][:, 0] <= knn["distance"][:, 1])
+    tie = knn["distance"][:, 0] == knn["distance"][:, 1]
+    assert np.all(knn["train_idx"][tie, 0] < knn["train_idx"][tie, 1])
+    # noisy copies (first half) must find their source row: distance ~ Binomial(256, 0.1)
+    d = np.unpackbits(fr[:2500] ^ mp[knn["train_idx"][:2500, 0]], axis=1).sum(1)
+    assert np.array_equal(d.astype(np.float32), knn["distance"][:2500, 0])
+    assert d.max() < 60 and knn["distance"][2500:, 0].min() > 60
+    sl = slice(2400, 2600)
+    idx, dist, c = c_oracle.knn(fr[sl], mp, 2)
+    check_knn(knn[sl], cnt[sl], idx, dist, c, q0=sl.start)
+    # linearity / symmetry: matching the best rows back gives distance 0 to themselves
+    back = m.match_descriptors(mp[knn["train_idx"][:64, 0]], mp)
+    assert np.all(back["distance"] == 0)
+
+
+def test_sequence_front_end_matches_per_frame_api(orbx):
+    import torch
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 7, 200, 320, 400
+    seq = synth.sequence(h, w, T, canvas_seed=77)
+    fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=3, reference_filter=True)
+    dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
+    dev[:, :, :w] = torch.from_numpy(seq).cuda()
+    torch.cuda.synchronize()
+    fe.run_device(dev)
+    torch.cuda.synchronize()
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h)
+    per = [det.detect_and_compute(f) for f in seq]
+    for t in range(T):
+        k, d = fe.frame_result(t)
+        assert np.array_equal(k, per[t][0]) and np.array_equal(d, per[t][1])
+    for t in range(1, T):
+        d0, d1 = per[t - 1][1], per[t][1]
+        idx, dist, c = R.knn(d0, d1, 2)
+        mutual = np.zeros(len(d0), bool)
+        mutual[R.cross_check(d0, d1)[:, 0]] = True
+        keep = R.ratio_test(idx, dist, c, 0.75) & mutual
+        good = fe.pair_result(t)
+        assert np.array_equal(good["query_idx"], np.nonzero(keep)[0])
+        assert np.array_equal(good["train_idx"], idx[keep, 0])
+        assert np.array_equal(good["distance"], dist[keep, 0].astype(np.float32))
+        n = int(fe.n_ref_good[t].item())
+        rg = fe.ref_good[t, :n].cpu().numpy().view(orbx.DMATCH_DTYPE).reshape(-1)
+        ref = R.filter_good_matches(R.match_k1(d0, d1), 2.0)
+        assert np.array_equal(rg["query_idx"], ref[:, 0]) and np.array_equal(rg["train_idx"], ref[:, 1])
+    # the host (end-to-end) path returns the same bytes
+    out = fe.alloc_host_outputs()
+    fe.run_host(torch.from_numpy(seq).pin_memory(), out)
+    torch.cuda.synchronize()
+    for t in range(T):
+        n = int(out["n"][t])
+        assert np.array_equal(out["desc"][t, :n].numpy(), per[t][1])
+    assert np.array_equal(out["n_good"][1:T].numpy(), fe.n_good[1:T].cpu().numpy())
