@@ -1,0 +1,32 @@
+//! 1:1 mirror of include/orbx.h.
+#![allow(non_camel_case_types)]
+use std::os::raw::{c_char, c_int, c_void};
+
+#[repr(C)] #[derive(Clone, Copy, Debug, Default)]
+pub struct orbx_keypoint { pub x: f32, pub y: f32, pub size: f32, pub angle: f32, pub response: f32, pub octave: i32, pub class_id: i32 }
+#[repr(C)] #[derive(Clone, Copy, Debug, Default)]
+pub struct orbx_dmatch { pub query_idx: i32, pub train_idx: i32, pub img_idx: i32, pub distance: f32 }
+#[repr(C)] #[derive(Clone, Copy, Debug)]
+pub struct orbx_params { pub nfeatures: i32, pub scale_factor: f32, pub nlevels: i32, pub edge_threshold: i32,
+    pub first_level: i32, pub wta_k: i32, pub score_type: i32, pub patch_size: i32, pub fast_threshold: i32 }
+pub enum orbx_detector {}
+pub enum orbx_matcher {}
+pub const ORBX_OK: c_int = 0;
+pub const ORBX_E_CAPACITY: c_int = -2;
+
+extern "C" {
+    pub fn orbx_default_params(p: *mut orbx_params);
+    pub fn orbx_detector_create(p: *const orbx_params, device: c_int, max_w: c_int, max_h: c_int, max_batch: c_int, out: *mut *mut orbx_detector) -> c_int;
+    pub fn orbx_detector_destroy(d: *mut orbx_detector);
+    pub fn orbx_detect(d: *mut orbx_detector, img: *const u8, w: c_int, h: c_int, pitch: usize, kps: *mut orbx_keypoint, cap: c_int, n: *mut c_int) -> c_int;
+    pub fn orbx_detect_and_compute(d: *mut orbx_detector, img: *const u8, w: c_int, h: c_int, pitch: usize, kps: *mut orbx_keypoint, desc: *mut u8, cap: c_int, n: *mut c_int) -> c_int;
+    pub fn orbx_detect_and_compute_batch(d: *mut orbx_detector, imgs: *const u8, w: c_int, h: c_int, pitch: usize, frame_stride: usize, batch: c_int, kps: *mut orbx_keypoint, desc: *mut u8, cap: c_int, n: *mut c_int) -> c_int;
+    pub fn orbx_matcher_create(device: c_int, cross_check: c_int, out: *mut *mut orbx_matcher) -> c_int;
+    pub fn orbx_matcher_destroy(m: *mut orbx_matcher);
+    pub fn orbx_match(m: *mut orbx_matcher, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n: *mut c_int) -> c_int;
+    pub fn orbx_knn_match2(m: *mut orbx_matcher, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n_per_q: *mut c_int) -> c_int;
+    pub fn orbx_ratio_test(m: *mut orbx_matcher, knn2: *const orbx_dmatch, n_per_q: *const c_int, nq: c_int, ratio: f32, out: *mut orbx_dmatch, n: *mut c_int) -> c_int;
+    pub fn orbx_filter_good_matches(m: *mut orbx_matcher, inp: *const orbx_dmatch, n: c_int, ratio: f32, out: *mut orbx_dmatch, n_out: *mut c_int) -> c_int;
+    pub fn orbx_last_error() -> *const c_char;
+    pub fn orbx_detector_set_stream(d: *mut orbx_detector, stream: *mut c_void) -> c_int;
+}

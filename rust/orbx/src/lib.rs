@@ -1,0 +1,87 @@
+//! Safe mirror of slamkit-rs `src/feature/{detector,matcher}.rs` over liborbx.
+//! Same method names and error behaviour: working calls take `&mut self`, empty inputs are not errors,
+//! results are freshly allocated.  NOT compiled in this repository's build image (no Rust toolchain).
+use orbx_sys as sys;
+use std::{error::Error, ffi::CStr, ptr};
+
+pub type KeyPoint = sys::orbx_keypoint; // layout == cv::KeyPoint
+pub type DMatch = sys::orbx_dmatch;     // layout == cv::DMatch
+
+fn err(code: i32) -> Box<dyn Error> {
+    let msg = unsafe { CStr::from_ptr(sys::orbx_last_error()) }.to_string_lossy().into_owned();
+    format!("liborbx error {code}: {msg}").into()
+}
+
+/// A borrowed 8-bit single-channel image (what `&Mat` CV_8UC1 is on the reference side).
+pub struct Gray<'a> { pub data: &'a [u8], pub width: i32, pub height: i32, pub pitch: usize }
+
+pub struct OrbDetector { h: *mut sys::orbx_detector, max_features: i32 }
+
+impl OrbDetector {
+    /// detector.rs:15-18 — unlike the reference, `max_features` is honoured.
+    pub fn new(max_features: i32) -> Result<Self, Box<dyn Error>> {
+        let mut p = unsafe { let mut p = std::mem::zeroed(); sys::orbx_default_params(&mut p); p };
+        p.nfeatures = max_features;
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_detector_create(&p, 0, 4095, 4095, 1, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h, max_features })
+    }
+    fn run(&mut self, img: &Gray, with_desc: bool) -> Result<(Vec<KeyPoint>, Vec<u8>), Box<dyn Error>> {
+        let mut cap = (self.max_features + self.max_features / 4 + 256) as usize;
+        loop {
+            let mut kps = vec![KeyPoint::default(); cap];
+            let mut desc = vec![0u8; if with_desc { cap * 32 } else { 0 }];
+            let mut n = 0i32;
+            let rc = unsafe {
+                if with_desc { sys::orbx_detect_and_compute(self.h, img.data.as_ptr(), img.width, img.height, img.pitch, kps.as_mut_ptr(), desc.as_mut_ptr(), cap as i32, &mut n) }
+                else { sys::orbx_detect(self.h, img.data.as_ptr(), img.width, img.height, img.pitch, kps.as_mut_ptr(), cap as i32, &mut n) }
+            };
+            if rc == sys::ORBX_E_CAPACITY && n as usize > cap { cap = n as usize; continue; }
+            if rc != 0 { return Err(err(rc)); }
+            kps.truncate(n as usize); desc.truncate(n as usize * 32);
+            return Ok((kps, desc));
+        }
+    }
+    /// detector.rs:20-24
+    pub fn detect(&mut self, image: &Gray) -> Result<Vec<KeyPoint>, Box<dyn Error>> { Ok(self.run(image, false)?.0) }
+    /// detector.rs:26-40 — descriptors are K x 32 bytes, row-major (== Mat K x 32 CV_8U)
+    pub fn detect_and_compute(&mut self, image: &Gray) -> Result<(Vec<KeyPoint>, Vec<u8>), Box<dyn Error>> { self.run(image, true) }
+    /// detector.rs:42-44
+    pub fn max_features(&self) -> i32 { self.max_features }
+}
+impl Drop for OrbDetector { fn drop(&mut self) { unsafe { sys::orbx_detector_destroy(self.h) } } }
+
+pub struct FeatureMatcher { h: *mut sys::orbx_matcher }
+
+impl FeatureMatcher {
+    /// matcher.rs:15-21
+    pub fn new() -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_matcher_create(0, 0, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h })
+    }
+    /// matcher.rs:24-37 — desc1/desc2: N x 32 bytes; either side empty -> empty result
+    pub fn match_descriptors(&mut self, desc1: &[u8], desc2: &[u8]) -> Result<Vec<DMatch>, Box<dyn Error>> {
+        let (nq, nt) = (desc1.len() / 32, desc2.len() / 32);
+        if nq == 0 || nt == 0 { return Ok(Vec::new()); }
+        let mut out = vec![DMatch::default(); nq];
+        let mut n = 0i32;
+        let rc = unsafe { sys::orbx_match(self.h, desc1.as_ptr(), nq as i32, desc2.as_ptr(), nt as i32, out.as_mut_ptr(), &mut n) };
+        if rc != 0 { return Err(err(rc)); }
+        out.truncate(n as usize);
+        Ok(out)
+    }
+    /// matcher.rs:40-66
+    pub fn filter_good_matches(&self, matches: &[DMatch], ratio: f32) -> Vec<DMatch> {
+        if matches.is_empty() { return Vec::new(); }
+        let mut out = vec![DMatch::default(); matches.len()];
+        let mut n = 0i32;
+        let rc = unsafe { sys::orbx_filter_good_matches(self.h, matches.as_ptr(), matches.len() as i32, ratio, out.as_mut_ptr(), &mut n) };
+        if rc != 0 { return Vec::new(); }
+        out.truncate(n as usize);
+        out
+    }
+}
+impl Drop for FeatureMatcher { fn drop(&mut self) { unsafe { sys::orbx_matcher_destroy(self.h) } } }
