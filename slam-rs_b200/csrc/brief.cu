@@ -24,14 +24,26 @@ __device__ __forceinline__ int reflect101(int i, int n) {
   return min(max(i, 0), n - 1);
 }
 
-constexpr int kBlurSrcW = kBlurTileW + 6;  // 70
-constexpr int kBlurSrcH = kBlurTileH + 6;  // 38
-constexpr int kBlurSrcPitch = 72;
+// Blur tile = 128 x 32 output pixels owned by ONE warp (4 independent warps per block, no block barrier):
+// the warp stages the 136 x 38 byte source footprint (reflect-101 applied while staging, aligned 32-bit
+// loads wherever the word lies inside the row) in its private shared-memory slab, then every lane walks
+// down its 4-pixel column: per source row 3 LDS.32 -> 10 bytes -> fp32 (PRMT into the mantissa of 2^23,
+// one FADD), the 7-tap row pass for 4 pixels (28 FMA-pipe ops), and - from a 7-row register window - the
+// symmetric column pass, round-half-even by the 1.5*2^23 magic add, and one coalesced 32-bit store.
+// FMA-pipe bound at ~19 fp32 ops per pixel; HBM traffic is read P + write P.
+constexpr int kBlurWarps = 4;
+constexpr int kBlurSrcRows = kBlurTileH + 6;       // 38
+constexpr int kBlurSrcWords = kBlurTileW / 4 + 2;  // 34 words: image columns x0-4 .. x0+131
 
-__global__ void __launch_bounds__(256) blur7_kernel(DevGeom g) {
-  __shared__ uint8_t s_src[kBlurSrcH][kBlurSrcPitch];
-  __shared__ float s_row[kBlurSrcH][kBlurTileW + 1];
-  const int tile = blockIdx.x;
+__device__ __forceinline__ float byte_to_float(unsigned w, int i) {
+  return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650 + i)), 8388608.0f);
+}
+
+__global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
+  __shared__ unsigned s_src[kBlurWarps][kBlurSrcRows * kBlurSrcWords];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tile = blockIdx.x * kBlurWarps + warp;
+  if (tile >= g.blur_tiles_total) return;
   int l = 0;
 #pragma unroll
   for (int i = 1; i < kMaxLevels; ++i)
@@ -41,44 +53,86 @@ __global__ void __launch_bounds__(256) blur7_kernel(DevGeom g) {
   const int lt = tile - L.blur_tile_begin;
   const int ty = lt / L.blur_tiles_x, tx = lt - ty * L.blur_tiles_x;
   const int x0 = tx * kBlurTileW, y0 = ty * kBlurTileH;
+  const int w = L.w, h = L.h, pitch = L.pitch;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
-  const int tid = threadIdx.x;
+  unsigned* src = s_src[warp];
 
-  for (int i = tid; i < kBlurSrcW * kBlurSrcH; i += 256) {
-    const int r = i / kBlurSrcW, c = i - r * kBlurSrcW;
-    const int gy = reflect101(y0 - 3 + r, L.h);
-    const int gx = reflect101(x0 - 3 + c, L.w);
-    s_src[r][c] = __ldg(img + (size_t)gy * L.pitch + gx);
+  const int nrows = min(kBlurSrcRows, h - y0 + 6);  // source rows needed for the output rows inside the image
+  for (int i = lane; i < nrows * kBlurSrcWords; i += 32) {
+    const int r = i / kBlurSrcWords, c = i - r * kBlurSrcWords;
+    const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+    const int x = x0 - 4 + 4 * c;
+    unsigned v;
+    if (L.aligned4 && x >= 0 && x + 3 < w) {
+      v = __ldg(reinterpret_cast<const unsigned*>(row + x));
+    } else {
+      v = (unsigned)__ldg(row + reflect101(x, w)) | ((unsigned)__ldg(row + reflect101(x + 1, w)) << 8) |
+          ((unsigned)__ldg(row + reflect101(x + 2, w)) << 16) | ((unsigned)__ldg(row + reflect101(x + 3, w)) << 24);
+    }
+    src[i] = v;
   }
-  __syncthreads();
-  // row pass: acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc), j = 1..6
-  for (int i = tid; i < kBlurTileW * kBlurSrcH; i += 256) {
-    const int r = i / kBlurTileW, c = i - r * kBlurTileW;
-    float acc = __fmul_rn(c_gauss[0], (float)s_src[r][c]);
+  __syncwarp();
+
+  const int gx = x0 + 4 * lane;
+  const bool store = gx < w;  // pad columns inside the 128-byte aligned pitch may receive don't-care bytes
+  uint8_t* out = L.blur + (size_t)frame * L.blur_stride + gx;
+  const float k0 = c_gauss[0], k1 = c_gauss[1], k2 = c_gauss[2], k3 = c_gauss[3];
+  float R[7][4];
+#pragma unroll 1
+  for (int rb = 0; rb < nrows; rb += 7) {
 #pragma unroll
-    for (int j = 1; j < 7; ++j) acc = __fmaf_rn(c_gauss[j], (float)s_src[r][c + j], acc);
-    s_row[r][c] = acc;
-  }
-  __syncthreads();
-  // column pass: acc = k3*r[y]; acc = fma(k_{3+j}, r[y+j] + r[y-j], acc), j = 1..3
-  uint8_t* out = L.blur + (size_t)frame * L.blur_stride;
-  for (int i = tid; i < kBlurTileW * kBlurTileH; i += 256) {
-    const int r = i / kBlurTileW, c = i - r * kBlurTileW;
-    const int gx = x0 + c, gy = y0 + r;
-    if (gx >= L.w || gy >= L.h) continue;
-    float acc = __fmul_rn(c_gauss[3], s_row[r + 3][c]);
+    for (int u = 0; u < 7; ++u) {
+      const int r = rb + u;
+      if (r < nrows) {
+        const unsigned* p = src + r * kBlurSrcWords + lane;
+        const unsigned w0 = p[0], w1 = p[1], w2 = p[2];
+        float f[10];
+        f[0] = byte_to_float(w0, 1);
+        f[1] = byte_to_float(w0, 2);
+        f[2] = byte_to_float(w0, 3);
 #pragma unroll
-    for (int j = 1; j <= 3; ++j)
-      acc = __fmaf_rn(c_gauss[3 + j], __fadd_rn(s_row[r + 3 + j][c], s_row[r + 3 - j][c]), acc);
-    const int v = __float2int_rn(acc);
-    out[(size_t)gy * L.blur_pitch + gx] = (uint8_t)min(max(v, 0), 255);
+        for (int i = 0; i < 4; ++i) f[3 + i] = byte_to_float(w1, i);
+        f[7] = byte_to_float(w2, 0);
+        f[8] = byte_to_float(w2, 1);
+        f[9] = byte_to_float(w2, 2);
+        // row pass (OpenCV order): acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc), j = 1..6
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float acc = __fmul_rn(k0, f[i]);
+          acc = __fmaf_rn(k1, f[i + 1], acc);
+          acc = __fmaf_rn(k2, f[i + 2], acc);
+          acc = __fmaf_rn(k3, f[i + 3], acc);
+          acc = __fmaf_rn(k2, f[i + 4], acc);
+          acc = __fmaf_rn(k1, f[i + 5], acc);
+          acc = __fmaf_rn(k0, f[i + 6], acc);
+          R[u][i] = acc;
+        }
+        // column pass for output row r-6 (window rows u-6..u, centre u-3, indices mod 7)
+        if (r >= 6) {
+          unsigned b[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float acc = __fmul_rn(k3, R[(u + 4) % 7][i]);
+            acc = __fmaf_rn(k2, __fadd_rn(R[(u + 5) % 7][i], R[(u + 3) % 7][i]), acc);
+            acc = __fmaf_rn(k1, __fadd_rn(R[(u + 6) % 7][i], R[(u + 2) % 7][i]), acc);
+            acc = __fmaf_rn(k0, __fadd_rn(R[u][i], R[(u + 1) % 7][i]), acc);
+            // round half to even: acc in [0, 255.01) so the low byte of acc + 1.5*2^23 is rint(acc)
+            b[i] = __float_as_uint(__fadd_rn(acc, 12582912.0f));
+          }
+          if (store) {
+            const unsigned lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+            *reinterpret_cast<unsigned*>(out + (size_t)(y0 + r - 6) * L.blur_pitch) = __byte_perm(lo, hi, 0x5410);
+          }
+        }
+      }
+    }
   }
 }
 
 int launch_blur(const DevGeom& g, cudaStream_t s) {
   if (g.blur_tiles_total == 0 || g.batch == 0) return ORBX_OK;
-  dim3 grid(g.blur_tiles_total, g.batch);
-  blur7_kernel<<<grid, 256, 0, s>>>(g);
+  dim3 grid(div_up(g.blur_tiles_total, kBlurWarps), g.batch);
+  blur7_kernel<<<grid, kBlurWarps * 32, 0, s>>>(g);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

@@ -7,10 +7,15 @@
 //
 // Kernel shape: one thread owns one query descriptor (8 x u32 in registers); the train set is streamed
 // through shared memory in 256-row tiles (cp.async double buffer) and every lane reads the same train
-// row (LDS.128 broadcast, conflict free).  Per (query, train) pair: 8 LOP3(xor) + 8 POPC + adds +
-// a packed-key min/max update of the running best-2: key = dist << 16 | local_train_idx, so the
-// lexicographic (distance, index) order is one unsigned compare and the lowest index wins ties.
-// This is POPC-pipe bound integer work; tensor cores are deliberately not used.
+// row (LDS.128 broadcast, conflict free).  Per (query, train) pair: 8 LOP3(xor), then a carry-save
+// adder tree (6 LOP3: three 3:2 compressors) folds the 8 words into 2 "ones" + 3 "twos" words so only
+// 5 POPC are issued instead of 8 (POPC is the quarter-rate pipe: 16 lanes/clk/SM measured, LOP3 runs at
+// 64), and a packed-key min/max update of the running best-2: key = dist << 16 | local_train_idx, so
+// the lexicographic (distance, index) order is one unsigned compare and the lowest index wins ties.
+// With cross-check the reverse (train -> query) best-1 comes out of the SAME distance evaluation: a
+// warp-wide CREDUX.MIN of (dist << 16 | query lane) per train row (32 lanes/clk/SM, its own pipe),
+// per-warp column minima in shared memory, one RED.MIN.U64 per (block, train row) to global memory.
+// Integer work only; tensor cores are deliberately not used.
 #include <cooperative_groups.h>
 #include <cuda_pipeline.h>
 
@@ -88,7 +93,31 @@ struct MatchArgs {
   orbx_dmatch* out;          // used when nsplits == 1: [problem][max_rows][K]
   int* n_per_q;              // optional [problem][max_rows] (K=2) ; for K=1: unused
   int* n_out;                // optional per problem count (K=1 batch): nq or 0
+  unsigned long long* rev;   // FUSED only: [problem][max_rows_t] reverse best-1 (dist << 32 | query_idx), preset ~0
+  int rev_rows;              // row pitch of rev (max train rows per problem)
 };
+
+__device__ __forceinline__ unsigned lop3_xor3(unsigned a, unsigned b, unsigned c) {
+  unsigned r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned lop3_maj3(unsigned a, unsigned b, unsigned c) {
+  unsigned r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+
+// popcount of the 256-bit XOR with 5 POPC: three carry-save 3:2 compressors (sum = a^b^c, carry = maj)
+// leave ones = {s3, x7} and twos = {c1, c2, c3};  dist = pop(s3) + pop(x7) + 2 (pop(c1)+pop(c2)+pop(c3)).
+__device__ __forceinline__ unsigned hamming256(const uint4& qa, const uint4& qb, const uint4& x, const uint4& y) {
+  const unsigned x0 = qa.x ^ x.x, x1 = qa.y ^ x.y, x2 = qa.z ^ x.z, x3 = qa.w ^ x.w;
+  const unsigned x4 = qb.x ^ y.x, x5 = qb.y ^ y.y, x6 = qb.z ^ y.z, x7 = qb.w ^ y.w;
+  const unsigned s1 = lop3_xor3(x0, x1, x2), c1 = lop3_maj3(x0, x1, x2);
+  const unsigned s2 = lop3_xor3(x3, x4, x5), c2 = lop3_maj3(x3, x4, x5);
+  const unsigned s3 = lop3_xor3(s1, s2, x6), c3 = lop3_maj3(s1, s2, x6);
+  return (__popc(s3) + __popc(x7)) + 2 * (__popc(c1) + __popc(c2) + __popc(c3));
+}
 
 template <int K>
 __device__ __forceinline__ void best_update(unsigned& b1, unsigned& b2, unsigned key) {
@@ -101,9 +130,10 @@ __device__ __forceinline__ void best_update(unsigned& b1, unsigned& b2, unsigned
   }
 }
 
-template <int K>
+template <int K, bool FUSED>
 __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
   __shared__ uint4 tile[2][kTile * 2];
+  __shared__ unsigned s_col[FUSED ? kQPB / 32 : 1][FUSED ? kTile : 1];
   const int prob = blockIdx.z;
   const int split = blockIdx.y;
   int nq = a.nq_dev ? min(a.nq_dev[prob], a.max_rows) : a.nq_fixed;
@@ -125,6 +155,10 @@ __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
     qb = __ldg(qp + (size_t)qi * 2 + 1);
   }
   unsigned b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;
+  // reverse key of this thread inside its block: dist << 16 | lane-in-block; idle lanes never win
+  const unsigned qoff = active ? threadIdx.x : 0x7F000000u;
+  const int warp = threadIdx.x >> 5;
+  const bool lane0 = (threadIdx.x & 31) == 0;
 
   const int ntiles = t_end > t_begin ? (t_end - t_begin + kTile - 1) / kTile : 0;
   auto issue = [&](int tl, int bufi) {
@@ -148,23 +182,38 @@ __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
     const int rows = min(kTile, t_end - (t_begin + base_local));
     const uint4* tt = tile[cur];
     int j = 0;
-#pragma unroll 4
+#pragma unroll 1
     for (; j + 4 <= rows; j += 4) {
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        uint4 x = tt[(j + u) * 2], y = tt[(j + u) * 2 + 1];
-        unsigned d = __popc(qa.x ^ x.x) + __popc(qa.y ^ x.y) + __popc(qa.z ^ x.z) + __popc(qa.w ^ x.w) +
-                     __popc(qb.x ^ y.x) + __popc(qb.y ^ y.y) + __popc(qb.z ^ y.z) + __popc(qb.w ^ y.w);
-        best_update<K>(b1, b2, (d << 16) | (unsigned)(base_local + j + u));
+        const uint4 x = tt[(j + u) * 2], y = tt[(j + u) * 2 + 1];
+        const unsigned d = hamming256(qa, qb, x, y);
+        best_update<K>(b1, b2, (d << 16) + (unsigned)(base_local + j + u));
+        if (FUSED) {
+          const unsigned r = __reduce_min_sync(0xFFFFFFFFu, (d << 16) + qoff);
+          if (lane0) s_col[warp][j + u] = r;
+        }
       }
     }
     for (; j < rows; ++j) {
-      uint4 x = tt[j * 2], y = tt[j * 2 + 1];
-      unsigned d = __popc(qa.x ^ x.x) + __popc(qa.y ^ x.y) + __popc(qa.z ^ x.z) + __popc(qa.w ^ x.w) +
-                   __popc(qb.x ^ y.x) + __popc(qb.y ^ y.y) + __popc(qb.z ^ y.z) + __popc(qb.w ^ y.w);
-      best_update<K>(b1, b2, (d << 16) | (unsigned)(base_local + j));
+      const uint4 x = tt[j * 2], y = tt[j * 2 + 1];
+      const unsigned d = hamming256(qa, qb, x, y);
+      best_update<K>(b1, b2, (d << 16) + (unsigned)(base_local + j));
+      if (FUSED) {
+        const unsigned r = __reduce_min_sync(0xFFFFFFFFu, (d << 16) + qoff);
+        if (lane0) s_col[warp][j] = r;
+      }
     }
     __syncthreads();
+    if (FUSED) {
+      // column minima of this block -> global reverse best-1 (lowest query index wins ties)
+      unsigned long long* rv = a.rev + (size_t)prob * a.rev_rows + (t_begin + base_local);
+      for (int c = threadIdx.x; c < rows; c += kQPB) {
+        const unsigned m = min(min(s_col[0][c], s_col[1][c]), min(s_col[2][c], s_col[3][c]));
+        atomicMin(rv + c, ((unsigned long long)(m >> 16) << 32) | (unsigned long long)(q0 + (int)(m & 0xFFFFu)));
+      }
+      // s_col is rewritten only after the __syncthreads at the top of the next tile
+    }
   }
   if (!active) return;
 
@@ -259,7 +308,7 @@ __device__ __forceinline__ int block_excl_scan_flag(bool flag, int* warp_sums, i
 // mode 0: Lowe ratio on knn2 (in: [rows][2], cnt: [rows]);  mode 1: min-distance filter on k=1 list
 // mode 2: cross-check of forward k=1 (in) against reverse k=1 (rev)
 __global__ void __launch_bounds__(kCompactThreads)
-compact_kernel(int mode, const orbx_dmatch* in, const int* cnt, const orbx_dmatch* rev, const int* n_dev,
+compact_kernel(int mode, const orbx_dmatch* in, const int* cnt, const unsigned long long* rev, const int* n_dev,
                int n_fixed, int max_rows, float ratio, orbx_dmatch* out, int* n_out) {
   __shared__ int warp_sums[33];
   __shared__ float s_min[32];
@@ -299,7 +348,7 @@ compact_kernel(int mode, const orbx_dmatch* in, const int* cnt, const orbx_dmatc
       } else if (mode == 1) {
         keep = m.distance < s_thr;
       } else {
-        keep = rev[m.train_idx].train_idx == i;
+        keep = (int)(unsigned)(rev[m.train_idx] & 0xFFFFFFFFull) == i;
       }
     }
     int total;
@@ -311,16 +360,16 @@ compact_kernel(int mode, const orbx_dmatch* in, const int* cnt, const orbx_dmatc
 }
 
 // zero n_per_q for queries failing the mutual-nearest test (k=2 + cross-check composition)
-__global__ void knn2_cross_mask_kernel(const orbx_dmatch* knn2, const orbx_dmatch* rev, int nq, int* n_per_q) {
+__global__ void knn2_cross_mask_kernel(const orbx_dmatch* knn2, const unsigned long long* rev, int nq, int* n_per_q) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
   if (n_per_q[i] == 0) return;
   const int j = knn2[(size_t)i * 2].train_idx;
-  if (rev[j].train_idx != i) n_per_q[i] = 0;
+  if ((int)(unsigned)(rev[j] & 0xFFFFFFFFull) != i) n_per_q[i] = 0;
 }
 
 // batched form: problem p = blockIdx.y; rows at p*max_rows
-__global__ void knn2_cross_mask_batch_kernel(const orbx_dmatch* knn2, const orbx_dmatch* rev, const int* nq_dev,
+__global__ void knn2_cross_mask_batch_kernel(const orbx_dmatch* knn2, const unsigned long long* rev, const int* nq_dev,
                                              int max_rows, int* n_per_q) {
   const int prob = blockIdx.y;
   const int nq = min(nq_dev[prob], max_rows);
@@ -329,14 +378,15 @@ __global__ void knn2_cross_mask_batch_kernel(const orbx_dmatch* knn2, const orbx
   const size_t row = (size_t)prob * max_rows + i;
   if (n_per_q[row] == 0) return;
   const int j = knn2[row * 2].train_idx;
-  if (rev[(size_t)prob * max_rows + j].train_idx != i) n_per_q[row] = 0;
+  if ((int)(unsigned)(rev[(size_t)prob * max_rows + j] & 0xFFFFFFFFull) != i) n_per_q[row] = 0;
 }
 
 // ------------------------------------------------------------------------------------------------
 // host-side launch logic
 // ------------------------------------------------------------------------------------------------
+// fused = also produce the reverse (train -> query) best-1 into a.rev (preset to ~0 by the caller)
 template <int K>
-static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs) {
+static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs, bool fused = false) {
   const int rows_q = a.nq_dev ? a.max_rows : a.nq_fixed;
   const int rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
   if (rows_q <= 0 || npairs <= 0) return ORBX_OK;
@@ -357,7 +407,10 @@ static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs) {
   }
   dim3 grid(qtiles, splits, npairs);
   m->timer.begin(0, m->stream);
-  hamming_knn_kernel<K><<<grid, kQPB, 0, m->stream>>>(a);
+  if (fused)
+    hamming_knn_kernel<K, true><<<grid, kQPB, 0, m->stream>>>(a);
+  else
+    hamming_knn_kernel<K, false><<<grid, kQPB, 0, m->stream>>>(a);
   m->timer.end(m->stream);
   ORBX_LAUNCH_CHECK();
   if (splits > 1) {
@@ -525,36 +578,33 @@ static int match_one(orbx_matcher* m, int K, const uint8_t* q, int nq, const uin
   a.max_rows = nq;
   a.out = fwd;
   a.n_per_q = counts;
+  if (cross) {
+    // reverse best-1 (train -> query) comes out of the same distance evaluation (fused kernel)
+    if ((rc = ensure(m, B_REV, (size_t)nt * sizeof(unsigned long long)))) return rc;
+    ORBX_CUDA(cudaMemsetAsync(m->buf[B_REV], 0xFF, (size_t)nt * sizeof(unsigned long long), m->stream));
+    a.rev = (unsigned long long*)m->buf[B_REV];
+    a.rev_rows = nt;
+  }
   if (K == 1)
-    rc = launch_knn<1>(m, a, 1);
+    rc = launch_knn<1>(m, a, 1, cross);
   else
-    rc = launch_knn<2>(m, a, 1);
+    rc = launch_knn<2>(m, a, 1, cross);
   if (rc) return rc;
 
   int n_final = nq;
   if (cross) {
-    // reverse k=1: train -> query
-    if ((rc = ensure(m, B_REV, (size_t)nt * sizeof(orbx_dmatch)))) return rc;
-    MatchArgs r{};
-    r.q = (const uint8_t*)dt;
-    r.t = (const uint8_t*)dq;
-    r.nq_fixed = nt;
-    r.nt_fixed = nq;
-    r.max_rows = nt;
-    r.out = (orbx_dmatch*)m->buf[B_REV];
-    if ((rc = launch_knn<1>(m, r, 1))) return rc;
     if (K == 1) {
       if ((rc = ensure(m, B_OUT2, (size_t)nq * sizeof(orbx_dmatch)))) return rc;
       if ((rc = ensure(m, B_CNT2, sizeof(int)))) return rc;
       orbx_dmatch* dst = out_dev ? out : (orbx_dmatch*)m->buf[B_OUT2];
-      compact_kernel<<<1, kCompactThreads, 0, m->stream>>>(2, fwd, nullptr, (orbx_dmatch*)m->buf[B_REV], nullptr,
+      compact_kernel<<<1, kCompactThreads, 0, m->stream>>>(2, fwd, nullptr, (const unsigned long long*)m->buf[B_REV], nullptr,
                                                           nq, nq, 0.f, dst, (int*)m->buf[B_CNT2]);
       ORBX_LAUNCH_CHECK();
       ORBX_CUDA(cudaMemcpyAsync(&n_final, m->buf[B_CNT2], sizeof(int), cudaMemcpyDeviceToHost, m->stream));
       ORBX_CUDA(cudaStreamSynchronize(m->stream));
       fwd = dst;
     } else {
-      knn2_cross_mask_kernel<<<div_up(nq, 256), 256, 0, m->stream>>>(fwd, (orbx_dmatch*)m->buf[B_REV], nq, counts);
+      knn2_cross_mask_kernel<<<div_up(nq, 256), 256, 0, m->stream>>>(fwd, (const unsigned long long*)m->buf[B_REV], nq, counts);
       ORBX_LAUNCH_CHECK();
     }
   }
@@ -614,22 +664,19 @@ int orbx_knn_match2_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, co
   a.n_per_q = n_per_q;
   if (n_per_q)
     ORBX_CUDA(cudaMemsetAsync(n_per_q, 0, (size_t)npairs * max_rows * sizeof(int), m->stream));
-  if ((rc = launch_knn<2>(m, a, npairs))) return rc;
-  if (m->cross_check && n_per_q) {
-    // mutual-nearest composition: reverse k=1 pass, then zero n_per_q of non-mutual queries
-    if ((rc = ensure(m, B_REV, (size_t)npairs * max_rows * sizeof(orbx_dmatch)))) return rc;
-    MatchArgs r{};
-    r.q = t;
-    r.t = q;
-    r.q_stride = t_stride;
-    r.t_stride = q_stride;
-    r.nq_dev = nt_dev;
-    r.nt_dev = nq_dev;
-    r.max_rows = max_rows;
-    r.out = (orbx_dmatch*)m->buf[B_REV];
-    if ((rc = launch_knn<1>(m, r, npairs))) return rc;
+  const bool cross = m->cross_check && n_per_q;
+  if (cross) {
+    // mutual-nearest composition: the reverse best-1 is produced by the same launch
+    const size_t rev_bytes = (size_t)npairs * max_rows * sizeof(unsigned long long);
+    if ((rc = ensure(m, B_REV, rev_bytes))) return rc;
+    ORBX_CUDA(cudaMemsetAsync(m->buf[B_REV], 0xFF, rev_bytes, m->stream));
+    a.rev = (unsigned long long*)m->buf[B_REV];
+    a.rev_rows = max_rows;
+  }
+  if ((rc = launch_knn<2>(m, a, npairs, cross))) return rc;
+  if (cross) {
     dim3 g(div_up(max_rows, 256), npairs);
-    knn2_cross_mask_batch_kernel<<<g, 256, 0, m->stream>>>(out, (const orbx_dmatch*)m->buf[B_REV], nq_dev, max_rows,
+    knn2_cross_mask_batch_kernel<<<g, 256, 0, m->stream>>>(out, (const unsigned long long*)m->buf[B_REV], nq_dev, max_rows,
                                                           n_per_q);
     ORBX_LAUNCH_CHECK();
   }
