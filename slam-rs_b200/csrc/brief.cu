@@ -53,29 +53,54 @@ __global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
   const int lt = tile - L.blur_tile_begin;
   const int ty = lt / L.blur_tiles_x, tx = lt - ty * L.blur_tiles_x;
   const int x0 = tx * kBlurTileW, y0 = ty * kBlurTileH;
-  const int w = L.w, h = L.h, pitch = L.pitch;
+  const int w = L.w, h = L.h, pitch = L.pitch, blur_pitch = L.blur_pitch;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
-  unsigned* src = s_src[warp];
+  uint8_t* out = L.blur + (size_t)frame * L.blur_stride + (size_t)y0 * blur_pitch + x0 + 4 * lane;
 
+  // staging: lane owns word column `lane` (image x0-4+4*lane ..+3); lanes 0,1 also own columns 32,33.
+  // The column geometry (aligned fast path or four reflected byte offsets) is row-invariant.
   const int nrows = min(kBlurSrcRows, h - y0 + 6);  // source rows needed for the output rows inside the image
-  for (int i = lane; i < nrows * kBlurSrcWords; i += 32) {
-    const int r = i / kBlurSrcWords, c = i - r * kBlurSrcWords;
-    const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
-    const int x = x0 - 4 + 4 * c;
-    unsigned v;
-    if (L.aligned4 && x >= 0 && x + 3 < w) {
-      v = __ldg(reinterpret_cast<const unsigned*>(row + x));
-    } else {
-      v = (unsigned)__ldg(row + reflect101(x, w)) | ((unsigned)__ldg(row + reflect101(x + 1, w)) << 8) |
-          ((unsigned)__ldg(row + reflect101(x + 2, w)) << 16) | ((unsigned)__ldg(row + reflect101(x + 3, w)) << 24);
+  {
+    const int xa = x0 - 4 + 4 * lane, xb = xa + 128;
+    const bool fa = L.aligned4 && xa >= 0 && xa + 3 < w;
+    const bool fb = L.aligned4 && xb + 3 < w;
+    const bool has_b = lane < 2;
+    int ca[4], cb[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      ca[k] = reflect101(xa + k, w);
+      cb[k] = reflect101(xb + k, w);
     }
-    src[i] = v;
+    // aligned words go global -> shared with cp.async (all rows in flight at once, no register staging);
+    // border words are assembled from reflected byte loads
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(&s_src[warp][lane]);
+#pragma unroll 2
+    for (int r = 0; r < nrows; ++r) {
+      const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+      const unsigned dst = sa + r * (kBlurSrcWords * 4);
+      if (fa) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(row + xa));
+      } else {
+        const unsigned va = (unsigned)__ldg(row + ca[0]) | ((unsigned)__ldg(row + ca[1]) << 8) |
+                            ((unsigned)__ldg(row + ca[2]) << 16) | ((unsigned)__ldg(row + ca[3]) << 24);
+        asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst), "r"(va));
+      }
+      if (has_b) {
+        if (fb) {
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 128), "l"(row + xb));
+        } else {
+          const unsigned vb = (unsigned)__ldg(row + cb[0]) | ((unsigned)__ldg(row + cb[1]) << 8) |
+                              ((unsigned)__ldg(row + cb[2]) << 16) | ((unsigned)__ldg(row + cb[3]) << 24);
+          asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst + 128), "r"(vb));
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
   }
   __syncwarp();
 
-  const int gx = x0 + 4 * lane;
-  const bool store = gx < w;  // pad columns inside the 128-byte aligned pitch may receive don't-care bytes
-  uint8_t* out = L.blur + (size_t)frame * L.blur_stride + gx;
+  const bool store = x0 + 4 * lane < w;  // pad columns inside the 128-byte aligned pitch may receive don't-care bytes
   const float k0 = c_gauss[0], k1 = c_gauss[1], k2 = c_gauss[2], k3 = c_gauss[3];
   float R[7][4];
 #pragma unroll 1
@@ -84,7 +109,7 @@ __global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
     for (int u = 0; u < 7; ++u) {
       const int r = rb + u;
       if (r < nrows) {
-        const unsigned* p = src + r * kBlurSrcWords + lane;
+        const unsigned* p = &s_src[warp][r * kBlurSrcWords + lane];
         const unsigned w0 = p[0], w1 = p[1], w2 = p[2];
         float f[10];
         f[0] = byte_to_float(w0, 1);
@@ -121,7 +146,7 @@ __global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
           }
           if (store) {
             const unsigned lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
-            *reinterpret_cast<unsigned*>(out + (size_t)(y0 + r - 6) * L.blur_pitch) = __byte_perm(lo, hi, 0x5410);
+            *reinterpret_cast<unsigned*>(out + (r - 6) * blur_pitch) = __byte_perm(lo, hi, 0x5410);
           }
         }
       }
@@ -137,38 +162,77 @@ int launch_blur(const DevGeom& g, cudaStream_t s) {
   return ORBX_OK;
 }
 
-// one warp per keypoint; lane i evaluates pairs 32j+i, the ballot of (a < b) is descriptor word j
+// one warp per keypoint; lane i evaluates pairs 32j+i, the ballot of (a < b) is descriptor word j.
+// The 39 x 39 neighbourhood (|offset| <= 19 after rotation) is first copied into a per-warp shared-memory
+// slab with row-contiguous aligned 32-bit loads (~3 rows per load instruction), so the 512 scattered
+// samples hit shared memory instead of issuing 16 fully divergent global loads per lane.
 constexpr int kBriefWarps = 8;
 constexpr int kBriefPerWarp = 4;
 
+// cvRound for |x| < 2^22 without the XU-pipe F2I: the fp32 add rounds half to even at integer granularity
+__device__ __forceinline__ int rint_small(float x) {
+  return (int)__float_as_uint(__fadd_rn(x, 12582912.0f)) - 0x4B400000;
+}
+constexpr int kBriefRows = 39;
+constexpr int kBriefWords = 11;                              // 44 bytes per row
+constexpr int kBriefLoads = (kBriefRows * kBriefWords + 31) / 32;  // 14
+
 __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutArgs o) {
-  __shared__ char4 s_pat[256];
-  s_pat[threadIdx.x] = c_pattern[threadIdx.x];
+  // pattern as fp32 (I2F and F2I are quarter-rate XU-pipe conversions: keep them out of the inner loop)
+  __shared__ float4 s_pat[256];
+  __shared__ unsigned s_patch[kBriefWarps][kBriefRows * kBriefWords + 3];
+  {
+    const char4 c = c_pattern[threadIdx.x];
+    s_pat[threadIdx.x] = make_float4((float)c.x, (float)c.y, (float)c.z, (float)c.w);
+  }
   __syncthreads();
   const int frame = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n = min(o.n[frame], min(o.cap, o.lvl_cap));
+  int st_off[kBriefLoads];  // row * 65536 + word of staged word i = lane + 32t
+#pragma unroll
+  for (int t = 0; t < kBriefLoads; ++t) {
+    const int i = lane + 32 * t;
+    const int r = i / kBriefWords;
+    st_off[t] = (r << 16) | (i - r * kBriefWords);
+  }
+  const uint8_t* sp = reinterpret_cast<const uint8_t*>(s_patch[warp]);
   for (int it = 0; it < kBriefPerWarp; ++it) {
     const int j = (blockIdx.x * kBriefPerWarp + it) * kBriefWarps + warp;
     if (j >= n) return;
     const uint32_t lv = o.kp_lvl[(size_t)frame * o.lvl_cap + j];
     const int l = (int)(lv >> 24), cx = (int)(lv & 0xFFF), cy = (int)((lv >> 12) & 0xFFF);
     const DevLevel& L = g.lv[l];
+    const int bp = L.blur_pitch;
+    // blurred planes are internal: base, pitch and frame stride are multiples of 128
+    const uint8_t* p0 = L.blur + (size_t)frame * L.blur_stride + (size_t)(cy - 19) * bp + (cx - 19);
+    const int off = (int)((uintptr_t)p0 & 3);
+    const uint8_t* base = p0 - off;
+    unsigned stg[kBriefLoads];
+#pragma unroll
+    for (int t = 0; t < kBriefLoads; ++t)
+      if (lane + 32 * t < kBriefRows * kBriefWords)
+        stg[t] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)(st_off[t] >> 16) * bp) + (st_off[t] & 0xFFFF));
     const float angle = o.kps[(size_t)frame * o.cap + j].angle;
     const float th = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));
     const float a = (float)cos((double)th), b = (float)sin((double)th);
-    const uint8_t* img = L.blur + (size_t)frame * L.blur_stride + (size_t)cy * L.blur_pitch + cx;
+    __syncwarp();  // the previous keypoint's samples have been read
+#pragma unroll
+    for (int t = 0; t < kBriefLoads; ++t)
+      if (lane + 32 * t < kBriefRows * kBriefWords) s_patch[warp][lane + 32 * t] = stg[t];
+    __syncwarp();
+    const uint8_t* centre = sp + 19 * (kBriefWords * 4) + 19 + off;
     uint32_t word = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const char4 p = s_pat[k * 32 + lane];
-      const float ax = (float)p.x, ay = (float)p.y, bx = (float)p.z, by = (float)p.w;
-      const int iax = __float2int_rn(__fsub_rn(__fmul_rn(ax, a), __fmul_rn(ay, b)));
-      const int iay = __float2int_rn(__fadd_rn(__fmul_rn(ax, b), __fmul_rn(ay, a)));
-      const int ibx = __float2int_rn(__fsub_rn(__fmul_rn(bx, a), __fmul_rn(by, b)));
-      const int iby = __float2int_rn(__fadd_rn(__fmul_rn(bx, b), __fmul_rn(by, a)));
-      const int va = __ldg(img + iay * L.blur_pitch + iax);
-      const int vb = __ldg(img + iby * L.blur_pitch + ibx);
+      const float4 p = s_pat[k * 32 + lane];
+      const float ax = p.x, ay = p.y, bx = p.z, by = p.w;
+      const int iax = rint_small(__fsub_rn(__fmul_rn(ax, a), __fmul_rn(ay, b)));
+      const int iay = rint_small(__fadd_rn(__fmul_rn(ax, b), __fmul_rn(ay, a)));
+      const int ibx = rint_small(__fsub_rn(__fmul_rn(bx, a), __fmul_rn(by, b)));
+      const int iby = rint_small(__fadd_rn(__fmul_rn(bx, b), __fmul_rn(by, a)));
+      const int va = centre[iay * (kBriefWords * 4) + iax];
+      const int vb = centre[iby * (kBriefWords * 4) + ibx];
       const uint32_t bal = __ballot_sync(0xFFFFFFFFu, va < vb);
       if (lane == k) word = bal;
     }

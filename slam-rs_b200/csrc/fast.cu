@@ -28,80 +28,74 @@ __host__ __device__ constexpr int ring_off(int k) {
   return dy[k] * kSrcPitch + dx[k];
 }
 
-// ---- packed 16x2 arithmetic: two pixels per instruction (VIMNMX3.S16x2 / VIADD.16x2 are native) ----
+// ---- packed 16x2 arithmetic: two pixels per instruction (VIMNMX3.S16x2 is native, ALU pipe) ----
 __device__ __forceinline__ unsigned min3x2(unsigned a, unsigned b, unsigned c) { return __vimin3_s16x2(a, b, c); }
 __device__ __forceinline__ unsigned max3x2(unsigned a, unsigned b, unsigned c) { return __vimax3_s16x2(a, b, c); }
 
-// D[k] = v - ring_k + 256 per 16-bit lane.  Returns m = max(dark, bright) per lane (signed 16x2), where
-//   dark   = max over the 16 cyclic 9-arcs of min over the arc of (v - ring)
-//   bright = max over arcs of min of (ring - v) = -(min over arcs of max over the arc of (v - ring))
-// Sliding-window min/max over 9 = 3-input ops over windows of 3, then over 3 windows of 3.
-__device__ __forceinline__ unsigned fast_m16x2(const unsigned (&D)[16]) {
+// R[k] = raw ring pixel k of two adjacent centres (one per 16-bit lane, 0..255).  Returns per lane
+//   lo = max over the 16 cyclic 9-arcs of (min over the arc)   -> bright contrast = lo - v
+//   hi = min over the 16 cyclic 9-arcs of (max over the arc)   -> dark   contrast = v - hi
+// Sliding-window min/max over 9 = 3-input ops over windows of 3, then over 3 windows of 3 (80 ops / 2 px).
+__device__ __forceinline__ void fast_arcs16x2(const unsigned (&R)[16], unsigned& lo, unsigned& hi) {
   unsigned lo3[16], hi3[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    lo3[k] = min3x2(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
-    hi3[k] = max3x2(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
+    lo3[k] = min3x2(R[k], R[(k + 1) & 15], R[(k + 2) & 15]);
+    hi3[k] = max3x2(R[k], R[(k + 1) & 15], R[(k + 2) & 15]);
   }
-  unsigned dark = 0u, brightn = 0x7FFF7FFFu;
+  unsigned l = 0u, h = 0x7FFF7FFFu;
 #pragma unroll
   for (int k = 0; k < 16; k += 2) {
     const unsigned a = min3x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
     const unsigned b = min3x2(lo3[k + 1], lo3[(k + 4) & 15], lo3[(k + 7) & 15]);
-    dark = max3x2(dark, a, b);
+    l = max3x2(l, a, b);
     const unsigned c = max3x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
     const unsigned d = max3x2(hi3[k + 1], hi3[(k + 4) & 15], hi3[(k + 7) & 15]);
-    brightn = min3x2(brightn, c, d);
+    h = min3x2(h, c, d);
   }
-  // dark - 256 and 256 - brightn per lane
-  const unsigned a = __vsub2(dark, 0x01000100u);
-  const unsigned b = __vsub2(0x01000100u, brightn);
-  return __vmaxs2(a, b);
+  lo = l;
+  hi = h;
 }
 
-// four horizontally adjacent bytes starting DX columns from the thread's first pixel, taken from the
-// three aligned words A (cols -4..-1), B (0..3), C (4..7) of one tile row
-template <int DX>
-__device__ __forceinline__ unsigned window4(unsigned A, unsigned B, unsigned C) {
-  if (DX == 0) return B;
-  if (DX < 0) return __funnelshift_r(A, B, 8 * (4 + DX));
-  return __funnelshift_r(B, C, 8 * DX);
-}
-__device__ __forceinline__ unsigned lo_pair(unsigned w) { return __byte_perm(w, 0u, 0x4140); }  // (b0, b1) -> 16x2
-__device__ __forceinline__ unsigned hi_pair(unsigned w) { return __byte_perm(w, 0u, 0x4342); }  // (b2, b3)
+// Shared-memory tiles hold the source footprint widened to 16 bits, twice: copy E pairs pixels
+// (2j, 2j+1), copy O pairs (2j+1, 2j+2), so every ring read of two adjacent centres is one aligned
+// 32-bit word already in 16x2 form (no PRMT / funnel shift in the hot loop).
+constexpr int kPairPitch = 36;  // words (= pixel pairs) per tile row; 72 pixels
 
-// scores of 4 adjacent pixels; `row` points at the word holding the 4 centre pixels (tile row pitch in words)
-__device__ __forceinline__ unsigned fast_score4(const unsigned* row, int t) {
-  constexpr int P = kSrcPitch / 4;
-  unsigned Dl[16], Dh[16];
-  unsigned vl, vh;
-  {
-    const unsigned B = row[0];
-    vl = lo_pair(B) + 0x01000100u;
-    vh = hi_pair(B) + 0x01000100u;
+// scores (shifted: 0 = not a corner, s' = m - t >= 1 for corners, i.e. score = s' + t - 1) of 4 adjacent
+// pixels whose first pixel is tile column tc (multiple of 4) of tile row tr
+__device__ __forceinline__ unsigned fast_score4(const unsigned* sE, const unsigned* sO, int tr, int tc, int t) {
+  const int pe = tc >> 1;  // pair index of (tc, tc+1) in E; O pair (tc+1, tc+2) has the same index
+  unsigned Rl[16], Rh[16];
+  // ring offset (DX, DY): pixels tc+DX, tc+DX+1 (lo reg) and tc+DX+2, tc+DX+3 (hi reg)
+#define ORBX_RING(K, DX, DY)                                                                  \
+  {                                                                                           \
+    const unsigned* r_ = (((DX) & 1) ? sO : sE) + (tr + (DY)) * kPairPitch + pe;               \
+    constexpr int o_ = ((DX) & 1) ? ((DX) - 1) / 2 : (DX) / 2;                                 \
+    Rl[K] = r_[o_];                                                                           \
+    Rh[K] = r_[o_ + 1];                                                                       \
   }
-#define ORBX_RING(K, DX, DY)                                                         \
-  {                                                                                  \
-    const unsigned* r_ = row + (DY) * P;                                             \
-    const unsigned w_ = window4<DX>(r_[-1], r_[0], r_[1]);                           \
-    Dl[K] = vl - lo_pair(w_);                                                        \
-    Dh[K] = vh - hi_pair(w_);                                                        \
-  }
-  // compass points first: cheap necessary condition, evaluated for the whole warp
   ORBX_RING(0, 0, 3)
   ORBX_RING(8, 0, -3)
   ORBX_RING(4, 3, 0)
   ORBX_RING(12, -3, 0)
+  const unsigned* c_ = sE + tr * kPairPitch + pe;
+  const unsigned vl = c_[0], vh = c_[1];
+  // contrasts are kept biased by +256 per lane so that plain 32-bit adds never borrow across lanes
+  constexpr unsigned kBias = 0x01000100u;
+  const unsigned tk = kBias + (unsigned)t * 0x00010001u;  // 256 + t
   {
-    const unsigned thi = 0x01000100u + (unsigned)t * 0x00010001u;  // 256 + t
-    const unsigned tlo = 0x01000100u - (unsigned)t * 0x00010001u;  // 256 - t
+    // compass points first: any 9-arc holds one pixel of {0,8} and one of {4,12} — a necessary
+    // condition evaluated for the whole warp (big win on smooth images, ~10 % overhead on dense texture)
     unsigned possible = 0;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
-      const unsigned* D = half ? Dh : Dl;
-      const unsigned pd = __vmins2(__vmaxs2(D[0], D[8]), __vmaxs2(D[4], D[12]));  // dark needs pd > 256+t
-      const unsigned pb = __vmaxs2(__vmins2(D[0], D[8]), __vmins2(D[4], D[12]));  // bright needs pb < 256-t
-      possible |= __vcmpgts2(pd, thi) | __vcmpgts2(tlo, pb);
+      const unsigned* R = half ? Rh : Rl;
+      const unsigned v = half ? vh : vl;
+      const unsigned pb = __vmins2(__vmaxs2(R[0], R[8]), __vmaxs2(R[4], R[12]));  // bright needs pb > v + t
+      const unsigned pd = __vmaxs2(__vmins2(R[0], R[8]), __vmins2(R[4], R[12]));  // dark needs pd < v - t
+      const unsigned mb = pb + kBias - v, md = v + kBias - pd;  // 256 + contrast, lanes in 1..511
+      possible |= __vmaxs2(__vmaxs2(mb, md), tk) - tk;          // > 0 in some lane?
     }
     if (!__any_sync(0xFFFFFFFFu, possible != 0)) return 0u;
   }
@@ -118,16 +112,18 @@ __device__ __forceinline__ unsigned fast_score4(const unsigned* row, int t) {
   ORBX_RING(14, -2, 2)
   ORBX_RING(15, -1, 3)
 #undef ORBX_RING
-  const unsigned ml = fast_m16x2(Dl), mh = fast_m16x2(Dh);
-  // score = m - 1 where m > t, else 0
-  const int m0 = (short)(ml & 0xFFFF), m1 = (short)(ml >> 16), m2 = (short)(mh & 0xFFFF), m3 = (short)(mh >> 16);
-  const unsigned s0 = m0 > t ? (unsigned)(m0 - 1) : 0u, s1 = m1 > t ? (unsigned)(m1 - 1) : 0u;
-  const unsigned s2 = m2 > t ? (unsigned)(m2 - 1) : 0u, s3 = m3 > t ? (unsigned)(m3 - 1) : 0u;
-  return s0 | (s1 << 8) | (s2 << 16) | (s3 << 24);
+  unsigned lo, hi, sl, sh;
+  fast_arcs16x2(Rl, lo, hi);
+  sl = __vmaxs2(__vmaxs2(lo + kBias - vl, vl + kBias - hi), tk) - tk;  // max(m - t, 0) per lane
+  fast_arcs16x2(Rh, lo, hi);
+  sh = __vmaxs2(__vmaxs2(lo + kBias - vh, vh + kBias - hi), tk) - tk;
+  return __byte_perm(sl, sh, 0x6420);
 }
 
 __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   __shared__ __align__(16) unsigned s_src[kSrcH * (kSrcPitch / 4)];
+  __shared__ __align__(16) unsigned s_E[kSrcH * kPairPitch];
+  __shared__ __align__(16) unsigned s_O[kSrcH * kPairPitch];
   __shared__ __align__(16) uint8_t s_score[kScoreH][kScoreW];
   __shared__ uint32_t s_list[(kFastTileW / 2 + 1) * (kFastTileH / 2 + 1) + 32];
   __shared__ uint32_t s_hist[256];
@@ -148,8 +144,12 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   // tile column c <-> image x = x0 - 5 + c (score column 0 = x0 - 1 sits at tile column 4, word aligned);
   // tile row r <-> image y = y0 - 4 + r
   const int gx0 = x0 - 5, gy0 = y0 - 4;
+  const int Lw = L.w, Lh = L.h, pitch = L.pitch;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
   const int tid = threadIdx.x;
+  // rows of the score region that can matter: image rows up to h - 31 (NMS ring of the last interior row)
+  const int rows_needed = min(kScoreH, Lh - kEdge + 1 - (y0 - 1));  // score rows 0 .. rows_needed-1
+  const int src_rows = min(kSrcH, rows_needed + 6);
 
   s_hist[tid] = 0;
   if (tid == 0) s_n = 0;
@@ -158,23 +158,36 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   if (L.aligned4) {
     const int sh = 8 * (gx0 & 3);
     const int ga = gx0 & ~3;
-    for (int i = tid; i < 18 * kSrcH; i += 256) {
+    for (int i = tid; i < 18 * src_rows; i += 256) {
       const int r = i / 18, c = i - r * 18;
-      const int gy = min(gy0 + r, L.h - 1);
-      const uint8_t* p = img + (size_t)gy * L.pitch;
-      const int a0 = min(ga + c * 4, L.pitch - 4), a1 = min(ga + c * 4 + 4, L.pitch - 4);
+      const int gy = min(gy0 + r, Lh - 1);
+      const uint8_t* p = img + (size_t)gy * pitch;
+      const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
       const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
       const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
       s_src[r * wpr + c] = __funnelshift_r(w0, w1, sh);
     }
   } else {
     uint8_t* sb = reinterpret_cast<uint8_t*>(s_src);
-    for (int i = tid; i < 72 * kSrcH; i += 256) {
+    for (int i = tid; i < 72 * src_rows; i += 256) {
       const int r = i / 72, c = i - r * 72;
-      const int gy = min(gy0 + r, L.h - 1);
-      const int gx = min(gx0 + c, L.w - 1);
-      sb[r * kSrcPitch + c] = __ldg(img + (size_t)gy * L.pitch + gx);
+      const int gy = min(gy0 + r, Lh - 1);
+      const int gx = min(gx0 + c, Lw - 1);
+      sb[r * kSrcPitch + c] = __ldg(img + (size_t)gy * pitch + gx);
     }
+  }
+  __syncthreads();
+  // widen to the two 16x2 copies
+  for (int i = tid; i < 18 * src_rows; i += 256) {
+    const int r = i / 18, c = i - r * 18;
+    const unsigned w = s_src[r * wpr + c];
+    const unsigned wn = c < 17 ? s_src[r * wpr + c + 1] : 0u;
+    unsigned* e = s_E + r * kPairPitch + 2 * c;
+    unsigned* o = s_O + r * kPairPitch + 2 * c;
+    e[0] = __byte_perm(w, 0u, 0x4140);   // (p0, p1)
+    e[1] = __byte_perm(w, 0u, 0x4342);   // (p2, p3)
+    o[0] = __byte_perm(w, 0u, 0x4241);   // (p1, p2)
+    o[1] = __byte_perm(w, wn, 0x4443) & 0x00FF00FFu;  // (p3, p4): p4 is byte 0 of the next word
   }
   __syncthreads();
 
@@ -185,32 +198,31 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
 #pragma unroll 1
     for (int k = 0; k < 2; ++k) {
       const int cy = (tid >> 4) + k * 16;
-      const int gy = y0 - 1 + cy;
       unsigned sc = 0;
-      // warp-uniform skip of rows/columns that are entirely outside the scored region is not needed:
-      // out-of-range pixels are masked below (their tile bytes are clamped copies, never out of bounds)
-      sc = fast_score4(s_src + (cy + 3) * wpr + c4 + 1, g.fast_threshold);
-      if (gy > L.h - kEdge) sc = 0;
-      const int over = gx + 3 - (L.w - kEdge);  // pixels with x > w-31 are not scored
+      // a warp covers score rows 2w, 2w+1 (+16): skip the ones below the last row that can matter
+      if ((cy & ~1) < rows_needed) sc = fast_score4(s_E, s_O, cy + 3, 4 + 4 * c4, g.fast_threshold);
+      if (cy >= rows_needed) sc = 0;
+      const int over = gx + 3 - (Lw - kEdge);  // pixels with x > w-31 are not scored
       if (over > 0) sc = over >= 4 ? 0u : (sc & (0xFFFFFFFFu >> (8 * over)));
       *reinterpret_cast<unsigned*>(&s_score[cy][c4 * 4]) = sc;
     }
   }
   __syncthreads();
 
-  // NMS + border cull over the 62x30 interior
+  // NMS + border cull over the 62x30 interior (shifted scores keep the order; emit score = s' + t - 1)
+  const int sadd = g.fast_threshold - 1;
   for (int i = tid; i < kFastTileW * kFastTileH; i += 256) {
     const int iy = i / kFastTileW, ix = i - iy * kFastTileW;
     const int gx = x0 + ix, gy = y0 + iy;
     const int s = s_score[iy + 1][ix + 1];
-    if (s == 0 || gx >= L.w - kEdge || gy >= L.h - kEdge) continue;
+    if (s == 0 || gx >= Lw - kEdge || gy >= Lh - kEdge) continue;
     const bool keep = s > s_score[iy][ix] && s > s_score[iy][ix + 1] && s > s_score[iy][ix + 2] &&
                       s > s_score[iy + 1][ix] && s > s_score[iy + 1][ix + 2] && s > s_score[iy + 2][ix] &&
                       s > s_score[iy + 2][ix + 1] && s > s_score[iy + 2][ix + 2];
     if (keep) {
       const uint32_t slot = atomicAdd(&s_n, 1u);
-      s_list[slot] = pack_cand(gx, gy, s);
-      atomicAdd(&s_hist[s], 1u);
+      s_list[slot] = pack_cand(gx, gy, s + sadd);
+      atomicAdd(&s_hist[s + sadd], 1u);
     }
   }
   __syncthreads();

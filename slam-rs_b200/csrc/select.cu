@@ -22,16 +22,22 @@ __device__ __forceinline__ float key_float(uint32_t k) {
 // ------------------------------------------------------------------------------------------------
 // S3 + S4: threshold from the score histogram, Harris for the survivors
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float harris_at(const uint8_t* img, int pitch, int x, int y) {
-  // 9x9 window, rows y-4..y+4; rolling rows of horizontal difference / smoothing (7 columns each)
+// Harris response from the 9x9 window held as 9 rows x 3 aligned words (bytes `off`.. of each row)
+__device__ __forceinline__ float harris_from_words(const unsigned* wds, unsigned off) {
+  // rolling rows of horizontal difference / smoothing (7 columns each)
   int hd[3][7], hs[3][7];
   int a = 0, b = 0, c = 0;
 #pragma unroll
   for (int r = 0; r < 9; ++r) {
-    const uint8_t* p = img + (size_t)(y - 4 + r) * pitch + (x - 4);
+    const unsigned w0 = wds[r * 3], w1 = wds[r * 3 + 1], w2 = wds[r * 3 + 2];
+    const unsigned a0 = __funnelshift_r(w0, w1, 8 * off), a1 = __funnelshift_r(w1, w2, 8 * off), a2 = w2 >> (8 * off);
     int v[9];
 #pragma unroll
-    for (int i = 0; i < 9; ++i) v[i] = __ldg(p + i);
+    for (int i = 0; i < 4; ++i) {
+      v[i] = (int)((a0 >> (8 * i)) & 0xFFu);
+      v[4 + i] = (int)((a1 >> (8 * i)) & 0xFFu);
+    }
+    v[8] = (int)(a2 & 0xFFu);
     const int slot = r % 3;
 #pragma unroll
     for (int i = 0; i < 7; ++i) {
@@ -60,18 +66,25 @@ __device__ __forceinline__ float harris_at(const uint8_t* img, int pitch, int x,
 }
 
 constexpr int kHarrisBlocksPerLevel = 8;
+constexpr int kHarrisWarps = 8;
+constexpr int kHarrisSlab = 27;  // 27 words per candidate; odd stride = conflict-free per-thread reads
 
-__global__ void __launch_bounds__(256) harris_kernel(DevGeom g) {
+// S3 threshold from the score histogram, then Harris on the survivors.  Survivors are queued per block;
+// each warp takes 32 of them, fetches every 9x9 window with ONE warp load (lane -> row lane/3, aligned
+// word lane%3: nine cache lines per candidate instead of 81 scattered byte loads per thread) into its
+// shared-memory slab, then runs one candidate per thread out of shared memory.
+__global__ void __launch_bounds__(kHarrisWarps * 32) harris_kernel(DevGeom g) {
   __shared__ uint32_t s_hist[256];
   __shared__ int s_thr;
   __shared__ uint32_t s_queue[512];
   __shared__ uint32_t s_qn;
+  __shared__ unsigned s_win[kHarrisWarps][32 * kHarrisSlab];
   const int l = blockIdx.y, frame = blockIdx.z;
   const DevLevel& L = g.lv[l];
   const size_t fl = (size_t)frame * kMaxLevels + l;
   const uint32_t count = min(g.cand_count[fl], (uint32_t)L.cand_cap);
   if (count == 0) return;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // S3: thr = largest score s with #(score >= s) >= 2*N_l; everything if the list is short
   s_hist[tid] = g.hist[fl * 256 + tid];
@@ -99,8 +112,9 @@ __global__ void __launch_bounds__(256) harris_kernel(DevGeom g) {
   const uint32_t* cand = L.cand + (size_t)frame * L.cand_cap;
   uint32_t* key = L.key + (size_t)frame * L.cand_cap;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
+  const int pitch = L.pitch;
+  const bool aligned = L.aligned4 != 0;
 
-  // block-compacted processing: gather survivors into a queue, run Harris on dense batches
   const uint32_t per_block = (count + gridDim.x - 1) / gridDim.x;
   const uint32_t begin = blockIdx.x * per_block;
   const uint32_t end = min(count, begin + per_block);
@@ -116,14 +130,48 @@ __global__ void __launch_bounds__(256) harris_kernel(DevGeom g) {
     }
     __syncthreads();
     const bool last = base + 256 >= end;
-    uint32_t qn = s_qn;
+    const uint32_t qn = s_qn;
     if (qn >= 256 || last) {
-      for (uint32_t off = 0; off < qn; off += 256) {
-        if (off + tid < qn) {
-          const uint32_t j = s_queue[off + tid];
-          const uint32_t cw = cand[j];
-          key[j] = float_key(harris_at(img, L.pitch, (int)(cw & 0xFFF), (int)((cw >> 12) & 0xFFF)));
+      for (uint32_t off0 = warp * 32; off0 < qn; off0 += kHarrisWarps * 32) {
+        const uint32_t mine = off0 + lane;
+        uint32_t j = 0, cw = 0;
+        if (mine < qn) {
+          j = s_queue[mine];
+          cw = cand[j];
         }
+        const int nloc = (int)min(32u, qn - off0);
+        // cooperative fetch: staged word i = lane + 32t belongs to candidate i/27, window word i%27
+        // (row (i%27)/3, aligned word (i%27)%3); all 27 loads of a lane are independent and in flight together
+        unsigned stg[27];
+#pragma unroll
+        for (int t = 0; t < 27; ++t) {
+          const int i = lane + 32 * t;
+          const int cidx = i / 27, wd = i - cidx * 27;
+          const int wrow = wd / 3, wword = wd - wrow * 3;
+          const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
+          stg[t] = 0;
+          if (cidx < nloc) {
+            const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
+            const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
+            if (aligned) {
+              stg[t] = __ldg(reinterpret_cast<const unsigned*>(p - ((uintptr_t)p & 3)) + wword);
+            } else {
+              const uint8_t* q = p + 4 * wword;
+              stg[t] = (unsigned)__ldg(q) | ((unsigned)__ldg(q + 1) << 8) | ((unsigned)__ldg(q + 2) << 16) |
+                       ((unsigned)__ldg(q + 3) << 24);
+            }
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < 27; ++t) s_win[warp][lane + 32 * t] = stg[t];
+        __syncwarp();
+        if (mine < qn) {
+          const int x = (int)(cw & 0xFFF), y = (int)((cw >> 12) & 0xFFF);
+          const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
+          const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
+          key[j] = float_key(harris_from_words(&s_win[warp][lane * kHarrisSlab], boff));
+        }
+        __syncwarp();
       }
       __syncthreads();
       if (tid == 0) s_qn = 0;
@@ -289,7 +337,20 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kOrientWarps = 8;
+constexpr int kOrientPerWarp = 4;
 
+__device__ __forceinline__ int dp4a_us(unsigned a, unsigned b_signed_bytes, int c) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b_signed_bytes), "r"(c));
+  return d;
+}
+
+// One warp per keypoint.  The 31 x 36-byte patch (nine aligned 32-bit words per row) is fetched with
+// row-contiguous lanes (word i = lane + 32t -> row i/9, word i%9: ~4 rows per load instruction instead
+// of 32 scattered lines) and transposed through a per-warp shared-memory slab; then lane = patch row
+// v = lane-15 funnel-shifts its nine words onto the u = -15 origin and takes the two row sums
+// (sum u*p and sum p over |u| <= umax[|v|]) with 16 DP4A against per-lane coefficient words that are
+// built once per warp; the warp totals are two integer warp reductions.
 __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, OutArgs o) {
   const int frame = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -302,53 +363,109 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
   const uint32_t total = pre[kMaxLevels];
   if (blockIdx.x == 0 && threadIdx.x == 0) o.n[frame] = (int)total;
   const uint32_t limit = min(total, (uint32_t)min(o.cap, o.lvl_cap));
-  const uint32_t j = blockIdx.x * kOrientWarps + warp;
-  if (j >= limit) return;
-  int l = 0;
-#pragma unroll
-  for (int i = 1; i < kMaxLevels; ++i)
-    if (j >= pre[i]) l = i;
-  const DevLevel& L = g.lv[l];
-  const unsigned long long e = L.sel[(size_t)frame * L.sel_cap + (j - pre[l])];
-  const uint32_t pos = 0xFFFFFFu - (uint32_t)(e & 0xFFFFFFu);
-  const int x = (int)(pos & 0xFFF), y = (int)(pos >> 12);
-  const float response = key_float((uint32_t)(e >> 32));
 
-  const uint8_t* img = L.img + (size_t)frame * L.frame_stride + (size_t)y * L.pitch + x;
-  const int u = lane - 15;  // lanes 0..30 cover u = -15..15
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-    for (int v = -15; v <= 15; ++v) {
-      if (abs(u) <= c_umax[abs(v)]) {
-        const int p = __ldg(img + v * L.pitch + u);
-        m10 += u * p;
-        m01 += v * p;
+  // per-lane coefficient words: byte b of word k <-> u = -15 + 4k + b
+  const int v = min(lane, 30) - 15;
+  const int um = lane < 31 ? c_umax[abs(v)] : -1;
+  unsigned cu[8], cm[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    unsigned wu = 0, wm = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int u = -15 + 4 * k + b;
+      if (abs(u) <= um) {
+        wu |= ((unsigned)u & 0xFFu) << (8 * b);
+        wm |= 1u << (8 * b);
       }
     }
+    cu[k] = wu;
+    cm[k] = wm;
   }
+
+  __shared__ unsigned s_patch[kOrientWarps][31 * 9 + 1];
+  // staging geometry of this lane: word i = lane + 32t of the 31 x 9 patch
+  int st_row[9], st_word[9];
 #pragma unroll
-  for (int s = 16; s > 0; s >>= 1) {
-    m10 += __shfl_xor_sync(0xFFFFFFFFu, m10, s);
-    m01 += __shfl_xor_sync(0xFFFFFFFFu, m01, s);
+  for (int t = 0; t < 9; ++t) {
+    const int i = lane + 32 * t;
+    st_row[t] = i / 9;
+    st_word[t] = i - st_row[t] * 9;
   }
-  if (lane == 0) {
-    orbx_keypoint kp;
-    kp.x = __fmul_rn((float)x, L.scale);
-    kp.y = __fmul_rn((float)y, L.scale);
-    kp.size = __fmul_rn(31.0f, L.scale);
-    kp.angle = fast_atan2_deg((float)m01, (float)m10);
-    kp.response = response;
-    kp.octave = l;
-    kp.class_id = -1;
-    o.kps[(size_t)frame * o.cap + j] = kp;
-    o.kp_lvl[(size_t)frame * o.lvl_cap + j] = ((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+
+  for (int it = 0; it < kOrientPerWarp; ++it) {
+    const uint32_t j = (blockIdx.x * kOrientPerWarp + it) * kOrientWarps + warp;
+    if (j >= limit) return;
+    int l = 0;
+    uint32_t first = 0;
+#pragma unroll
+    for (int i = 1; i < kMaxLevels; ++i)
+      if (j >= pre[i]) {
+        l = i;
+        first = pre[i];
+      }
+    const DevLevel& L = g.lv[l];
+    const unsigned long long e = L.sel[(size_t)frame * L.sel_cap + (j - first)];
+    const uint32_t pos = 0xFFFFFFu - (uint32_t)(e & 0xFFFFFFu);
+    const int x = (int)(pos & 0xFFF), y = (int)(pos >> 12);
+    const int pitch = L.pitch;
+
+    const uint8_t* seg = L.img + (size_t)frame * L.frame_stride + (size_t)(y + v) * pitch + (x - 15);
+    unsigned a[8];
+    if (L.aligned4) {
+      // all rows share the alignment of row 0 (pitch and stride are multiples of 4)
+      const uint8_t* seg0 = L.img + (size_t)frame * L.frame_stride + (size_t)(y - 15) * pitch + (x - 15);
+      const unsigned off = (unsigned)((uintptr_t)seg0 & 3);
+      const uint8_t* base = seg0 - off;
+      unsigned stg[9];
+#pragma unroll
+      for (int t = 0; t < 9; ++t)
+        if (t < 8 || lane < 279 - 256)
+          stg[t] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)st_row[t] * pitch) + st_word[t]);
+      __syncwarp();  // previous keypoint's reads are done
+#pragma unroll
+      for (int t = 0; t < 9; ++t)
+        if (t < 8 || lane < 279 - 256) s_patch[warp][lane + 32 * t] = stg[t];
+      __syncwarp();
+      unsigned w[9];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) w[k] = s_patch[warp][min(lane, 30) * 9 + k];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] = __funnelshift_r(w[k], w[k + 1], 8 * off);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        a[k] = (unsigned)__ldg(seg + 4 * k) | ((unsigned)__ldg(seg + 4 * k + 1) << 8) |
+               ((unsigned)__ldg(seg + 4 * k + 2) << 16) | ((unsigned)__ldg(seg + 4 * k + 3) << 24);
+    }
+    int ru = 0, rs = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      ru = dp4a_us(a[k], cu[k], ru);
+      rs = dp4a_us(a[k], cm[k], rs);
+    }
+    const int m10 = __reduce_add_sync(0xFFFFFFFFu, ru);
+    const int m01 = __reduce_add_sync(0xFFFFFFFFu, v * rs);
+    if (lane == 0) {
+      const float response = key_float((uint32_t)(e >> 32));
+      orbx_keypoint kp;
+      kp.x = __fmul_rn((float)x, L.scale);
+      kp.y = __fmul_rn((float)y, L.scale);
+      kp.size = __fmul_rn(31.0f, L.scale);
+      kp.angle = fast_atan2_deg((float)m01, (float)m10);
+      kp.response = response;
+      kp.octave = l;
+      kp.class_id = -1;
+      o.kps[(size_t)frame * o.cap + j] = kp;
+      o.kp_lvl[(size_t)frame * o.lvl_cap + j] = ((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+    }
   }
 }
 
 int launch_orient(const DevGeom& g, const OutArgs& o, cudaStream_t s) {
   if (g.batch == 0) return ORBX_OK;
   const int lim = o.cap < o.lvl_cap ? o.cap : o.lvl_cap;
-  dim3 grid(div_up(lim > 0 ? lim : 1, kOrientWarps), g.batch);
+  dim3 grid(div_up(lim > 0 ? lim : 1, kOrientWarps * kOrientPerWarp), g.batch);
   orient_kernel<<<grid, kOrientWarps * 32, 0, s>>>(g, o);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
