@@ -64,7 +64,8 @@ constexpr int kPairPitch = 36;  // words (= pixel pairs) per tile row; 72 pixels
 
 // scores (shifted: 0 = not a corner, s' = m - t >= 1 for corners, i.e. score = s' + t - 1) of 4 adjacent
 // pixels whose first pixel is tile column tc (multiple of 4) of tile row tr
-__device__ __forceinline__ unsigned fast_score4(const unsigned* sE, const unsigned* sO, int tr, int tc, int t) {
+__device__ __forceinline__ void fast_score4(const unsigned* sE, const unsigned* sO, int tr, int tc, int t, unsigned& sl,
+                                            unsigned& sh) {
   const int pe = tc >> 1;  // pair index of (tc, tc+1) in E; O pair (tc+1, tc+2) has the same index
   unsigned Rl[16], Rh[16];
   // ring offset (DX, DY): pixels tc+DX, tc+DX+1 (lo reg) and tc+DX+2, tc+DX+3 (hi reg)
@@ -97,7 +98,7 @@ __device__ __forceinline__ unsigned fast_score4(const unsigned* sE, const unsign
       const unsigned mb = pb + kBias - v, md = v + kBias - pd;  // 256 + contrast, lanes in 1..511
       possible |= __vmaxs2(__vmaxs2(mb, md), tk) - tk;          // > 0 in some lane?
     }
-    if (!__any_sync(0xFFFFFFFFu, possible != 0)) return 0u;
+    if (!__any_sync(0xFFFFFFFFu, possible != 0)) return;  // sl, sh stay 0
   }
   ORBX_RING(1, 1, 3)
   ORBX_RING(2, 2, 2)
@@ -112,19 +113,19 @@ __device__ __forceinline__ unsigned fast_score4(const unsigned* sE, const unsign
   ORBX_RING(14, -2, 2)
   ORBX_RING(15, -1, 3)
 #undef ORBX_RING
-  unsigned lo, hi, sl, sh;
+  unsigned lo, hi;
   fast_arcs16x2(Rl, lo, hi);
   sl = __vmaxs2(__vmaxs2(lo + kBias - vl, vl + kBias - hi), tk) - tk;  // max(m - t, 0) per lane
   fast_arcs16x2(Rh, lo, hi);
   sh = __vmaxs2(__vmaxs2(lo + kBias - vh, vh + kBias - hi), tk) - tk;
-  return __byte_perm(sl, sh, 0x6420);
 }
 
+constexpr int kScPitch = 34;  // words per row of the 16x2 score tile: pad pair, 32 pairs, pad pair
+
 __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
-  __shared__ __align__(16) unsigned s_src[kSrcH * (kSrcPitch / 4)];
   __shared__ __align__(16) unsigned s_E[kSrcH * kPairPitch];
   __shared__ __align__(16) unsigned s_O[kSrcH * kPairPitch];
-  __shared__ __align__(16) uint8_t s_score[kScoreH][kScoreW];
+  __shared__ __align__(16) unsigned s_sc[kScoreH * kScPitch];
   __shared__ uint32_t s_list[(kFastTileW / 2 + 1) * (kFastTileH / 2 + 1) + 32];
   __shared__ uint32_t s_hist[256];
   __shared__ uint32_t s_n, s_base;
@@ -154,75 +155,102 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   s_hist[tid] = 0;
   if (tid == 0) s_n = 0;
 
-  constexpr int wpr = kSrcPitch / 4;  // 20 words per tile row, 18 used
-  if (L.aligned4) {
+  // stage the 72 x 38 footprint, widened to the two 16x2 copies, straight from global memory
+  {
+    const bool al = L.aligned4 != 0;
     const int sh = 8 * (gx0 & 3);
     const int ga = gx0 & ~3;
-    for (int i = tid; i < 18 * src_rows; i += 256) {
-      const int r = i / 18, c = i - r * 18;
-      const int gy = min(gy0 + r, Lh - 1);
-      const uint8_t* p = img + (size_t)gy * pitch;
-      const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
-      const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
-      const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
-      s_src[r * wpr + c] = __funnelshift_r(w0, w1, sh);
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int i = tid + it * 256;
+      if (i < 18 * src_rows) {
+        const int r = i / 18, c = i - r * 18;
+        const int gy = min(gy0 + r, Lh - 1);
+        const uint8_t* p = img + (size_t)gy * pitch;
+        unsigned w, nx;  // w = pixels 4c..4c+3 of the tile row, nx byte 0 = pixel 4c+4
+        if (al) {
+          const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
+          const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
+          const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
+          w = __funnelshift_r(w0, w1, sh);
+          nx = w1 >> sh;
+        } else {
+          const int gx = gx0 + 4 * c;
+          w = (unsigned)__ldg(p + min(gx, Lw - 1)) | ((unsigned)__ldg(p + min(gx + 1, Lw - 1)) << 8) |
+              ((unsigned)__ldg(p + min(gx + 2, Lw - 1)) << 16) | ((unsigned)__ldg(p + min(gx + 3, Lw - 1)) << 24);
+          nx = __ldg(p + min(gx + 4, Lw - 1));
+        }
+        unsigned* e = s_E + r * kPairPitch + 2 * c;
+        unsigned* o = s_O + r * kPairPitch + 2 * c;
+        e[0] = __byte_perm(w, 0u, 0x4140);                 // (p0, p1)
+        e[1] = __byte_perm(w, 0u, 0x4342);                 // (p2, p3)
+        o[0] = __byte_perm(w, 0u, 0x4241);                 // (p1, p2)
+        o[1] = __byte_perm(w, nx, 0x4443) & 0x00FF00FFu;   // (p3, p4)
+      }
     }
-  } else {
-    uint8_t* sb = reinterpret_cast<uint8_t*>(s_src);
-    for (int i = tid; i < 72 * src_rows; i += 256) {
-      const int r = i / 72, c = i - r * 72;
-      const int gy = min(gy0 + r, Lh - 1);
-      const int gx = min(gx0 + c, Lw - 1);
-      sb[r * kSrcPitch + c] = __ldg(img + (size_t)gy * pitch + gx);
-    }
-  }
-  __syncthreads();
-  // widen to the two 16x2 copies
-  for (int i = tid; i < 18 * src_rows; i += 256) {
-    const int r = i / 18, c = i - r * 18;
-    const unsigned w = s_src[r * wpr + c];
-    const unsigned wn = c < 17 ? s_src[r * wpr + c + 1] : 0u;
-    unsigned* e = s_E + r * kPairPitch + 2 * c;
-    unsigned* o = s_O + r * kPairPitch + 2 * c;
-    e[0] = __byte_perm(w, 0u, 0x4140);   // (p0, p1)
-    e[1] = __byte_perm(w, 0u, 0x4342);   // (p2, p3)
-    o[0] = __byte_perm(w, 0u, 0x4241);   // (p1, p2)
-    o[1] = __byte_perm(w, wn, 0x4443) & 0x00FF00FFu;  // (p3, p4): p4 is byte 0 of the next word
   }
   __syncthreads();
 
   // score region: columns x0-1 .. x0+62, rows y0-1 .. y0+30; 4 pixels per thread, 2 rows per thread
-  {
-    const int c4 = tid & 15;          // group of 4 score columns
-    const int gx = x0 - 1 + c4 * 4;   // image x of the first of the 4 pixels
+  const int c4 = tid & 15;               // group of 4 score columns
+  const int gxs = x0 - 1 + c4 * 4;       // image x of the first of the 4 pixels
+  const int over = gxs + 3 - (Lw - kEdge);  // pixels with x > w-31 are not scored
 #pragma unroll 1
-    for (int k = 0; k < 2; ++k) {
-      const int cy = (tid >> 4) + k * 16;
-      unsigned sc = 0;
-      // a warp covers score rows 2w, 2w+1 (+16): skip the ones below the last row that can matter
-      if ((cy & ~1) < rows_needed) sc = fast_score4(s_E, s_O, cy + 3, 4 + 4 * c4, g.fast_threshold);
-      if (cy >= rows_needed) sc = 0;
-      const int over = gx + 3 - (Lw - kEdge);  // pixels with x > w-31 are not scored
-      if (over > 0) sc = over >= 4 ? 0u : (sc & (0xFFFFFFFFu >> (8 * over)));
-      *reinterpret_cast<unsigned*>(&s_score[cy][c4 * 4]) = sc;
-    }
+  for (int k = 0; k < 2; ++k) {
+    const int cy = (tid >> 4) + k * 16;
+    unsigned sl = 0, sh = 0;
+    // a warp covers score rows 2w, 2w+1 (+16): skip the ones below the last row that can matter
+    if ((cy & ~1) < rows_needed) fast_score4(s_E, s_O, cy + 3, 4 + 4 * c4, g.fast_threshold, sl, sh);
+    if (cy >= rows_needed || over >= 4) sl = sh = 0;
+    if (over >= 2) sh = 0;
+    if (over == 3) sl &= 0xFFFFu;
+    if (over == 1) sh &= 0xFFFFu;
+    s_sc[cy * kScPitch + 1 + 2 * c4] = sl;
+    s_sc[cy * kScPitch + 2 + 2 * c4] = sh;
   }
   __syncthreads();
 
-  // NMS + border cull over the 62x30 interior (shifted scores keep the order; emit score = s' + t - 1)
+  // strict 3x3 NMS in the same 16x2 form: horizontal 3-max of the rows above and below plus the two
+  // side neighbours, then one compare per pixel; border cull; emit score = s' + t - 1
   const int sadd = g.fast_threshold - 1;
-  for (int i = tid; i < kFastTileW * kFastTileH; i += 256) {
-    const int iy = i / kFastTileW, ix = i - iy * kFastTileW;
-    const int gx = x0 + ix, gy = y0 + iy;
-    const int s = s_score[iy + 1][ix + 1];
-    if (s == 0 || gx >= Lw - kEdge || gy >= Lh - kEdge) continue;
-    const bool keep = s > s_score[iy][ix] && s > s_score[iy][ix + 1] && s > s_score[iy][ix + 2] &&
-                      s > s_score[iy + 1][ix] && s > s_score[iy + 1][ix + 2] && s > s_score[iy + 2][ix] &&
-                      s > s_score[iy + 2][ix + 1] && s > s_score[iy + 2][ix + 2];
-    if (keep) {
-      const uint32_t slot = atomicAdd(&s_n, 1u);
-      s_list[slot] = pack_cand(gx, gy, s + sadd);
-      atomicAdd(&s_hist[s + sadd], 1u);
+#pragma unroll 1
+  for (int k = 0; k < 2; ++k) {
+    const int cy = (tid >> 4) + k * 16;
+    const int gy = y0 - 1 + cy;
+    if (cy < 1 || cy > kFastTileH || gy >= Lh - kEdge) continue;
+    const unsigned* base = s_sc + cy * kScPitch + 2 * c4;  // pairs (x-2,x-1) (x,x+1) (x+2,x+3) (x+4,x+5)
+    unsigned nb0, nb1, m0, m1;
+    {
+      const uint2 a = *reinterpret_cast<const uint2*>(base - kScPitch), b = *reinterpret_cast<const uint2*>(base - kScPitch + 2);
+      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
+      nb0 = max3x2(l0, a.y, l1);
+      nb1 = max3x2(l1, b.x, l2);
+    }
+    {
+      const uint2 a = *reinterpret_cast<const uint2*>(base + kScPitch), b = *reinterpret_cast<const uint2*>(base + kScPitch + 2);
+      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
+      nb0 = max3x2(nb0, max3x2(l0, a.y, l1), 0u);
+      nb1 = max3x2(nb1, max3x2(l1, b.x, l2), 0u);
+    }
+    {
+      const uint2 a = *reinterpret_cast<const uint2*>(base), b = *reinterpret_cast<const uint2*>(base + 2);
+      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
+      nb0 = max3x2(nb0, l0, l1);
+      nb1 = max3x2(nb1, l1, l2);
+      m0 = a.y;
+      m1 = b.x;
+    }
+    // per pixel j: column 4*c4 + j of the score region; interior columns are 1..62
+    const int sv[4] = {(int)(m0 & 0xFFFF), (int)(m0 >> 16), (int)(m1 & 0xFFFF), (int)(m1 >> 16)};
+    const int nv[4] = {(int)(nb0 & 0xFFFF), (int)(nb0 >> 16), (int)(nb1 & 0xFFFF), (int)(nb1 >> 16)};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int col = 4 * c4 + j, gx = gxs + j;
+      if (sv[j] > nv[j] && col >= 1 && col <= kFastTileW && gx < Lw - kEdge) {
+        const uint32_t slot = atomicAdd(&s_n, 1u);
+        s_list[slot] = pack_cand(gx, gy, sv[j] + sadd);
+        atomicAdd(&s_hist[sv[j] + sadd], 1u);
+      }
     }
   }
   __syncthreads();
