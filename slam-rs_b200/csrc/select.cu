@@ -65,19 +65,58 @@ __device__ __forceinline__ float harris_from_words(const unsigned* wds, unsigned
   return __fmul_rn(__fsub_rn(t1, t2), s4);
 }
 
-constexpr int kHarrisBlocksPerLevel = 8;
+constexpr int kHarrisBlocksPerLevel = 4;
 constexpr int kHarrisWarps = 8;
 constexpr int kHarrisSlab = 27;  // 27 words per candidate; odd stride = conflict-free per-thread reads
 
-// S3 threshold from the score histogram, then Harris on the survivors.  Survivors are queued per block;
-// each warp takes 32 of them, fetches every 9x9 window with ONE warp load (lane -> row lane/3, aligned
-// word lane%3: nine cache lines per candidate instead of 81 scattered byte loads per thread) into its
-// shared-memory slab, then runs one candidate per thread out of shared memory.
-__global__ void __launch_bounds__(kHarrisWarps * 32) harris_kernel(DevGeom g) {
+// Largest bin b >= 1 of a 256-bin histogram with sum_{i >= b} hist[i] >= rem (0 if there is none), and the
+// count strictly above it.  Block-wide (>= 256 threads), replaces a 256-step serial scan by thread 0.
+// scratch: 10 words of shared memory.  Ends with a __syncthreads().
+__device__ __forceinline__ void find_bin_desc(const uint32_t* hist, uint32_t rem, uint32_t* scratch, int& bin,
+                                              uint32_t& above) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint32_t v = 0, incl = 0;
+  if (tid < 256) {
+    v = hist[255 - tid];  // position j = tid <-> bin 255 - j, so a prefix over j is a suffix over bins
+    incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (lane == 31) scratch[warp] = incl;
+  }
+  __syncthreads();
+  if (tid < 256) {
+    uint32_t pre = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w)
+      if (w < warp) pre += scratch[w];
+    incl += pre;
+    if (tid == 254) {  // bin 1: default answer = "not reached": bin 0, everything in bins 1..255 above it
+      scratch[8] = 0;
+      scratch[9] = incl;
+    }
+  }
+  __syncthreads();
+  if (tid < 255 && incl >= rem && incl - v < rem) {
+    scratch[8] = 255 - tid;
+    scratch[9] = incl - v;
+  }
+  __syncthreads();
+  bin = (int)scratch[8];
+  above = scratch[9];
+}
+
+// S3 threshold from the score histogram (parallel suffix scan), then Harris on the survivors.  After the
+// threshold every warp works alone on its slice of the candidate list: ballot-compacts survivors into a
+// warp-private queue and, 32 at a time, fetches the 9x9 windows with cp.async (word i = lane + 32t ->
+// candidate i/27, row (i%27)/3, aligned word (i%27)%3: ~11 cache lines per load instruction, all 27 in
+// flight) into its shared-memory slab, then runs one candidate per thread out of shared memory.
+__global__ void __launch_bounds__(kHarrisWarps * 32, 2) harris_kernel(DevGeom g) {
   __shared__ uint32_t s_hist[256];
-  __shared__ int s_thr;
-  __shared__ uint32_t s_queue[512];
-  __shared__ uint32_t s_qn;
+  __shared__ uint32_t s_scratch[10];
+  __shared__ uint32_t s_queue[kHarrisWarps][64];
   __shared__ unsigned s_win[kHarrisWarps][32 * kHarrisSlab];
   const int l = blockIdx.y, frame = blockIdx.z;
   const DevLevel& L = g.lv[l];
@@ -87,96 +126,97 @@ __global__ void __launch_bounds__(kHarrisWarps * 32) harris_kernel(DevGeom g) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // S3: thr = largest score s with #(score >= s) >= 2*N_l; everything if the list is short
-  s_hist[tid] = g.hist[fl * 256 + tid];
-  if (tid == 0) {
-    s_thr = 0;
-    s_qn = 0;
-  }
-  __syncthreads();
   const uint32_t n_keep = 2u * (uint32_t)L.quota;
-  if (tid == 0) {
-    if (n_keep == 0) {
-      s_thr = 256;  // retainBest(0): nothing survives
-    } else if (count > n_keep) {
-      uint32_t acc = 0;
-      int s = 255;
-      for (; s > 0; --s) {
-        acc += s_hist[s];
-        if (acc >= n_keep) break;
-      }
-      s_thr = s;
-    }
+  int thr = 0;
+  if (n_keep == 0) {
+    thr = 256;  // retainBest(0): nothing survives
+  } else if (count > n_keep) {
+    s_hist[tid] = g.hist[fl * 256 + tid];
+    __syncthreads();
+    uint32_t above;
+    find_bin_desc(s_hist, n_keep, s_scratch, thr, above);
   }
-  __syncthreads();
-  const int thr = s_thr;
   const uint32_t* cand = L.cand + (size_t)frame * L.cand_cap;
   uint32_t* key = L.key + (size_t)frame * L.cand_cap;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
   const int pitch = L.pitch;
   const bool aligned = L.aligned4 != 0;
 
-  const uint32_t per_block = (count + gridDim.x - 1) / gridDim.x;
-  const uint32_t begin = blockIdx.x * per_block;
-  const uint32_t end = min(count, begin + per_block);
-  for (uint32_t base = begin; base < end; base += 256) {
-    const uint32_t i = base + tid;
-    if (i < end) {
-      const uint32_t cw = cand[i];
-      if ((int)(cw >> 24) >= thr) {
-        s_queue[atomicAdd(&s_qn, 1u)] = i;
-      } else {
-        key[i] = 0;
+  // slice of this warp (multiple of 32 candidates)
+  const uint32_t nwarps = gridDim.x * kHarrisWarps;
+  const uint32_t per_warp = ((count + nwarps - 1) / nwarps + 31u) & ~31u;
+  const uint32_t begin = (blockIdx.x * kHarrisWarps + warp) * per_warp;
+  const uint32_t end = min(count, begin + per_warp);
+  if (begin >= end) return;
+  uint32_t* q = s_queue[warp];
+  unsigned* win = s_win[warp];
+  const unsigned win_sa = (unsigned)__cvta_generic_to_shared(win);
+
+  auto process = [&](int nloc) {
+    // candidates q[0 .. nloc) : cooperative window fetch, then one candidate per lane
+    uint32_t j = 0, cw = 0;
+    if (lane < nloc) {
+      j = q[lane];
+      cw = cand[j];
+    }
+#pragma unroll
+    for (int t = 0; t < 27; ++t) {
+      const int i = lane + 32 * t;
+      const int cidx = i / 27, wd = i - cidx * 27;
+      const int wrow = wd / 3, wword = wd - wrow * 3;
+      const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
+      if (cidx < nloc) {
+        const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
+        const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
+        if (aligned) {
+          const uint8_t* src = p - ((uintptr_t)p & 3) + 4 * wword;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(win_sa + 4 * i), "l"(src));
+        } else {
+          const uint8_t* b = p + 4 * wword;
+          win[i] = (unsigned)__ldg(b) | ((unsigned)__ldg(b + 1) << 8) | ((unsigned)__ldg(b + 2) << 16) |
+                   ((unsigned)__ldg(b + 3) << 24);
+        }
       }
     }
-    __syncthreads();
-    const bool last = base + 256 >= end;
-    const uint32_t qn = s_qn;
-    if (qn >= 256 || last) {
-      for (uint32_t off0 = warp * 32; off0 < qn; off0 += kHarrisWarps * 32) {
-        const uint32_t mine = off0 + lane;
-        uint32_t j = 0, cw = 0;
-        if (mine < qn) {
-          j = s_queue[mine];
-          cw = cand[j];
-        }
-        const int nloc = (int)min(32u, qn - off0);
-        // cooperative fetch: staged word i = lane + 32t belongs to candidate i/27, window word i%27
-        // (row (i%27)/3, aligned word (i%27)%3); all 27 loads of a lane are independent and in flight together
-        unsigned stg[27];
-#pragma unroll
-        for (int t = 0; t < 27; ++t) {
-          const int i = lane + 32 * t;
-          const int cidx = i / 27, wd = i - cidx * 27;
-          const int wrow = wd / 3, wword = wd - wrow * 3;
-          const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
-          stg[t] = 0;
-          if (cidx < nloc) {
-            const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
-            const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
-            if (aligned) {
-              stg[t] = __ldg(reinterpret_cast<const unsigned*>(p - ((uintptr_t)p & 3)) + wword);
-            } else {
-              const uint8_t* q = p + 4 * wword;
-              stg[t] = (unsigned)__ldg(q) | ((unsigned)__ldg(q + 1) << 8) | ((unsigned)__ldg(q + 2) << 16) |
-                       ((unsigned)__ldg(q + 3) << 24);
-            }
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < 27; ++t) s_win[warp][lane + 32 * t] = stg[t];
-        __syncwarp();
-        if (mine < qn) {
-          const int x = (int)(cw & 0xFFF), y = (int)((cw >> 12) & 0xFFF);
-          const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
-          const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
-          key[j] = float_key(harris_from_words(&s_win[warp][lane * kHarrisSlab], boff));
-        }
-        __syncwarp();
-      }
-      __syncthreads();
-      if (tid == 0) s_qn = 0;
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncwarp();
+    if (lane < nloc) {
+      const int x = (int)(cw & 0xFFF), y = (int)((cw >> 12) & 0xFFF);
+      const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
+      const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
+      key[j] = float_key(harris_from_words(win + lane * kHarrisSlab, boff));
     }
-    __syncthreads();
+    __syncwarp();
+  };
+
+  uint32_t qn = 0;
+  for (uint32_t base = begin;; base += 32) {
+    const bool more = base < end;
+    if (more) {
+      const uint32_t i = base + lane;
+      bool pass = false;
+      if (i < end) {
+        pass = (int)(cand[i] >> 24) >= thr;
+        if (!pass) key[i] = 0;
+      }
+      const unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
+      if (pass) q[qn + __popc(bal & ((1u << lane) - 1u))] = i;
+      qn += __popc(bal);
+      __syncwarp();
+    }
+    if (qn >= 32 || (!more && qn > 0)) {
+      const uint32_t take = min(qn, 32u);
+      process((int)take);
+      const uint32_t rest = qn - take;
+      uint32_t tmp = 0;
+      if (lane < rest) tmp = q[32 + lane];
+      __syncwarp();
+      if (lane < rest) q[lane] = tmp;
+      qn = rest;
+      __syncwarp();
+    }
+    if (!more && qn == 0) break;
   }
 }
 
@@ -196,7 +236,8 @@ constexpr int kSelThreads = 512;
 __global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort_cap) {
   extern __shared__ __align__(16) unsigned long long s_sort[];  // sort_cap entries
   __shared__ uint32_t s_hist[256];
-  __shared__ uint32_t s_prefix, s_remaining, s_nvalid, s_nsel;
+  __shared__ uint32_t s_scratch[10];
+  __shared__ uint32_t s_nvalid, s_nsel;
   const int l = blockIdx.x, frame = blockIdx.y;
   const DevLevel& L = g.lv[l];
   const size_t fl = (size_t)frame * kMaxLevels + l;
@@ -224,35 +265,25 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort
   const uint32_t nvalid = s_nvalid;
   uint32_t thr = 1;  // keep every valid entry
   if (nvalid > (uint32_t)L.quota) {
-    // MSB-first 8-bit radix select of the quota-th largest key
-    if (tid == 0) {
-      s_prefix = 0;
-      s_remaining = (uint32_t)L.quota;
-    }
+    // MSB-first 8-bit radix select of the quota-th largest key (bin search = parallel suffix scan)
+    uint32_t prefix = 0, remaining = (uint32_t)L.quota;
     for (int pass = 0; pass < 4; ++pass) {
       const int shift = 24 - 8 * pass;
       if (tid < 256) s_hist[tid] = 0;
       __syncthreads();
-      const uint32_t prefix = s_prefix;
       const uint32_t mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
       for (uint32_t i = tid; i < count; i += kSelThreads) {
         const uint32_t k = key[i];
         if (k != 0 && (k & mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 0xFF], 1u);
       }
       __syncthreads();
-      if (tid == 0) {
-        uint32_t rem = s_remaining, acc = 0;
-        int b = 255;
-        for (; b > 0; --b) {
-          if (acc + s_hist[b] >= rem) break;
-          acc += s_hist[b];
-        }
-        s_prefix = prefix | ((uint32_t)b << shift);
-        s_remaining = rem - acc;
-      }
-      __syncthreads();
+      int b;
+      uint32_t above;
+      find_bin_desc(s_hist, remaining, s_scratch, b, above);
+      prefix |= (uint32_t)b << shift;
+      remaining -= above;
     }
-    thr = s_prefix;
+    thr = prefix;
   }
   // compaction into the sort buffer
   for (uint32_t i = tid; i < count; i += kSelThreads) {
