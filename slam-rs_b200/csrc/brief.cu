@@ -58,44 +58,44 @@ __global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
   uint8_t* out = L.blur + (size_t)frame * L.blur_stride + (size_t)y0 * blur_pitch + x0 + 4 * lane;
 
   // staging: lane owns word column `lane` (image x0-4+4*lane ..+3); lanes 0,1 also own columns 32,33.
-  // The column geometry (aligned fast path or four reflected byte offsets) is row-invariant.
+  // Words that lie inside the row go global -> shared with cp.async (all rows in flight at once, no
+  // register staging); a second, usually skipped, loop assembles border words from reflected bytes.
   const int nrows = min(kBlurSrcRows, h - y0 + 6);  // source rows needed for the output rows inside the image
   {
     const int xa = x0 - 4 + 4 * lane, xb = xa + 128;
     const bool fa = L.aligned4 && xa >= 0 && xa + 3 < w;
-    const bool fb = L.aligned4 && xb + 3 < w;
-    const bool has_b = lane < 2;
-    int ca[4], cb[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      ca[k] = reflect101(xa + k, w);
-      cb[k] = reflect101(xb + k, w);
-    }
-    // aligned words go global -> shared with cp.async (all rows in flight at once, no register staging);
-    // border words are assembled from reflected byte loads
+    const bool fb = lane < 2 && L.aligned4 && xb + 3 < w;
+    const bool slow_a = !fa, slow_b = lane < 2 && !fb;
     const unsigned sa = (unsigned)__cvta_generic_to_shared(&s_src[warp][lane]);
-#pragma unroll 2
     for (int r = 0; r < nrows; ++r) {
-      const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+      int ry = y0 - 3 + r;
+      ry = ry < 0 ? -ry : ry;
+      ry = ry >= h ? 2 * h - 2 - ry : ry;
+      const uint8_t* row = img + (size_t)ry * pitch;
       const unsigned dst = sa + r * (kBlurSrcWords * 4);
-      if (fa) {
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(row + xa));
-      } else {
-        const unsigned va = (unsigned)__ldg(row + ca[0]) | ((unsigned)__ldg(row + ca[1]) << 8) |
-                            ((unsigned)__ldg(row + ca[2]) << 16) | ((unsigned)__ldg(row + ca[3]) << 24);
-        asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst), "r"(va));
-      }
-      if (has_b) {
-        if (fb) {
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 128), "l"(row + xb));
-        } else {
-          const unsigned vb = (unsigned)__ldg(row + cb[0]) | ((unsigned)__ldg(row + cb[1]) << 8) |
-                              ((unsigned)__ldg(row + cb[2]) << 16) | ((unsigned)__ldg(row + cb[3]) << 24);
-          asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(dst + 128), "r"(vb));
-        }
-      }
+      if (fa) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(row + xa));
+      if (fb) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 128), "l"(row + xb));
     }
     asm volatile("cp.async.commit_group;\n" ::);
+    if (__any_sync(0xFFFFFFFFu, slow_a || slow_b)) {
+      int ca[4], cb[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        ca[k] = reflect101(xa + k, w);
+        cb[k] = reflect101(xb + k, w);
+      }
+      for (int r = 0; r < nrows; ++r) {
+        const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+        if (slow_a)
+          s_src[warp][r * kBlurSrcWords + lane] = (unsigned)__ldg(row + ca[0]) | ((unsigned)__ldg(row + ca[1]) << 8) |
+                                                  ((unsigned)__ldg(row + ca[2]) << 16) |
+                                                  ((unsigned)__ldg(row + ca[3]) << 24);
+        if (slow_b)
+          s_src[warp][r * kBlurSrcWords + 32 + lane] = (unsigned)__ldg(row + cb[0]) | ((unsigned)__ldg(row + cb[1]) << 8) |
+                                                       ((unsigned)__ldg(row + cb[2]) << 16) |
+                                                       ((unsigned)__ldg(row + cb[3]) << 24);
+      }
+    }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
   }
   __syncwarp();

@@ -11,7 +11,7 @@ constexpr int kFastTileH = 30;
 constexpr int kBlurTileW = 128;  // one warp blurs a 128 x 32 tile
 constexpr int kBlurTileH = 32;
 constexpr int kResizeTileW = 128;
-constexpr int kResizeTileH = 16;
+constexpr int kResizeTileH = 32;
 
 // candidate word: score << 24 | y << 12 | x   (level coordinates, < 4096)
 __host__ __device__ inline uint32_t pack_cand(int x, int y, int score) {
