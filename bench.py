@@ -192,7 +192,7 @@ def run_ours(args, rank, world, local_rank):
     # every rank owns an independent sequence (canvas seed differs): weak scaling, no collective
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
-                          ratio=RATIO, cross_check=True)
+                          ratio=RATIO, cross_check=True, overlap=args.overlap)
     frames_pinned = torch.from_numpy(frames).pin_memory()
     frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
     frames_dev[:, :, :W_IMG].copy_(frames_pinned)
@@ -341,6 +341,8 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=100, help="frames of the sequence timed for cpu_baseline")
     ap.add_argument("--ref-frames", type=int, default=60, help="frames per step of the reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--overlap", action="store_true",
+                    help="run matching on a second stream (about +2 %% frames/s, but per-stage event times then overlap)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
