@@ -62,7 +62,7 @@ struct ResizeArgs {
   int sw, sh, spitch, dw, dh, dpitch;
   const uint32_t* xtab;  // [dw]  ofs << 16 | c1
   const uint32_t* ytab;  // [dh]
-  int src_aligned4;
+  int src_align;       // 16, 4 or 1: common alignment of the source base, pitch and frame stride
   int smem_w, smem_h;  // staged source region (bytes, rows)
 };
 

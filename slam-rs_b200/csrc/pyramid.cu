@@ -5,28 +5,66 @@
 //   H = c0x*p[ofs] + c1x*p[ofs+1];  out = (c0y*H0 + c1y*H1 + 32768) >> 16, weights sum to 256.
 // The per-axis (ofs, c1) tables are computed on the host in double (detector.cu) exactly as OpenCV
 // does.  One launch per level over the whole batch.  A block of 128 threads owns a 128 x 32 output tile:
-//   pass 1 (horizontal): thread = output column; it walks down the ~40 source rows the tile touches and
-//           writes H = c0x*p[ofs] + c1x*p[ofs+1] (<= 65280) to shared memory - each source row is
-//           interpolated once, the two byte loads of a warp fall into one or two 32-byte sectors;
-//   pass 2 (vertical): thread = 4 adjacent columns x 8 rows; two LDS.128 of H, 8 IMAD, one 32-bit store.
-// HBM-bound by design (reads px(l-1), writes px(l)); ~15 instructions per output pixel.
+//   stage : the source footprint (<= 42 rows x 192 bytes) goes global -> shared with cp.async (16-byte
+//           chunks when the plane is 16-byte aligned, else 4-byte, else byte loads);
+//   pass 1: thread = output column; it walks down the source rows and writes
+//           H = c0x*p[ofs] + c1x*p[ofs+1] (<= 65280) to shared memory: each source row is interpolated
+//           once, 2 LDS.U8 + 2 IMAD + 1 STS per value with immediate offsets;
+//   pass 2: thread = 4 adjacent columns x 8 rows; two LDS.128 of H, 8 IMAD, 3 PRMT, one 32-bit store.
+// HBM-bound by design (reads px(l-1), writes px(l)).
 #include "detector.cuh"
 
 namespace orbx {
 
 constexpr int kResizeThreads = 128;
+constexpr int kResizeSrcPitch = 192;  // bytes per staged source row (128 * 1.2 + 2 + 15 alignment slack <= 176)
+constexpr int kResizeMaxRows = 44;    // source rows per tile (32 * 1.2 + 2 <= 41)
 
 __global__ void __launch_bounds__(kResizeThreads) resize_exact_kernel(ResizeArgs a) {
-  extern __shared__ __align__(16) uint32_t s_h[];  // [source rows of the tile][128]
+  __shared__ __align__(16) uint8_t s_src[kResizeMaxRows * kResizeSrcPitch];
+  __shared__ __align__(16) uint32_t s_h[kResizeMaxRows * kResizeTileW];
   const int frame = blockIdx.z;
   const int ox0 = blockIdx.x * kResizeTileW;
   const int oy0 = blockIdx.y * kResizeTileH;
+  const int ox1 = min(ox0 + kResizeTileW, a.dw) - 1;
   const int oy1 = min(oy0 + kResizeTileH, a.dh) - 1;
+  const int sx0 = (int)(__ldg(a.xtab + ox0) >> 16);
+  const int sx1 = min((int)(__ldg(a.xtab + ox1) >> 16) + 1, a.sw - 1);
   const int sy0 = (int)(__ldg(a.ytab + oy0) >> 16);
   const int sy1 = min((int)(__ldg(a.ytab + oy1) >> 16) + 1, a.sh - 1);
   const int rows = sy1 - sy0 + 1;
-  const uint8_t* src = a.src + (size_t)frame * a.src_stride + (size_t)sy0 * a.spitch;
+  const int bx = sx0 & ~15;          // staging origin
+  const int cols = sx1 - bx + 1;     // bytes needed per row (<= kResizeSrcPitch, checked on the host)
+  const uint8_t* src = a.src + (size_t)frame * a.src_stride + (size_t)sy0 * a.spitch + bx;
   const int tid = threadIdx.x;
+
+  // stage
+  {
+    const unsigned sbase = (unsigned)__cvta_generic_to_shared(s_src);
+    if (a.src_align >= 16) {
+      const int cpr = (cols + 15) >> 4;
+      for (int i = tid; i < cpr * rows; i += kResizeThreads) {
+        const int r = i / cpr, c = i - r * cpr;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sbase + r * kResizeSrcPitch + c * 16),
+                     "l"(src + (size_t)r * a.spitch + c * 16));
+      }
+    } else if (a.src_align >= 4) {
+      const int cpr = (cols + 3) >> 2;
+      for (int i = tid; i < cpr * rows; i += kResizeThreads) {
+        const int r = i / cpr, c = i - r * cpr;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sbase + r * kResizeSrcPitch + c * 4),
+                     "l"(src + (size_t)r * a.spitch + c * 4));
+      }
+    } else {
+      for (int i = tid; i < cols * rows; i += kResizeThreads) {
+        const int r = i / cols, c = i - r * cols;
+        s_src[r * kResizeSrcPitch + c] = __ldg(src + (size_t)r * a.spitch + c);
+      }
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+  }
+  __syncthreads();
 
   // pass 1
   {
@@ -34,22 +72,18 @@ __global__ void __launch_bounds__(kResizeThreads) resize_exact_kernel(ResizeArgs
     const uint32_t xt = __ldg(a.xtab + x);
     const int xo = (int)(xt >> 16);
     const int c1x = (int)(xt & 0xFFFF), c0x = 256 - c1x;
-    const uint8_t* p0 = src + xo;
-    const uint8_t* p1 = src + min(xo + 1, a.sw - 1);
-    const int sp = a.spitch;
+    const uint8_t* p0 = s_src + (xo - bx);
+    const uint8_t* p1 = s_src + (min(xo + 1, a.sw - 1) - bx);
+    uint32_t* hp = s_h + tid;
     int r = 0;
-    for (; r + 4 <= rows; r += 4) {
-      int v0[4], v1[4];
+    for (; r + 8 <= rows; r += 8) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        v0[u] = __ldg(p0 + (size_t)(r + u) * sp);
-        v1[u] = __ldg(p1 + (size_t)(r + u) * sp);
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) s_h[(r + u) * kResizeTileW + tid] = (uint32_t)(c0x * v0[u] + c1x * v1[u]);
+      for (int u = 0; u < 8; ++u)
+        hp[(r + u) * kResizeTileW] =
+            (uint32_t)(c0x * (int)p0[(r + u) * kResizeSrcPitch] + c1x * (int)p1[(r + u) * kResizeSrcPitch]);
     }
     for (; r < rows; ++r)
-      s_h[r * kResizeTileW + tid] = (uint32_t)(c0x * (int)__ldg(p0 + (size_t)r * sp) + c1x * (int)__ldg(p1 + (size_t)r * sp));
+      hp[r * kResizeTileW] = (uint32_t)(c0x * (int)p0[r * kResizeSrcPitch] + c1x * (int)p1[r * kResizeSrcPitch]);
   }
   __syncthreads();
 
@@ -67,23 +101,25 @@ __global__ void __launch_bounds__(kResizeThreads) resize_exact_kernel(ResizeArgs
     const int c1y = (int)(yt & 0xFFFF), c0y = 256 - c1y;
     const uint4 h0 = *reinterpret_cast<const uint4*>(s_h + (yo - sy0) * kResizeTileW + cg * 4);
     const uint4 h1 = *reinterpret_cast<const uint4*>(s_h + (min(yo + 1, a.sh - 1) - sy0) * kResizeTileW + cg * 4);
-    const uint32_t v0 = (uint32_t)(c0y * (int)h0.x + c1y * (int)h1.x + 32768) >> 16;  // <= 255 by construction
-    const uint32_t v1 = (uint32_t)(c0y * (int)h0.y + c1y * (int)h1.y + 32768) >> 16;
-    const uint32_t v2 = (uint32_t)(c0y * (int)h0.z + c1y * (int)h1.z + 32768) >> 16;
-    const uint32_t v3 = (uint32_t)(c0y * (int)h0.w + c1y * (int)h1.w + 32768) >> 16;
+    // (c0y*H0 + c1y*H1 + 32768) >> 16 is <= 255 by construction: the result is byte 2 of the sum
+    const uint32_t v0 = (uint32_t)(c0y * (int)h0.x + c1y * (int)h1.x + 32768);
+    const uint32_t v1 = (uint32_t)(c0y * (int)h0.y + c1y * (int)h1.y + 32768);
+    const uint32_t v2 = (uint32_t)(c0y * (int)h0.z + c1y * (int)h1.z + 32768);
+    const uint32_t v3 = (uint32_t)(c0y * (int)h0.w + c1y * (int)h1.w + 32768);
     // dpitch is a multiple of 128, so the whole word is ours even when it runs past dw
-    *reinterpret_cast<uint32_t*>(dst + (size_t)y * a.dpitch) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+    *reinterpret_cast<uint32_t*>(dst + (size_t)y * a.dpitch) =
+        __byte_perm(__byte_perm(v0, v1, 0x0062), __byte_perm(v2, v3, 0x0062), 0x5410);
   }
 }
 
 int launch_resize(const ResizeArgs& a, int batch, cudaStream_t s) {
-  dim3 grid(div_up(a.dw, kResizeTileW), div_up(a.dh, kResizeTileH), batch);
-  dim3 block(kResizeThreads);
-  const size_t smem = (size_t)a.smem_h * kResizeTileW * sizeof(uint32_t);
-  if (smem > 48 * 1024) {
-    cudaFuncSetAttribute(resize_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (a.smem_w + 16 > kResizeSrcPitch || a.smem_h > kResizeMaxRows) {
+    set_error("orbx resize: source footprint %d x %d of a tile exceeds the staged %d x %d", a.smem_w, a.smem_h,
+              kResizeSrcPitch, kResizeMaxRows);
+    return ORBX_E_BADARG;
   }
-  resize_exact_kernel<<<grid, block, smem, s>>>(a);
+  dim3 grid(div_up(a.dw, kResizeTileW), div_up(a.dh, kResizeTileH), batch);
+  resize_exact_kernel<<<grid, kResizeThreads, 0, s>>>(a);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

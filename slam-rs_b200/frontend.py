@@ -51,6 +51,7 @@ class SequenceFrontEnd:
         # staging for the host path
         self.frames_dev = torch.zeros((T, self.h, self.pitch), dtype=u8, device=self.dev)
         self.copy_stream = torch.cuda.Stream(device=self.dev)
+        self.d2h_stream = torch.cuda.Stream(device=self.dev)
         # liborbx runs on one explicit (non-default) stream; callers' streams are joined with events
         self.stream = torch.cuda.Stream(device=self.dev)
         # overlap=True puts matching on its own stream (ordered by events) so the Hamming kernel of chunk i
@@ -107,12 +108,13 @@ class SequenceFrontEnd:
     def run_host(self, frames_pinned, out):
         """End-to-end pass over HOST frames (pinned uint8 [T, h, w]) into the pinned host buffers of
         ``out`` (see alloc_host_outputs).  H2D copies run chunk-wise on a copy stream and overlap the
-        kernels of the previous chunk; results come back with one D2H copy per array at the end."""
+        kernels of the previous chunk; each chunk's results go back on a third stream while the next chunk computes."""
         T = int(frames_pinned.shape[0])
         cur = torch.cuda.current_stream(self.dev)
         self.stream.wait_stream(cur)
         self.mstream.wait_stream(cur)
         self.copy_stream.wait_stream(cur)
+        self.d2h_stream.wait_stream(cur)
         events = []
         with torch.cuda.stream(self.copy_stream):
             for a in range(0, T, self.chunk):
@@ -127,13 +129,17 @@ class SequenceFrontEnd:
             self.extract(self.frames_dev, a, b)
             self.mstream.wait_stream(self.stream)
             self.match(a, b)
+            # results of this chunk go back on the D2H stream while the next chunk computes
+            self.d2h_stream.wait_stream(self.mstream)
+            with torch.cuda.stream(self.d2h_stream):
+                out["n"][a:b].copy_(self.n[a:b], non_blocking=True)
+                out["kps"][a:b].copy_(self.kps[a:b], non_blocking=True)
+                out["desc"][a:b].copy_(self.desc[a:b], non_blocking=True)
+                out["good"][a:b].copy_(self.good[a:b], non_blocking=True)
+                out["n_good"][a:b].copy_(self.n_good[a:b], non_blocking=True)
         cur.wait_stream(self.stream)
         cur.wait_stream(self.mstream)
-        out["n"][:T].copy_(self.n[:T], non_blocking=True)
-        out["kps"][:T].copy_(self.kps[:T], non_blocking=True)
-        out["desc"][:T].copy_(self.desc[:T], non_blocking=True)
-        out["good"][:T].copy_(self.good[:T], non_blocking=True)
-        out["n_good"][:T].copy_(self.n_good[:T], non_blocking=True)
+        cur.wait_stream(self.d2h_stream)
         return T
 
     def alloc_host_outputs(self):
