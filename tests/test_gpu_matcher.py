@@ -191,3 +191,38 @@ def test_sequence_front_end_matches_per_frame_api(orbx):
         n = int(out["n"][t])
         assert np.array_equal(out["desc"][t, :n].numpy(), per[t][1])
     assert np.array_equal(out["n_good"][1:T].numpy(), fe.n_good[1:T].cpu().numpy())
+
+
+def test_map_to_frame_matcher_class(orbx):
+    """slam_rs_b200.mapmatch.MapToFrameMatcher at world == 1 (the multi-rank slicing/gather logic is covered
+    on CPU by tests/test_abi_cpu.py::test_query_sharding_world2_gloo): both orientations vs the C oracle,
+    plus a hand-sliced query range to check the global query_idx offset."""
+    import torch
+    from slam_rs_b200.mapmatch import MapToFrameMatcher
+    from slam_rs_b200.sharding import query_slice
+    mp, fr = synth.map_and_frame_descriptors(70000, 601, f=2)
+    mm = MapToFrameMatcher(device=0)
+    assert mm.set_train(mp) == len(mp)
+    rec, cnt = mm.knn2(torch.from_numpy(fr).cuda())
+    torch.cuda.synchronize()
+    knn = rec.cpu().numpy().view(orbx.DMATCH_DTYPE).reshape(len(fr), 2)
+    idx, dist, c = c_oracle.knn(fr, mp, 2)
+    check_knn(knn, cnt.cpu().numpy(), idx, dist, c)
+    # a rank-1-of-2 style slice: records must carry global query indices
+    mm.rank, mm.world = 1, 2
+    lo, hi = query_slice(len(fr), 1, 2)
+    mm_gather = mm._gather
+    mm._gather = lambda part, total: part          # no process group here: look at the local part only
+    rec1, cnt1 = mm.knn2(torch.from_numpy(fr).cuda(), replicate_query=False)
+    torch.cuda.synchronize()
+    part = rec1.cpu().numpy().view(orbx.DMATCH_DTYPE).reshape(hi - lo, 2)
+    check_knn(part, cnt1.cpu().numpy(), idx[lo:hi], dist[lo:hi], c[lo:hi], q0=lo)
+    mm.rank, mm.world, mm._gather = 0, 1, mm_gather
+    # reference orientation (map.rs:107-108): query = map, train = frame, k = 1 + filter_good_matches(2.0)
+    good = mm.match_train_as_query(torch.from_numpy(fr).cuda(), 2.0)
+    ref = R.filter_good_matches(R.match_k1(mp, fr), 2.0) if len(mp) <= 5000 else None
+    i1, d1, _ = c_oracle.knn(mp, fr, 1)
+    thr = max(2.0 * float(d1.min()), 30.0)
+    keep = np.nonzero(d1[:, 0] < thr)[0]
+    assert np.array_equal(good["query_idx"], keep) and np.array_equal(good["train_idx"], i1[keep, 0])
+    assert np.array_equal(good["distance"], d1[keep, 0].astype(np.float32))
