@@ -155,37 +155,45 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   s_hist[tid] = 0;
   if (tid == 0) s_n = 0;
 
-  // stage the 72 x 38 footprint, widened to the two 16x2 copies, straight from global memory
-  {
+  // stage the 72 x 38 footprint, widened to the two 16x2 copies, straight from global memory:
+  // thread -> tile word column c = tid % 18 (fixed), rows tid/18, +14, +28
+  if (tid < 252) {
     const bool al = L.aligned4 != 0;
+    const int c = tid % 18, r0 = tid / 18;
     const int sh = 8 * (gx0 & 3);
     const int ga = gx0 & ~3;
+    const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
+    const int gx = gx0 + 4 * c;
+    const int b0 = min(gx, Lw - 1), b1 = min(gx + 1, Lw - 1), b2 = min(gx + 2, Lw - 1), b3 = min(gx + 3, Lw - 1),
+              b4 = min(gx + 4, Lw - 1);
+    unsigned w[3], nx[3];
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
-      const int i = tid + it * 256;
-      if (i < 18 * src_rows) {
-        const int r = i / 18, c = i - r * 18;
-        const int gy = min(gy0 + r, Lh - 1);
-        const uint8_t* p = img + (size_t)gy * pitch;
-        unsigned w, nx;  // w = pixels 4c..4c+3 of the tile row, nx byte 0 = pixel 4c+4
+      const int r = r0 + 14 * it;
+      if (r < src_rows) {
+        const uint8_t* p = img + (size_t)min(gy0 + r, Lh - 1) * pitch;
         if (al) {
-          const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
           const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
           const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
-          w = __funnelshift_r(w0, w1, sh);
-          nx = w1 >> sh;
+          w[it] = __funnelshift_r(w0, w1, sh);  // pixels 4c..4c+3 of the tile row
+          nx[it] = w1 >> sh;                    // byte 0 = pixel 4c+4
         } else {
-          const int gx = gx0 + 4 * c;
-          w = (unsigned)__ldg(p + min(gx, Lw - 1)) | ((unsigned)__ldg(p + min(gx + 1, Lw - 1)) << 8) |
-              ((unsigned)__ldg(p + min(gx + 2, Lw - 1)) << 16) | ((unsigned)__ldg(p + min(gx + 3, Lw - 1)) << 24);
-          nx = __ldg(p + min(gx + 4, Lw - 1));
+          w[it] = (unsigned)__ldg(p + b0) | ((unsigned)__ldg(p + b1) << 8) | ((unsigned)__ldg(p + b2) << 16) |
+                  ((unsigned)__ldg(p + b3) << 24);
+          nx[it] = __ldg(p + b4);
         }
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+      const int r = r0 + 14 * it;
+      if (r < src_rows) {
         unsigned* e = s_E + r * kPairPitch + 2 * c;
         unsigned* o = s_O + r * kPairPitch + 2 * c;
-        e[0] = __byte_perm(w, 0u, 0x4140);                 // (p0, p1)
-        e[1] = __byte_perm(w, 0u, 0x4342);                 // (p2, p3)
-        o[0] = __byte_perm(w, 0u, 0x4241);                 // (p1, p2)
-        o[1] = __byte_perm(w, nx, 0x4443) & 0x00FF00FFu;   // (p3, p4)
+        e[0] = __byte_perm(w[it], 0u, 0x4140);                    // (p0, p1)
+        e[1] = __byte_perm(w[it], 0u, 0x4342);                    // (p2, p3)
+        o[0] = __byte_perm(w[it], 0u, 0x4241);                    // (p1, p2)
+        o[1] = __byte_perm(w[it], nx[it], 0x4443) & 0x00FF00FFu;  // (p3, p4)
       }
     }
   }
@@ -213,6 +221,12 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   // strict 3x3 NMS in the same 16x2 form: horizontal 3-max of the rows above and below plus the two
   // side neighbours, then one compare per pixel; border cull; emit score = s' + t - 1
   const int sadd = g.fast_threshold - 1;
+  unsigned colmask = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int col = 4 * c4 + j;
+    if (col >= 1 && col <= kFastTileW && gxs + j < Lw - kEdge) colmask |= 1u << j;
+  }
 #pragma unroll 1
   for (int k = 0; k < 2; ++k) {
     const int cy = (tid >> 4) + k * 16;
@@ -240,17 +254,22 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
       m0 = a.y;
       m1 = b.x;
     }
-    // per pixel j: column 4*c4 + j of the score region; interior columns are 1..62
+    // keep mask of the 4 pixels (column 4*c4 + j of the score region; interior columns are 1..62)
     const int sv[4] = {(int)(m0 & 0xFFFF), (int)(m0 >> 16), (int)(m1 & 0xFFFF), (int)(m1 >> 16)};
     const int nv[4] = {(int)(nb0 & 0xFFFF), (int)(nb0 >> 16), (int)(nb1 & 0xFFFF), (int)(nb1 >> 16)};
+    unsigned keep = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int col = 4 * c4 + j, gx = gxs + j;
-      if (sv[j] > nv[j] && col >= 1 && col <= kFastTileW && gx < Lw - kEdge) {
-        const uint32_t slot = atomicAdd(&s_n, 1u);
-        s_list[slot] = pack_cand(gx, gy, sv[j] + sadd);
-        atomicAdd(&s_hist[sv[j] + sadd], 1u);
-      }
+    for (int j = 0; j < 4; ++j) keep |= (sv[j] > nv[j] ? 1u : 0u) << j;
+    keep &= colmask;
+    // survivors are rare (~3 % of pixels): one shared-memory slot reservation per thread that has any
+    if (keep) {
+      uint32_t slot = atomicAdd(&s_n, (uint32_t)__popc(keep));
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (keep & (1u << j)) {
+          s_list[slot++] = pack_cand(gxs + j, gy, sv[j] + sadd);
+          atomicAdd(&s_hist[sv[j] + sadd], 1u);
+        }
     }
   }
   __syncthreads();
