@@ -90,6 +90,13 @@ int orbx_detect_and_compute(orbx_detector* d, const uint8_t* img, int w, int h, 
 int orbx_detect_and_compute_batch(orbx_detector* d, const uint8_t* imgs, int w, int h, size_t pitch,
                                   size_t frame_stride, int batch, orbx_keypoint* kps, uint8_t* desc,
                                   int cap_per_frame, int* n_per_frame);
+/* the same for interleaved 8UC3 BGR frames (pitch in bytes >= 3*w): the frame ingest in front of S1.  Replaces
+ * imgproc::cvt_color(COLOR_BGR2GRAY) at examples/visual_odometry.rs:93-99 / src/main.rs:43-49 and the implicit
+ * conversion cv::ORB applies to non-8UC1 input (detector.rs:22,32): gray = (B*3735 + G*19235 + R*9798 + 16384) >> 15,
+ * computed on the device straight into the pitched level-0 plane. */
+int orbx_detect_and_compute_batch_bgr(orbx_detector* d, const uint8_t* imgs, int w, int h, size_t pitch,
+                                      size_t frame_stride, int batch, orbx_keypoint* kps, uint8_t* desc,
+                                      int cap_per_frame, int* n_per_frame);
 int orbx_detector_sync(orbx_detector* d);
 /* run on a caller-owned CUDA stream (cudaStream_t as void*); NULL restores the handle's own stream */
 int orbx_detector_set_stream(orbx_detector* d, void* stream);

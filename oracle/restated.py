@@ -261,6 +261,15 @@ def describe(B, cx, cy, angle_deg, pat=PATTERN):
     return out
 
 
+# ---------------------------------------------------------------- ingest: BGR -> gray in front of S1
+def bgr_to_gray(img):
+    """cv::cvtColor(COLOR_BGR2GRAY) for 8UC3, as called at /root/reference/examples/visual_odometry.rs:93-99 and
+    src/main.rs:43-49 (and implicitly by cv::ORB for non-8UC1 input, src/feature/detector.rs:22,32).  15-bit fixed
+    point: (B*3735 + G*19235 + R*9798 + 16384) >> 15.  Pinned against cv2 in tests/test_oracle_cpu.py."""
+    a = np.asarray(img).astype(np.int64)
+    return ((a[..., 0] * 3735 + a[..., 1] * 19235 + a[..., 2] * 9798 + 16384) >> 15).astype(np.uint8)
+
+
 # ---------------------------------------------------------------- S1–S9 end to end
 def orb_detect_and_compute(img, nfeatures=500, with_desc=True, return_stages=False):
     """Restated cv::ORB_Impl::detectAndCompute.  Returns a dict of arrays in level-major order;

@@ -21,6 +21,7 @@ extern "C" {
     pub fn orbx_detect(d: *mut orbx_detector, img: *const u8, w: c_int, h: c_int, pitch: usize, kps: *mut orbx_keypoint, cap: c_int, n: *mut c_int) -> c_int;
     pub fn orbx_detect_and_compute(d: *mut orbx_detector, img: *const u8, w: c_int, h: c_int, pitch: usize, kps: *mut orbx_keypoint, desc: *mut u8, cap: c_int, n: *mut c_int) -> c_int;
     pub fn orbx_detect_and_compute_batch(d: *mut orbx_detector, imgs: *const u8, w: c_int, h: c_int, pitch: usize, frame_stride: usize, batch: c_int, kps: *mut orbx_keypoint, desc: *mut u8, cap: c_int, n: *mut c_int) -> c_int;
+    pub fn orbx_detect_and_compute_batch_bgr(d: *mut orbx_detector, imgs: *const u8, w: c_int, h: c_int, pitch: usize, frame_stride: usize, batch: c_int, kps: *mut orbx_keypoint, desc: *mut u8, cap: c_int, n: *mut c_int) -> c_int;
     pub fn orbx_matcher_create(device: c_int, cross_check: c_int, out: *mut *mut orbx_matcher) -> c_int;
     pub fn orbx_matcher_destroy(m: *mut orbx_matcher);
     pub fn orbx_match(m: *mut orbx_matcher, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n: *mut c_int) -> c_int;

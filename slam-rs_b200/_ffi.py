@@ -53,6 +53,7 @@ def _load():
         "orbx_detect": (i, [vp, vp, i, i, sz, vp, i, vp]),
         "orbx_detect_and_compute": (i, [vp, vp, i, i, sz, vp, vp, i, vp]),
         "orbx_detect_and_compute_batch": (i, [vp, vp, i, i, sz, sz, i, vp, vp, i, vp]),
+        "orbx_detect_and_compute_batch_bgr": (i, [vp, vp, i, i, sz, sz, i, vp, vp, i, vp]),
         "orbx_detector_sync": (i, [vp]),
         "orbx_detector_set_stream": (i, [vp, vp]),
         "orbx_detector_level_info": (i, [vp, i, i, ip, ip, C.POINTER(sz), C.POINTER(sz), C.POINTER(vp)]),

@@ -34,6 +34,8 @@ struct orbx_detector {
   orbx_keypoint* out_kps = nullptr;
   uint8_t* out_desc = nullptr;
   int* out_n = nullptr;  // [max_batch] counts + [1] flags
+  uint8_t* bgr_stage = nullptr;  // host BGR frames land here before the ingest kernel (allocated on first use)
+  size_t bgr_stage_bytes = 0;
   size_t pyr_bytes = 0, cand_words = 0, sel_words = 0, counter_words = 0, table_words = 0;
   int out_cap = 0, sort_cap = 0;
   // geometry of the current image size
@@ -234,6 +236,7 @@ void orbx_detector_destroy(orbx_detector* d) {
   cudaFree(d->out_kps);
   cudaFree(d->out_desc);
   cudaFree(d->out_n);
+  cudaFree(d->bgr_stage);
   if (d->own_stream) cudaStreamDestroy(d->own_stream);
   delete d;
 }

@@ -36,10 +36,12 @@ def _as_gray(image):
     if img.ndim == 3:  # OpenCV gray-converts non-8UC1 input internally
         if img.shape[2] == 1:
             img = img[:, :, 0]
+        elif img.shape[2] == 3 and img.dtype == np.uint8:
+            return img  # BGR: converted on the device by the ingest kernel (orbx_detect_and_compute_batch_bgr)
         else:
-            raise ValueError("OrbDetector expects an 8-bit single-channel image")
+            raise ValueError("OrbDetector expects an 8-bit single-channel or BGR image")
     if img.dtype != np.uint8 or img.ndim != 2:
-        raise ValueError("OrbDetector expects an 8-bit single-channel image")
+        raise ValueError("OrbDetector expects an 8-bit single-channel or BGR image")
     return img
 
 
@@ -81,13 +83,18 @@ class OrbDetector:
     # ------------------------------------------------------------------ host (numpy) interface
     def _run(self, image, with_desc, cap=None):
         img = np.ascontiguousarray(_as_gray(image))
-        h, w = img.shape
+        h, w = img.shape[:2]
         cap = int(cap or self.default_cap)
         while True:
             kps = np.zeros(cap, KEYPOINT_DTYPE)
             desc = np.zeros((cap, 32), np.uint8) if with_desc else None
             n = C.c_int(0)
-            if with_desc:
+            if img.ndim == 3:
+                # 8UC3: cv::ORB gray-converts such input itself (detector.rs:22,32); here the ingest kernel does
+                rc = lib.orbx_detect_and_compute_batch_bgr(self._h, _ptr(img), w, h, img.strides[0],
+                                                           img.strides[0] * h, 1, _ptr(kps), _ptr(desc), cap,
+                                                           C.byref(n))
+            elif with_desc:
                 rc = lib.orbx_detect_and_compute(self._h, _ptr(img), w, h, img.strides[0], _ptr(kps), _ptr(desc),
                                                  cap, C.byref(n))
             else:
@@ -121,7 +128,29 @@ class OrbDetector:
                                                 _ptr(kps), _ptr(desc), cap, _ptr(n)))
         return [(kps[i, :n[i]], desc[i, :n[i]]) for i in range(b)]
 
+    def detect_and_compute_batch_bgr(self, images, cap=None):
+        """Batch of equally sized host BGR frames [B, H, W, 3] -> list of (keypoints, descriptors)."""
+        imgs = np.ascontiguousarray(images)
+        if imgs.dtype != np.uint8 or imgs.ndim != 4 or imgs.shape[3] != 3:
+            raise ValueError("expected uint8 [B, H, W, 3]")
+        b, h, w, _ = imgs.shape
+        cap = int(cap or self.default_cap)
+        kps = np.zeros((b, cap), KEYPOINT_DTYPE)
+        desc = np.zeros((b, cap, 32), np.uint8)
+        n = np.zeros(b, np.int32)
+        check(lib.orbx_detect_and_compute_batch_bgr(self._h, _ptr(imgs), w, h, imgs.strides[1], imgs.strides[0], b,
+                                                    _ptr(kps), _ptr(desc), cap, _ptr(n)))
+        return [(kps[i, :n[i]], desc[i, :n[i]]) for i in range(b)]
+
     # ------------------------------------------------------------------ device interface (torch tensors)
+    def detect_and_compute_device_bgr(self, imgs, kps, desc, n, width=None):
+        """Asynchronous batch over device-resident BGR frames: uint8 CUDA tensor [B, H, W(+pad), 3]."""
+        b, h = int(imgs.shape[0]), int(imgs.shape[1])
+        width = int(width or imgs.shape[2])
+        check(lib.orbx_detect_and_compute_batch_bgr(self._h, _ptr(imgs), width, h, int(imgs.stride(1)),
+                                                    int(imgs.stride(0)), b, _ptr(kps), _ptr(desc), int(kps.shape[1]),
+                                                    _ptr(n)))
+
     def detect_and_compute_device(self, imgs, kps, desc, n, pitch=None, frame_stride=None, width=None):
         """Asynchronous batch over device-resident frames.  imgs: uint8 CUDA tensor [B, H, pitch];
         kps: uint8 CUDA tensor [B, cap, 28]; desc: uint8 CUDA [B, cap, 32] or None; n: int32 CUDA [B]."""

@@ -178,3 +178,36 @@ def test_determinism(orbx):
     for _ in range(3):
         b = det.detect_and_compute(img)
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_bgr_ingest(orbx):
+    """Frame ingest in front of S1 (visual_odometry.rs:93-99): 8UC3 BGR input is gray-converted on the device with
+    OpenCV's 15-bit fixed-point weights; level 0 and all results must equal the run on the oracle's gray image."""
+    import torch
+    from tests.test_oracle_cpu import bgr_frame
+    for h, w, nf in ((200, 333, 400), (240, 320, 300)):            # odd width: unaligned 3*w rows
+        bgr = bgr_frame(h, w, 60)
+        gray = R.bgr_to_gray(bgr)
+        det = orbx.OrbDetector(nf, max_width=w, max_height=h, max_batch=3)
+        k1, d1 = det.detect_and_compute(bgr)
+        assert np.array_equal(det.level(0), gray)
+        k2, d2 = det.detect_and_compute(gray)
+        assert np.array_equal(k1, k2) and np.array_equal(d1, d2) and len(k1) > 50
+        assert np.array_equal(det.detect(bgr), k2)
+        batch = np.stack([bgr, bgr[::-1].copy(), bgr[:, ::-1].copy()])
+        host = det.detect_and_compute_batch_bgr(batch)
+        for i in range(3):
+            kg, dg = det.detect_and_compute(R.bgr_to_gray(batch[i]))
+            assert np.array_equal(host[i][0], kg) and np.array_equal(host[i][1], dg)
+        cap = 640
+        dev = torch.from_numpy(batch).cuda()
+        kps = torch.zeros((3, cap, 28), dtype=torch.uint8, device="cuda")
+        desc = torch.zeros((3, cap, 32), dtype=torch.uint8, device="cuda")
+        n = torch.zeros((3,), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        det.detect_and_compute_device_bgr(dev, kps, desc, n)
+        det.sync()
+        nn = n.cpu().numpy()
+        for i in range(3):
+            k = kps[i, :nn[i]].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+            assert np.array_equal(k, host[i][0]) and np.array_equal(desc[i, :nn[i]].cpu().numpy(), host[i][1])

@@ -128,3 +128,25 @@ def test_restated_match_vs_cv2_live():
     i2, d2, c2 = cv_ref.knn2(f, m)
     assert np.array_equal(i1, i2) and np.array_equal(d1, d2) and np.array_equal(c1, c2)
     assert np.array_equal(R.cross_check(f, m), cv_ref.match_k1(f, m, cross_check=True))
+
+
+def bgr_frame(h, w, seed):
+    """Three differently seeded textures as B, G, R planes (deterministic)."""
+    return np.stack([synth.frame(h, w, seed + 100 * c) for c in range(3)], axis=-1)
+
+
+@pytest.mark.skipif(not cv_ref.HAVE_CV2, reason="cv2 not importable")
+def test_bgr_to_gray_vs_cv2_live():
+    import cv2
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (97, 131, 3), dtype=np.uint8)
+    assert np.array_equal(R.bgr_to_gray(img), cv2.cvtColor(img, cv2.COLOR_BGR2GRAY))
+    v = np.arange(0, 256, 5, dtype=np.uint8)                       # a grid over the whole colour cube
+    cube = np.stack(np.meshgrid(v, v, v, indexing="ij"), -1).reshape(-1, 1, 3)
+    assert np.array_equal(R.bgr_to_gray(cube), cv2.cvtColor(np.ascontiguousarray(cube), cv2.COLOR_BGR2GRAY))
+    # cv::ORB on a BGR image == cv::ORB on its gray conversion (the implicit conversion the reference relies on)
+    bgr = bgr_frame(200, 260, 40)
+    orb = cv2.ORB_create(nfeatures=300)
+    k1, d1 = orb.detectAndCompute(bgr, None)
+    k2, d2 = orb.detectAndCompute(R.bgr_to_gray(bgr), None)
+    assert [k.pt for k in k1] == [k.pt for k in k2] and np.array_equal(d1, d2)
