@@ -176,6 +176,40 @@ int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const i
 int orbx_matcher_set_timing(orbx_matcher* m, int enable);
 int orbx_matcher_timing(orbx_matcher* m, float* ms, int* launches, int reset);
 
+/* ------------------------------------------------------------------ Map
+ * Device-resident replacement of the hot part of mapping::Map (src/mapping/map.rs): positions, descriptors and
+ * observation counts live in HBM; point id == slot index, handed out sequentially (map.rs:31-37).
+ * R is the 3x3 rotation in ROW-major order (nalgebra stores column-major), t the translation. */
+typedef struct orbx_map orbx_map;
+/* Map::new(intrinsics) (map.rs:21-28) with a fixed capacity (total points ever added) */
+int orbx_map_create(int device, int capacity, double fx, double fy, double cx, double cy, orbx_map** out);
+void orbx_map_destroy(orbx_map* m);
+/* Map::size (map.rs:45-47) / Map::clear (:147-150) */
+int orbx_map_size(const orbx_map* m);
+int orbx_map_clear(orbx_map* m);
+/* Map::add_points (map.rs:31-37): xyz n x 3 doubles; desc n x 32 or NULL (MapPoint::new has no descriptor);
+ * has_desc (host, n bytes) or NULL = every point has one; observations (n ints) or NULL = 1 each.
+ * xyz/desc/observations may be host or device memory.  *first_id = id of the first new point. */
+int orbx_map_add_points(orbx_map* m, const double* xyz, const uint8_t* desc, const uint8_t* has_desc,
+                        const int* observations, int n, int64_t* first_id);
+/* Map::project_point (map.rs:50-69) + the bounds test of find_matches (:90) for every slot (host outputs):
+ * xy: used x 2 (0,0 when behind the camera); vis bit0 = in front and 0<=x<4000, 0<=y<3000; bit1 = alive;
+ * bit2 = has a descriptor.  Parity hook for the tests. */
+int orbx_map_project(orbx_map* m, const double* R, const double* t, double* xy, uint8_t* vis);
+/* Map::find_matches (map.rs:72-118): cull by projection, gather the visible descriptors, k=1 Hamming search
+ * with query = map rows, train = frame rows (map.rs:107), filter_good_matches(2.0) (:108).
+ * pairs: cap x 2 ints (map_id, kp_idx) in ascending map_id (host or device); frame_desc host or device. */
+int orbx_map_find_matches(orbx_map* m, orbx_matcher* matcher, const double* R, const double* t,
+                          const uint8_t* frame_desc, int n_frame, int* pairs, int cap, int* n_pairs, int* n_visible);
+/* Map::update_observations (map.rs:121-127): pairs n x 2 as returned above (host or device) */
+int orbx_map_update_observations(orbx_map* m, const int* pairs, int n);
+/* Map::prune_outliers (map.rs:130-137): drops points with observations < 2, *removed = how many */
+int orbx_map_prune_outliers(orbx_map* m, int* removed);
+/* number of Map::stable_points (map.rs:140-145) */
+int orbx_map_stable_count(orbx_map* m, int* count);
+/* test hook: observation counts and alive flags of the first n slots (host outputs, either may be NULL) */
+int orbx_map_read_observations(orbx_map* m, int* obs, uint8_t* alive, int n);
+
 /* ------------------------------------------------------------------ misc */
 const char* orbx_last_error(void);
 const char* orbx_version(void);

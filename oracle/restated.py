@@ -385,3 +385,31 @@ def filter_good_matches(matches, ratio):
     d = matches[:, 2].astype(f32)
     thr = max(f32(f32(ratio) * d.min()), f32(30.0))
     return matches[d < thr]
+
+
+# ---------------------------------------------------------------- mapping::Map hot path
+def map_project(points, R, t, fx, fy, cx, cy):
+    """Map::project_point (/root/reference/src/mapping/map.rs:50-69) and the bounds test of find_matches (:90) for
+    an [n, 3] float64 array.  nalgebra's r * point + t accumulates the columns left to right in f64 without fused
+    multiply-adds: ((r_i0*X + r_i1*Y) + r_i2*Z) + t_i.  Returns (xy [n, 2], visible [n])."""
+    P = np.asarray(points, np.float64).reshape(-1, 3)
+    R = np.asarray(R, np.float64).reshape(3, 3)
+    t = np.asarray(t, np.float64).reshape(3)
+    cam = [((R[i, 0] * P[:, 0] + R[i, 1] * P[:, 1]) + R[i, 2] * P[:, 2]) + t[i] for i in range(3)]
+    front = cam[2] > 0.0
+    z = np.where(front, cam[2], 1.0)
+    x = np.where(front, fx * (cam[0] / z) + cx, 0.0)
+    y = np.where(front, fy * (cam[1] / z) + cy, 0.0)
+    vis = front & (x >= 0.0) & (x < 4000.0) & (y >= 0.0) & (y < 3000.0)
+    return np.stack([x, y], 1), vis
+
+
+def map_find_matches(points, descs, has_desc, alive, R, t, intr, frame_desc):
+    """Map::find_matches (map.rs:72-118): visible points with a descriptor, in ascending id; k=1 match with
+    query = map rows, train = frame rows (:107); filter_good_matches(2.0) (:108); -> [(map_id, kp_idx)]."""
+    _, vis = map_project(points, R, t, *intr)
+    ids = np.nonzero(vis & np.asarray(has_desc, bool) & np.asarray(alive, bool))[0]
+    if len(ids) == 0 or len(frame_desc) == 0:
+        return np.zeros((0, 2), np.int64)
+    good = filter_good_matches(match_k1(np.asarray(descs)[ids], frame_desc), 2.0)
+    return np.stack([ids[good[:, 0]], good[:, 1]], 1) if len(good) else np.zeros((0, 2), np.int64)

@@ -11,6 +11,7 @@ pub struct orbx_params { pub nfeatures: i32, pub scale_factor: f32, pub nlevels:
     pub first_level: i32, pub wta_k: i32, pub score_type: i32, pub patch_size: i32, pub fast_threshold: i32 }
 pub enum orbx_detector {}
 pub enum orbx_matcher {}
+pub enum orbx_map {}
 pub const ORBX_OK: c_int = 0;
 pub const ORBX_E_CAPACITY: c_int = -2;
 
@@ -28,6 +29,15 @@ extern "C" {
     pub fn orbx_knn_match2(m: *mut orbx_matcher, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n_per_q: *mut c_int) -> c_int;
     pub fn orbx_ratio_test(m: *mut orbx_matcher, knn2: *const orbx_dmatch, n_per_q: *const c_int, nq: c_int, ratio: f32, out: *mut orbx_dmatch, n: *mut c_int) -> c_int;
     pub fn orbx_filter_good_matches(m: *mut orbx_matcher, inp: *const orbx_dmatch, n: c_int, ratio: f32, out: *mut orbx_dmatch, n_out: *mut c_int) -> c_int;
+    pub fn orbx_map_create(device: c_int, capacity: c_int, fx: f64, fy: f64, cx: f64, cy: f64, out: *mut *mut orbx_map) -> c_int;
+    pub fn orbx_map_destroy(m: *mut orbx_map);
+    pub fn orbx_map_size(m: *const orbx_map) -> c_int;
+    pub fn orbx_map_clear(m: *mut orbx_map) -> c_int;
+    pub fn orbx_map_add_points(m: *mut orbx_map, xyz: *const f64, desc: *const u8, has_desc: *const u8, observations: *const c_int, n: c_int, first_id: *mut i64) -> c_int;
+    pub fn orbx_map_find_matches(m: *mut orbx_map, matcher: *mut orbx_matcher, r: *const f64, t: *const f64, frame_desc: *const u8, n_frame: c_int, pairs: *mut c_int, cap: c_int, n_pairs: *mut c_int, n_visible: *mut c_int) -> c_int;
+    pub fn orbx_map_update_observations(m: *mut orbx_map, pairs: *const c_int, n: c_int) -> c_int;
+    pub fn orbx_map_prune_outliers(m: *mut orbx_map, removed: *mut c_int) -> c_int;
+    pub fn orbx_map_stable_count(m: *mut orbx_map, count: *mut c_int) -> c_int;
     pub fn orbx_last_error() -> *const c_char;
     pub fn orbx_detector_set_stream(d: *mut orbx_detector, stream: *mut c_void) -> c_int;
 }

@@ -61,6 +61,17 @@ def _load():
         "orbx_detector_candidates": (i, [vp, i, i, vp, i, ip]),
         "orbx_detector_set_timing": (i, [vp, i]),
         "orbx_detector_timing": (i, [vp, C.POINTER(f), ip, i]),
+        "orbx_map_create": (i, [i, i, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(vp)]),
+        "orbx_map_destroy": (None, [vp]),
+        "orbx_map_size": (i, [vp]),
+        "orbx_map_clear": (i, [vp]),
+        "orbx_map_add_points": (i, [vp, vp, vp, vp, vp, i, C.POINTER(C.c_int64)]),
+        "orbx_map_project": (i, [vp, vp, vp, vp, vp]),
+        "orbx_map_find_matches": (i, [vp, vp, vp, vp, vp, i, vp, i, ip, ip]),
+        "orbx_map_update_observations": (i, [vp, vp, i]),
+        "orbx_map_prune_outliers": (i, [vp, ip]),
+        "orbx_map_stable_count": (i, [vp, ip]),
+        "orbx_map_read_observations": (i, [vp, vp, vp, i]),
         "orbx_matcher_create": (i, [i, i, C.POINTER(vp)]),
         "orbx_matcher_destroy": (None, [vp]),
         "orbx_matcher_sync": (i, [vp]),

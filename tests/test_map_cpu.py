@@ -1,0 +1,38 @@
+"""CPU: the oracle's restatement of mapping::Map's hot path (oracle/restated.py::map_project / map_find_matches)
+against the closed-form checks the reference's own tests make (/root/reference/src/mapping/map.rs:183-240)."""
+import numpy as np
+
+from oracle import restated as R, synth
+
+KITTI = (718.856, 718.856, 607.1928, 185.2157)      # CameraIntrinsics::kitti() (camera.rs:19-26)
+
+
+def test_projection_principal_point():
+    """map.rs:207-221 test_projection: (0,0,10) under identity pose projects to (cx, cy)."""
+    xy, vis = R.map_project([[0.0, 0.0, 10.0]], np.eye(3), np.zeros(3), *KITTI)
+    assert vis[0] and abs(xy[0, 0] - KITTI[2]) < 1e-6 and abs(xy[0, 1] - KITTI[3]) < 1e-6
+
+
+def test_projection_cull_rules():
+    pts = np.array([[0, 0, -1.0], [0, 0, 0.0], [1e3, 0, 1.0], [-1.0, 0, 1.0], [0, 5.0, 1.0], [0.5, 0.2, 2.0]])
+    xy, vis = R.map_project(pts, np.eye(3), np.zeros(3), *KITTI)
+    # behind / on the camera plane (map.rs:61), x >= 4000, x < 0, y >= 3000 (map.rs:90), inside
+    assert vis.tolist() == [False, False, False, False, False, True]
+
+
+def test_find_matches_semantics():
+    rng = np.random.default_rng(5)
+    mp, fr = synth.map_and_frame_descriptors(500, 60, f=3)
+    pts = np.stack([rng.uniform(-5, 5, 500), rng.uniform(-2, 2, 500), rng.uniform(-3, 30, 500)], 1)
+    has = rng.random(500) < 0.9
+    alive = np.ones(500, bool)
+    out = R.map_find_matches(pts, mp, has, alive, np.eye(3), np.zeros(3), KITTI, fr)
+    _, vis = R.map_project(pts, np.eye(3), np.zeros(3), *KITTI)
+    ids = np.nonzero(vis & has)[0]
+    assert len(out) and set(out[:, 0]) <= set(ids) and np.all(np.diff(out[:, 0]) > 0)
+    # every reported pair is the first-min train row of that map point and passes the min-distance filter
+    D = R.hamming_matrix(mp[ids], fr)
+    thr = max(2.0 * D.min(axis=1).min(), 30.0)
+    want = [(i, int(D[k].argmin())) for k, i in enumerate(ids) if D[k].min() < thr]
+    assert [tuple(r) for r in out.tolist()] == want
+    assert len(R.map_find_matches(pts, mp, has, alive, np.eye(3), np.zeros(3), KITTI, fr[:0])) == 0
