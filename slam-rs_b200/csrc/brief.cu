@@ -197,10 +197,26 @@ __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutA
     st_off[t] = (r << 16) | (i - r * kBriefWords);
   }
   const uint8_t* sp = reinterpret_cast<const uint8_t*>(s_patch[warp]);
+  // lane k < kBriefPerWarp prepares keypoint k of this warp: position word and (float)cos/sin((double)theta).
+  // The double-precision sin/cos (~150 instructions) is evaluated once per warp for all of its keypoints
+  // instead of once per keypoint by all 32 lanes.
+  uint32_t lv_mine = 0;
+  float a_mine = 0.f, b_mine = 0.f;
+  {
+    const int jm = (blockIdx.x * kBriefPerWarp + min(lane, kBriefPerWarp - 1)) * kBriefWarps + warp;
+    if (lane < kBriefPerWarp && jm < n) {
+      lv_mine = o.kp_lvl[(size_t)frame * o.lvl_cap + jm];
+      const float angle = o.kps[(size_t)frame * o.cap + jm].angle;
+      const float th = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));
+      a_mine = (float)cos((double)th);
+      b_mine = (float)sin((double)th);
+    }
+  }
   for (int it = 0; it < kBriefPerWarp; ++it) {
     const int j = (blockIdx.x * kBriefPerWarp + it) * kBriefWarps + warp;
     if (j >= n) return;
-    const uint32_t lv = o.kp_lvl[(size_t)frame * o.lvl_cap + j];
+    const uint32_t lv = __shfl_sync(0xFFFFFFFFu, lv_mine, it);
+    const float a = __shfl_sync(0xFFFFFFFFu, a_mine, it), b = __shfl_sync(0xFFFFFFFFu, b_mine, it);
     const int l = (int)(lv >> 24), cx = (int)(lv & 0xFFF), cy = (int)((lv >> 12) & 0xFFF);
     const DevLevel& L = g.lv[l];
     const int bp = L.blur_pitch;
@@ -213,9 +229,6 @@ __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutA
     for (int t = 0; t < kBriefLoads; ++t)
       if (lane + 32 * t < kBriefRows * kBriefWords)
         stg[t] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)(st_off[t] >> 16) * bp) + (st_off[t] & 0xFFFF));
-    const float angle = o.kps[(size_t)frame * o.cap + j].angle;
-    const float th = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));
-    const float a = (float)cos((double)th), b = (float)sin((double)th);
     __syncwarp();  // the previous keypoint's samples have been read
 #pragma unroll
     for (int t = 0; t < kBriefLoads; ++t)

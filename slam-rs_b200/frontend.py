@@ -115,16 +115,29 @@ class SequenceFrontEnd:
         self.mstream.wait_stream(cur)
         self.copy_stream.wait_stream(cur)
         self.d2h_stream.wait_stream(cur)
+        # chunk schedule: a short first chunk so that compute starts early, full chunks in the middle, a short
+        # last chunk so that little is left to copy back after the last kernel
+        c = self.chunk
+        bounds, a = [], 0
+        for size in (max(c // 4, 1), max(c // 2, 1)):
+            if T - a > c:
+                bounds.append((a, a + size))
+                a += size
+        while T - a > c + c // 2:
+            bounds.append((a, a + c))
+            a += c
+        if T - a > c:
+            bounds.append((a, T - c // 2))
+            a = T - c // 2
+        bounds.append((a, T))
         events = []
         with torch.cuda.stream(self.copy_stream):
-            for a in range(0, T, self.chunk):
-                b = min(a + self.chunk, T)
+            for a, b in bounds:
                 self.frames_dev[a:b, :, :self.w].copy_(frames_pinned[a:b], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
                 events.append(ev)
-        for i, a in enumerate(range(0, T, self.chunk)):
-            b = min(a + self.chunk, T)
+        for i, (a, b) in enumerate(bounds):
             self.stream.wait_event(events[i])
             self.extract(self.frames_dev, a, b)
             self.mstream.wait_stream(self.stream)
