@@ -158,42 +158,47 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   // stage the 72 x 38 footprint, widened to the two 16x2 copies, straight from global memory:
   // thread -> tile word column c = tid % 18 (fixed), rows tid/18, +14, +28
   if (tid < 252) {
-    const bool al = L.aligned4 != 0;
     const int c = tid % 18, r0 = tid / 18;
-    const int sh = 8 * (gx0 & 3);
-    const int ga = gx0 & ~3;
-    const int a0 = min(ga + c * 4, pitch - 4), a1 = min(ga + c * 4 + 4, pitch - 4);
-    const int gx = gx0 + 4 * c;
-    const int b0 = min(gx, Lw - 1), b1 = min(gx + 1, Lw - 1), b2 = min(gx + 2, Lw - 1), b3 = min(gx + 3, Lw - 1),
-              b4 = min(gx + 4, Lw - 1);
-    unsigned w[3], nx[3];
+    unsigned w[3], nx[3];  // w = pixels 4c..4c+3 of the tile row, byte 0 of nx = pixel 4c+4
+    if (L.aligned4) {
+      const int sh = 8 * (gx0 & 3);
+      const int ga = (gx0 & ~3) + c * 4;
+      const uint8_t* c0 = img + min(ga, pitch - 4);
+      const uint8_t* c1 = img + min(ga + 4, pitch - 4);
 #pragma unroll
-    for (int it = 0; it < 3; ++it) {
-      const int r = r0 + 14 * it;
-      if (r < src_rows) {
-        const uint8_t* p = img + (size_t)min(gy0 + r, Lh - 1) * pitch;
-        if (al) {
-          const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(p + a0));
-          const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(p + a1));
-          w[it] = __funnelshift_r(w0, w1, sh);  // pixels 4c..4c+3 of the tile row
-          nx[it] = w1 >> sh;                    // byte 0 = pixel 4c+4
-        } else {
+      for (int it = 0; it < 3; ++it) {
+        const int r = r0 + 14 * it;
+        if (r < src_rows) {
+          const unsigned roff = (unsigned)(min(gy0 + r, Lh - 1) * pitch);
+          const unsigned w0 = __ldg(reinterpret_cast<const unsigned*>(c0 + roff));
+          const unsigned w1 = __ldg(reinterpret_cast<const unsigned*>(c1 + roff));
+          w[it] = __funnelshift_r(w0, w1, sh);
+          nx[it] = w1 >> sh;
+        }
+      }
+    } else {
+      const int gx = gx0 + 4 * c;
+      const int b0 = min(gx, Lw - 1), b1 = min(gx + 1, Lw - 1), b2 = min(gx + 2, Lw - 1), b3 = min(gx + 3, Lw - 1),
+                b4 = min(gx + 4, Lw - 1);
+      for (int it = 0; it < 3; ++it) {
+        const int r = r0 + 14 * it;
+        if (r < src_rows) {
+          const uint8_t* p = img + (size_t)min(gy0 + r, Lh - 1) * pitch;
           w[it] = (unsigned)__ldg(p + b0) | ((unsigned)__ldg(p + b1) << 8) | ((unsigned)__ldg(p + b2) << 16) |
                   ((unsigned)__ldg(p + b3) << 24);
           nx[it] = __ldg(p + b4);
         }
       }
     }
+    unsigned* e = s_E + r0 * kPairPitch + 2 * c;
+    unsigned* o = s_O + r0 * kPairPitch + 2 * c;
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
-      const int r = r0 + 14 * it;
-      if (r < src_rows) {
-        unsigned* e = s_E + r * kPairPitch + 2 * c;
-        unsigned* o = s_O + r * kPairPitch + 2 * c;
-        e[0] = __byte_perm(w[it], 0u, 0x4140);                    // (p0, p1)
-        e[1] = __byte_perm(w[it], 0u, 0x4342);                    // (p2, p3)
-        o[0] = __byte_perm(w[it], 0u, 0x4241);                    // (p1, p2)
-        o[1] = __byte_perm(w[it], nx[it], 0x4443) & 0x00FF00FFu;  // (p3, p4)
+      if (r0 + 14 * it < src_rows) {
+        e[it * 14 * kPairPitch] = __byte_perm(w[it], 0u, 0x4140);                        // (p0, p1)
+        e[it * 14 * kPairPitch + 1] = __byte_perm(w[it], 0u, 0x4342);                    // (p2, p3)
+        o[it * 14 * kPairPitch] = __byte_perm(w[it], 0u, 0x4241);                        // (p1, p2)
+        o[it * 14 * kPairPitch + 1] = __byte_perm(w[it], nx[it], 0x4443) & 0x00FF00FFu;  // (p3, p4)
       }
     }
   }
@@ -221,11 +226,16 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   // strict 3x3 NMS in the same 16x2 form: horizontal 3-max of the rows above and below plus the two
   // side neighbours, then one compare per pixel; border cull; emit score = s' + t - 1
   const int sadd = g.fast_threshold - 1;
-  unsigned colmask = 0;
+  unsigned colmask0 = 0, colmask1 = 0;  // bit 15 = even pixel of the pair, bit 31 = odd pixel
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int col = 4 * c4 + j;
-    if (col >= 1 && col <= kFastTileW && gxs + j < Lw - kEdge) colmask |= 1u << j;
+    if (col >= 1 && col <= kFastTileW && gxs + j < Lw - kEdge) {
+      if (j < 2)
+        colmask0 |= 0x8000u << (16 * (j & 1));
+      else
+        colmask1 |= 0x8000u << (16 * (j & 1));
+    }
   }
 #pragma unroll 1
   for (int k = 0; k < 2; ++k) {
@@ -254,22 +264,20 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
       m0 = a.y;
       m1 = b.x;
     }
-    // keep mask of the 4 pixels (column 4*c4 + j of the score region; interior columns are 1..62)
-    const int sv[4] = {(int)(m0 & 0xFFFF), (int)(m0 >> 16), (int)(m1 & 0xFFFF), (int)(m1 >> 16)};
-    const int nv[4] = {(int)(nb0 & 0xFFFF), (int)(nb0 >> 16), (int)(nb1 & 0xFFFF), (int)(nb1 >> 16)};
-    unsigned keep = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) keep |= (sv[j] > nv[j] ? 1u : 0u) << j;
-    keep &= colmask;
-    // survivors are rare (~3 % of pixels): one shared-memory slot reservation per thread that has any
-    if (keep) {
-      uint32_t slot = atomicAdd(&s_n, (uint32_t)__popc(keep));
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (keep & (1u << j)) {
-          s_list[slot++] = pack_cand(gxs + j, gy, sv[j] + sadd);
-          atomicAdd(&s_hist[sv[j] + sadd], 1u);
-        }
+    // keep bit per lane: bit 15 / 31 of (nb | 0x8000) - m is clear iff nb < m (no borrow leaves a lane);
+    // colmask has the same layout (interior columns 1..62, x < w - 31)
+    unsigned k0 = ~((nb0 | 0x80008000u) - m0) & colmask0;
+    unsigned k1 = ~((nb1 | 0x80008000u) - m1) & colmask1;
+    // survivors are rare (~3 % of pixels): a short divergent loop over the set bits
+    unsigned kb = ((k0 >> 15) & 1u) | ((k0 >> 30) & 2u) | ((k1 >> 13) & 4u) | ((k1 >> 28) & 8u);
+    while (kb) {
+      const int j = __ffs(kb) - 1;
+      kb &= kb - 1;
+      const unsigned mm = j < 2 ? m0 : m1;
+      const int sv = (int)((j & 1) ? (mm >> 16) : (mm & 0xFFFFu)) + sadd;
+      const uint32_t slot = atomicAdd(&s_n, 1u);
+      s_list[slot] = pack_cand(gxs + j, gy, sv);
+      atomicAdd(&s_hist[sv], 1u);
     }
   }
   __syncthreads();
