@@ -175,6 +175,19 @@ def pyramid_pixels(h, w):
     return tot
 
 
+def fast_tiles(h, w):
+    """FAST tiles (62 x 30 interior of the 31-px-culled level) per frame — mirrors build_geom in detector_run.inc."""
+    n = 0
+    sf = np.float32(1.2)
+    for l in range(8):
+        inv = np.float32(1.0) / np.float32(np.power(np.float64(sf), np.float64(l)))
+        lh, lw = int(np.rint(np.float32(h) * inv)), int(np.rint(np.float32(w) * inv))
+        iw, ih = lw - 62, lh - 62
+        if iw > 0 and ih > 0:
+            n += -(-iw // 62) * -(-ih // 30)
+    return n
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -329,6 +342,13 @@ def run_ours(args, rank, world, local_rank):
                     "avg_launch_ms": stage[dom][0] / nl,
                     "algorithmic_bytes_per_launch": (alg.get(dom, 0) * frames_timed / nl) if dom in alg else None}
             if dom == "fast":
+                # algorithmic ALU work of FAST: 40 packed 3-input min/max lane-ops per scored pixel, 609 tiles x 64x32
+                # scored pixels per 1241x376 frame; ALU-pipe peak = 64 lanes/clk/SM (scripts/exp/pipe_exp.cu)
+                sm_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
+                tiles = fast_tiles(H_IMG, W_IMG)
+                ops = tiles * 64 * 32 * 40.0 * frames_timed / (stage["fast"][0] * 1e-3)
+                roof["alu"] = {"achieved": ops / 1e12, "peak": 148 * 64 * sm_clk / 1e12, "unit": "T lane-ops/s",
+                               "frac": ops / (148 * 64 * sm_clk), "what": "VIMNMX3.S16x2 of the two 9-of-16 arc networks"}
                 # FAST-9 needs 160 VIMNMX3.S16x2 per 4 pixels (two 9-of-16 sliding min/max networks): its floor on
                 # this chip is the ALU pipe (64 lanes/clk/SM, scripts/exp/pipe_exp.cu), not HBM
                 roof["note"] = ("ALU-pipe bound: 40 packed min/max per pixel; ncu sm__pipe_alu ~75 % busy, DRAM ~3 % "

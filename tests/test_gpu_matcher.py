@@ -226,3 +226,33 @@ def test_map_to_frame_matcher_class(orbx):
     keep = np.nonzero(d1[:, 0] < thr)[0]
     assert np.array_equal(good["query_idx"], keep) and np.array_equal(good["train_idx"], i1[keep, 0])
     assert np.array_equal(good["distance"], d1[keep, 0].astype(np.float32))
+
+
+@pytest.mark.parametrize("nq,nt,seed", [(1, 1, 11), (5, 300, 12), (130, 127, 13), (700, 900, 14), (300, 70001, 15),
+                                        (70001, 300, 16), (2049, 2047, 17)])
+def test_cross_check_fused_vs_oracle(orbx, nq, nt, seed):
+    """crossCheck=true (mutual first-arg-min, ascending queryIdx — SURVEY.md Appendix A S10): the reverse search is
+    produced by the same kernel launch as the forward one (CREDUX column minima), including the train-split path
+    (> 65536 train rows) and more than 65536 queries; forced duplicate rows exercise the lowest-index tie rule in
+    both directions."""
+    q, t = synth.random_descriptors(nq, seed), synth.random_descriptors(nt, seed + 100)
+    if nt > 20 and nq > 4:
+        t[nt // 2] = t[nt - 1] = t[3]        # duplicate train rows: forward ties
+        q[0] = t[3]
+        q[nq - 1] = q[2] = q[1]              # duplicate query rows: reverse ties
+        t[5] = q[1]
+    mx = orbx.FeatureMatcher(cross_check=True)
+    fwd_i, fwd_d, c = c_oracle.knn(q, t, 2)
+    rev_i, _, _ = c_oracle.knn(t, q, 1)
+    mutual = rev_i[fwd_i[:, 0], 0] == np.arange(nq)
+    out = mx.match_descriptors(q, t)
+    assert np.array_equal(out["query_idx"], np.nonzero(mutual)[0])
+    assert np.array_equal(out["train_idx"], fwd_i[mutual, 0])
+    assert np.array_equal(out["distance"], fwd_d[mutual, 0].astype(np.float32))
+    knn, cnt = mx.knn_match(q, t)
+    assert np.array_equal(cnt, np.where(mutual, c, 0))
+    ok = cnt > 0
+    assert np.array_equal(knn["train_idx"][ok, 0], fwd_i[ok, 0])
+    if cv_ref.HAVE_CV2 and nt < 262144 and nq < 5000:
+        x = cv_ref.match_k1(q, t, cross_check=True)
+        assert np.array_equal(out["query_idx"], x[:, 0]) and np.array_equal(out["train_idx"], x[:, 1])
