@@ -205,7 +205,8 @@ def run_ours(args, rank, world, local_rank):
     # every rank owns an independent sequence (canvas seed differs): weak scaling, no collective
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
-                          ratio=RATIO, cross_check=True, overlap=args.overlap)
+                          ratio=RATIO, cross_check=True, overlap=args.overlap,
+                          host_chunk=args.host_chunk)
     frames_pinned = torch.from_numpy(frames).pin_memory()
     frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
     frames_dev[:, :, :W_IMG].copy_(frames_pinned)
@@ -357,7 +358,7 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk,
+            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "host_chunk": args.host_chunk,
                        "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (T * H_IMG * fe.pitch / 1e6),
                        "keypoints_per_frame": K_mean, "fast_candidates_frame0": cand0,
                        "good_matches_per_pair": n_good / max(T - 1, 1)},
@@ -503,7 +504,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=T_SEQ, help="frames per GPU per step")
-    ap.add_argument("--chunk", type=int, default=250, help="frames per extraction launch")
+    ap.add_argument("--chunk", type=int, default=1000, help="frames per extraction launch (device-resident pass)")
+    ap.add_argument("--host-chunk", type=int, default=250,
+                    help="frames per pipeline stage of the end-to-end pass (H2D / kernels / D2H overlap)")
     ap.add_argument("--cpu-frames", type=int, default=100, help="frames of the sequence timed for cpu_baseline")
     ap.add_argument("--ref-frames", type=int, default=60, help="frames per step of the reference arm")
     ap.add_argument("--no-cpu", action="store_true")

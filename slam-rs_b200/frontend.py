@@ -19,12 +19,14 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
-                 ratio=0.75, cross_check=True, reference_filter=False, overlap=False):
+                 ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
         self.max_frames = int(max_frames)
         self.chunk = int(min(chunk, max_frames))
+        # pipeline granularity of run_host (H2D / compute / D2H overlap); run_device uses `chunk`
+        self.host_chunk = int(min(host_chunk or chunk, self.chunk))
         self.nfeatures = int(nfeatures)
         self.cap = int(cap or (nfeatures + nfeatures // 8 + 64 + 31) // 32 * 32)
         self.ratio = float(ratio)
@@ -117,7 +119,7 @@ class SequenceFrontEnd:
         self.d2h_stream.wait_stream(cur)
         # chunk schedule: a short first chunk so that compute starts early, full chunks in the middle, a short
         # last chunk so that little is left to copy back after the last kernel
-        c = self.chunk
+        c = self.host_chunk
         bounds, a = [], 0
         for size in (max(c // 4, 1), max(c // 2, 1)):
             if T - a > c:
