@@ -43,6 +43,7 @@ struct orbx_detector {
   int lw[kMaxLevels], lh[kMaxLevels], lpitch[kMaxLevels], quota[kMaxLevels], cand_cap[kMaxLevels], sel_cap[kMaxLevels];
   float lscale[kMaxLevels];
   size_t tab_x[kMaxLevels], tab_y[kMaxLevels];  // word offsets into tables
+  size_t tab_fast = 0;                          // FAST tile table (level | x0 << 4 | y0 << 16)
   int rs_smem_w[kMaxLevels], rs_smem_h[kMaxLevels];
   DevGeom geom;
   size_t lvl_off[kMaxLevels];  // byte offset of level l inside pyr / blr for the last batch
@@ -185,6 +186,7 @@ int orbx_detector_create(const orbx_params* params, int device, int max_w, int m
     d->cand_words += B * d->cand_cap[l];
     d->sel_words += B * d->sel_cap[l];
     d->table_words += (size_t)d->lw[l] + d->lh[l];
+    d->table_words += (size_t)div_up(d->lw[l], kFastTileW) * div_up(d->lh[l], kFastTileH);  // >= FAST tiles
     d->out_cap += d->sel_cap[l];
     max_sel = std::max(max_sel, d->sel_cap[l]);
   }

@@ -41,6 +41,7 @@ struct DevGeom {
   int nlevels, batch;
   int fast_threshold;
   int fast_tiles_total, blur_tiles_total;
+  const uint32_t* fast_tab;  // [fast_tiles_total] level | x0 << 4 | y0 << 16 (first interior pixel of the tile)
   uint32_t* cand_count;  // [B][8]
   uint32_t* hist;        // [B][8][256]
   uint32_t* sel_count;   // [B][8]

@@ -7,141 +7,90 @@
 // maxima of the 3x3 score neighbourhood; keep 31 <= x < w-31, 31 <= y < h-31.
 //
 // One launch covers every level of every frame (tile table in DevGeom).  A block owns a 62x30 interior
-// tile: it stages the 70x38 source footprint in shared memory with aligned 32-bit loads, computes the
-// 64x32 score region (tile + 1 px NMS ring; 8 pixels per thread), then emits NMS survivors as packed
-// (score<<24 | y<<12 | x) words: block-local compaction in shared memory, one global atomicAdd per
-// block to reserve list space, and a per-(frame,level) 256-bin score histogram for retainBest(2N_l).
+// tile and its 64x32 score region (tile + 1 px NMS ring):
+//   1. stage the 72x38 source footprint in shared memory, widened to 16x2 pixel pairs (plain + inverted);
+//   2. pretest every pixel pair on the 4 compass points (a necessary condition for any 9-arc) and
+//      compact the (pair, polarity) work items that pass into a block-wide queue;
+//   3. run the 9-of-16 arc network (40 packed 3-input min/max) only on queued items, all lanes busy;
+//   4. strict 3x3 NMS on the 16x2 score tile, border cull, emit survivors as packed
+//      (score<<24 | y<<12 | x) words: block-local compaction, one global atomicAdd per block to reserve
+//      list space, and a per-(frame,level) 256-bin score histogram for retainBest(2N_l).
 // Only pixels that can survive the border cull (and their NMS ring) are ever scored.
 #include "detector.cuh"
 
 namespace orbx {
 
-constexpr int kScoreW = kFastTileW + 2;  // 64
-constexpr int kScoreH = kFastTileH + 2;  // 32
-constexpr int kSrcH = kScoreH + 6;       // 38
-constexpr int kSrcPitch = 80;            // tile row pitch in bytes (72 used: 4 + 64 + 4)
-
-// ring offsets in the shared-memory tile (dy*kSrcPitch + dx); folds to immediates after unrolling
-__host__ __device__ constexpr int ring_off(int k) {
-  constexpr int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
-  constexpr int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
-  return dy[k] * kSrcPitch + dx[k];
-}
+constexpr int kScoreH = kFastTileH + 2;  // 32 score rows (score columns: 64 = 32 pixel pairs)
+constexpr int kSrcH = kScoreH + 6;       // 38 source rows
+constexpr int kPairPitch = 36;           // words (= pixel pairs) per tile row: 72 pixels = 4 + 64 + 4
+constexpr int kPlane = 1376;             // words per plane (38 x 36 = 1368, padded: 2 * kPlane % 32 == 0)
+constexpr int kScoreOff = 4 * kPlane;    // score tile (32 x 36 words) sits behind the four planes
+constexpr int kQueueCap = 2 * kScoreH * 32;  // every pair, both polarities
 
 // ---- packed 16x2 arithmetic: two pixels per instruction (VIMNMX3.S16x2 is native, ALU pipe) ----
 __device__ __forceinline__ unsigned min3x2(unsigned a, unsigned b, unsigned c) { return __vimin3_s16x2(a, b, c); }
 __device__ __forceinline__ unsigned max3x2(unsigned a, unsigned b, unsigned c) { return __vimax3_s16x2(a, b, c); }
 
-// R[k] = raw ring pixel k of two adjacent centres (one per 16-bit lane, 0..255).  Returns per lane
-//   lo = max over the 16 cyclic 9-arcs of (min over the arc)   -> bright contrast = lo - v
-//   hi = min over the 16 cyclic 9-arcs of (max over the arc)   -> dark   contrast = v - hi
-// Sliding-window min/max over 9 = 3-input ops over windows of 3, then over 3 windows of 3 (80 ops / 2 px).
-__device__ __forceinline__ void fast_arcs16x2(const unsigned (&R)[16], unsigned& lo, unsigned& hi) {
-  unsigned lo3[16], hi3[16];
+// Shared-memory planes hold the source footprint widened to 16 bits, as pixel pairs: plane E pairs tile
+// pixels (2p, 2p+1), plane O pairs (2p+1, 2p+2), so every ring read of two adjacent centres is one aligned
+// 32-bit word already in 16x2 form.  Planes 2 and 3 hold 255 - pixel: on them the bright-arc network
+// (max over the 16 arcs of the min over the arc) returns 255 - (min over arcs of the max), i.e. the dark
+// contrast comes out of the same 40 instructions: score' = arcs(plane) - centre(plane) - t, either polarity.
+//
+// B points at the centre pair of a work item in plane E (bright) or plane ~E (dark).
+__device__ __forceinline__ unsigned fast_arc_score(const unsigned* B, unsigned tk) {
+  unsigned R[16];
+#define ORBX_RING(K, DX, DY) \
+  R[K] = B[(((DX) & 1) ? kPlane + ((DX) - 1) / 2 : (DX) / 2) + (DY) * kPairPitch];
+  ORBX_RING(0, 0, 3)
+  ORBX_RING(1, 1, 3)
+  ORBX_RING(2, 2, 2)
+  ORBX_RING(3, 3, 1)
+  ORBX_RING(4, 3, 0)
+  ORBX_RING(5, 3, -1)
+  ORBX_RING(6, 2, -2)
+  ORBX_RING(7, 1, -3)
+  ORBX_RING(8, 0, -3)
+  ORBX_RING(9, -1, -3)
+  ORBX_RING(10, -2, -2)
+  ORBX_RING(11, -3, -1)
+  ORBX_RING(12, -3, 0)
+  ORBX_RING(13, -3, 1)
+  ORBX_RING(14, -2, 2)
+  ORBX_RING(15, -1, 3)
+#undef ORBX_RING
+  const unsigned v = B[0];
+  // sliding min over 9 = 3-input min over windows of 3, then over 3 windows of 3; max over the 16 arcs
+  unsigned lo3[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    lo3[k] = min3x2(R[k], R[(k + 1) & 15], R[(k + 2) & 15]);
-    hi3[k] = max3x2(R[k], R[(k + 1) & 15], R[(k + 2) & 15]);
-  }
-  unsigned l = 0u, h = 0x7FFF7FFFu;
+  for (int k = 0; k < 16; ++k) lo3[k] = min3x2(R[k], R[(k + 1) & 15], R[(k + 2) & 15]);
+  unsigned l = 0u;
 #pragma unroll
   for (int k = 0; k < 16; k += 2) {
     const unsigned a = min3x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
     const unsigned b = min3x2(lo3[k + 1], lo3[(k + 4) & 15], lo3[(k + 7) & 15]);
     l = max3x2(l, a, b);
-    const unsigned c = max3x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
-    const unsigned d = max3x2(hi3[k + 1], hi3[(k + 4) & 15], hi3[(k + 7) & 15]);
-    h = min3x2(h, c, d);
   }
-  lo = l;
-  hi = h;
-}
-
-// Shared-memory tiles hold the source footprint widened to 16 bits, twice: copy E pairs pixels
-// (2j, 2j+1), copy O pairs (2j+1, 2j+2), so every ring read of two adjacent centres is one aligned
-// 32-bit word already in 16x2 form (no PRMT / funnel shift in the hot loop).
-constexpr int kPairPitch = 36;  // words (= pixel pairs) per tile row; 72 pixels
-
-// scores (shifted: 0 = not a corner, s' = m - t >= 1 for corners, i.e. score = s' + t - 1) of 4 adjacent
-// pixels whose first pixel is tile column tc (multiple of 4) of tile row tr
-__device__ __forceinline__ void fast_score4(const unsigned* sE, const unsigned* sO, int tr, int tc, int t, unsigned& sl,
-                                            unsigned& sh) {
-  const int pe = tc >> 1;  // pair index of (tc, tc+1) in E; O pair (tc+1, tc+2) has the same index
-  unsigned Rl[16], Rh[16];
-  // ring offset (DX, DY): pixels tc+DX, tc+DX+1 (lo reg) and tc+DX+2, tc+DX+3 (hi reg)
-#define ORBX_RING(K, DX, DY)                                                                  \
-  {                                                                                           \
-    const unsigned* r_ = (((DX) & 1) ? sO : sE) + (tr + (DY)) * kPairPitch + pe;               \
-    constexpr int o_ = ((DX) & 1) ? ((DX) - 1) / 2 : (DX) / 2;                                 \
-    Rl[K] = r_[o_];                                                                           \
-    Rh[K] = r_[o_ + 1];                                                                       \
-  }
-  ORBX_RING(0, 0, 3)
-  ORBX_RING(8, 0, -3)
-  ORBX_RING(4, 3, 0)
-  ORBX_RING(12, -3, 0)
-  const unsigned* c_ = sE + tr * kPairPitch + pe;
-  const unsigned vl = c_[0], vh = c_[1];
-  // contrasts are kept biased by +256 per lane so that plain 32-bit adds never borrow across lanes
+  // contrasts are kept biased by +256 per lane so that plain 32-bit adds never borrow across lanes:
+  // tk = 256 + t per lane; result = max(contrast - t, 0) per lane (0 = not a corner of this polarity)
   constexpr unsigned kBias = 0x01000100u;
-  const unsigned tk = kBias + (unsigned)t * 0x00010001u;  // 256 + t
-  {
-    // compass points first: any 9-arc holds one pixel of {0,8} and one of {4,12} — a necessary
-    // condition evaluated for the whole warp (big win on smooth images, ~10 % overhead on dense texture)
-    unsigned possible = 0;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const unsigned* R = half ? Rh : Rl;
-      const unsigned v = half ? vh : vl;
-      const unsigned pb = __vmins2(__vmaxs2(R[0], R[8]), __vmaxs2(R[4], R[12]));  // bright needs pb > v + t
-      const unsigned pd = __vmaxs2(__vmins2(R[0], R[8]), __vmins2(R[4], R[12]));  // dark needs pd < v - t
-      const unsigned mb = pb + kBias - v, md = v + kBias - pd;  // 256 + contrast, lanes in 1..511
-      possible |= __vmaxs2(__vmaxs2(mb, md), tk) - tk;          // > 0 in some lane?
-    }
-    if (!__any_sync(0xFFFFFFFFu, possible != 0)) return;  // sl, sh stay 0
-  }
-  ORBX_RING(1, 1, 3)
-  ORBX_RING(2, 2, 2)
-  ORBX_RING(3, 3, 1)
-  ORBX_RING(5, 3, -1)
-  ORBX_RING(6, 2, -2)
-  ORBX_RING(7, 1, -3)
-  ORBX_RING(9, -1, -3)
-  ORBX_RING(10, -2, -2)
-  ORBX_RING(11, -3, -1)
-  ORBX_RING(13, -3, 1)
-  ORBX_RING(14, -2, 2)
-  ORBX_RING(15, -1, 3)
-#undef ORBX_RING
-  unsigned lo, hi;
-  fast_arcs16x2(Rl, lo, hi);
-  sl = __vmaxs2(__vmaxs2(lo + kBias - vl, vl + kBias - hi), tk) - tk;  // max(m - t, 0) per lane
-  fast_arcs16x2(Rh, lo, hi);
-  sh = __vmaxs2(__vmaxs2(lo + kBias - vh, vh + kBias - hi), tk) - tk;
+  return __vmaxs2(l + kBias - v, tk) - tk;
 }
 
-constexpr int kScPitch = 34;  // words per row of the 16x2 score tile: pad pair, 32 pairs, pad pair
-
-__global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
-  __shared__ __align__(16) unsigned s_E[kSrcH * kPairPitch];
-  __shared__ __align__(16) unsigned s_O[kSrcH * kPairPitch];
-  __shared__ __align__(16) unsigned s_sc[kScoreH * kScPitch];
-  __shared__ uint32_t s_list[(kFastTileW / 2 + 1) * (kFastTileH / 2 + 1) + 32];
+__global__ void __launch_bounds__(256, 6) fast_nms_kernel(DevGeom g) {
+  // planes E, O, ~E, ~O, then the 16x2 score tile (row pitch kPairPitch, word (cy, pe) = score pair pe - 2)
+  __shared__ __align__(16) unsigned s_mem[4 * kPlane + kScoreH * kPairPitch];
+  __shared__ unsigned s_q[kQueueCap];  // work items: plane byte offset | score byte offset << 16
+  uint32_t* const s_list = s_q;        // survivor list of step 4 (<= 31 x 15 strict maxima) reuses the queue
   __shared__ uint32_t s_hist[256];
-  __shared__ uint32_t s_n, s_base;
+  __shared__ uint32_t s_n, s_base, s_qn;
 
-  // tile -> (level, tx, ty)
-  const int tile = blockIdx.x;
-  int l = 0;
-#pragma unroll
-  for (int i = 1; i < kMaxLevels; ++i)
-    if (i < g.nlevels && tile >= g.lv[i].fast_tile_begin) l = i;
+  // tile -> (level, first interior pixel)
+  const uint32_t tt = __ldg(g.fast_tab + blockIdx.x);
+  const int l = tt & 7;
+  const int x0 = (tt >> 4) & 0xFFF, y0 = tt >> 16;
   const DevLevel& L = g.lv[l];
   const int frame = blockIdx.y;
-  const int lt = tile - L.fast_tile_begin;
-  const int ty = lt / L.fast_tiles_x, tx = lt - ty * L.fast_tiles_x;
-  const int x0 = kEdge + tx * kFastTileW;  // first interior pixel of the tile
-  const int y0 = kEdge + ty * kFastTileH;
   // tile column c <-> image x = x0 - 5 + c (score column 0 = x0 - 1 sits at tile column 4, word aligned);
   // tile row r <-> image y = y0 - 4 + r
   const int gx0 = x0 - 5, gy0 = y0 - 4;
@@ -153,9 +102,9 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
   const int src_rows = min(kSrcH, rows_needed + 6);
 
   s_hist[tid] = 0;
-  if (tid == 0) s_n = 0;
+  if (tid == 0) s_n = 0, s_qn = 0;
 
-  // stage the 72 x 38 footprint, widened to the two 16x2 copies, straight from global memory:
+  // 1. stage the 72 x 38 footprint, widened to the 16x2 planes, straight from global memory:
   // thread -> tile word column c = tid % 18 (fixed), rows tid/18, +14, +28
   if (tid < 252) {
     const int c = tid % 18, r0 = tid / 18;
@@ -190,93 +139,124 @@ __global__ void __launch_bounds__(256) fast_nms_kernel(DevGeom g) {
         }
       }
     }
-    unsigned* e = s_E + r0 * kPairPitch + 2 * c;
-    unsigned* o = s_O + r0 * kPairPitch + 2 * c;
+    unsigned* e = s_mem + r0 * kPairPitch + 2 * c;
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
       if (r0 + 14 * it < src_rows) {
-        e[it * 14 * kPairPitch] = __byte_perm(w[it], 0u, 0x4140);                        // (p0, p1)
-        e[it * 14 * kPairPitch + 1] = __byte_perm(w[it], 0u, 0x4342);                    // (p2, p3)
-        o[it * 14 * kPairPitch] = __byte_perm(w[it], 0u, 0x4241);                        // (p1, p2)
-        o[it * 14 * kPairPitch + 1] = __byte_perm(w[it], nx[it], 0x4443) & 0x00FF00FFu;  // (p3, p4)
+        const unsigned e0 = __byte_perm(w[it], 0u, 0x4140);                        // (p0, p1)
+        const unsigned e1 = __byte_perm(w[it], 0u, 0x4342);                        // (p2, p3)
+        const unsigned o0 = __byte_perm(w[it], 0u, 0x4241);                        // (p1, p2)
+        const unsigned o1 = __byte_perm(w[it], nx[it], 0x4443) & 0x00FF00FFu;      // (p3, p4)
+        unsigned* q = e + it * 14 * kPairPitch;
+        *reinterpret_cast<uint2*>(q) = make_uint2(e0, e1);
+        *reinterpret_cast<uint2*>(q + kPlane) = make_uint2(o0, o1);
+        *reinterpret_cast<uint2*>(q + 2 * kPlane) = make_uint2(e0 ^ 0x00FF00FFu, e1 ^ 0x00FF00FFu);
+        *reinterpret_cast<uint2*>(q + 3 * kPlane) = make_uint2(o0 ^ 0x00FF00FFu, o1 ^ 0x00FF00FFu);
       }
     }
   }
   __syncthreads();
 
-  // score region: columns x0-1 .. x0+62, rows y0-1 .. y0+30; 4 pixels per thread, 2 rows per thread
-  const int c4 = tid & 15;               // group of 4 score columns
-  const int gxs = x0 - 1 + c4 * 4;       // image x of the first of the 4 pixels
-  const int over = gxs + 3 - (Lw - kEdge);  // pixels with x > w-31 are not scored
-#pragma unroll 1
-  for (int k = 0; k < 2; ++k) {
-    const int cy = (tid >> 4) + k * 16;
-    unsigned sl = 0, sh = 0;
-    // a warp covers score rows 2w, 2w+1 (+16): skip the ones below the last row that can matter
-    if ((cy & ~1) < rows_needed) fast_score4(s_E, s_O, cy + 3, 4 + 4 * c4, g.fast_threshold, sl, sh);
-    if (cy >= rows_needed || over >= 4) sl = sh = 0;
-    if (over >= 2) sh = 0;
-    if (over == 3) sl &= 0xFFFFu;
-    if (over == 1) sh &= 0xFFFFu;
-    s_sc[cy * kScPitch + 1 + 2 * c4] = sl;
-    s_sc[cy * kScPitch + 2 + 2 * c4] = sh;
+  // 2. compass pretest: any 9-arc holds one pixel of {0, 8} and one of {4, 12}.  Warp w owns score rows
+  // 4w .. 4w+3, lane j owns score pair j (columns 2j, 2j+1; tile pair pe = j + 2).  Items that pass go to the
+  // block-wide queue (ballot-compacted: one shared atomic per warp and row); the pair's score word is zeroed.
+  const int lane = tid & 31, warp = tid >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  constexpr unsigned kBias = 0x01000100u;
+  const unsigned tk = kBias + (unsigned)g.fast_threshold * 0x00010001u;  // 256 + t per lane
+  // pixels with x > w - 31 are never needed (x = w - 31 is the NMS ring of the last kept column)
+  const bool col_ok = x0 - 1 + 2 * lane <= Lw - kEdge;
+  if (4 * warp < rows_needed) {  // warp-uniform
+    const int off0 = (4 * warp + 3) * kPairPitch + lane + 2;  // centre pair of row 4w in plane E
+    const unsigned* B0 = s_mem + off0;
+    unsigned mb[4], md[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const unsigned* B = B0 + i * kPairPitch;
+      const unsigned v = B[0], a = B[3 * kPairPitch], b = B[-3 * kPairPitch], c = B[kPlane + 1], d = B[kPlane - 2];
+      const unsigned pb = __vmins2(__vmaxs2(a, b), __vmaxs2(c, d));  // bright needs pb > v + t
+      const unsigned pd = __vmaxs2(__vmins2(a, b), __vmins2(c, d));  // dark needs pd < v - t
+      const bool ok = col_ok && 4 * warp + i < rows_needed;
+      mb[i] = __ballot_sync(0xFFFFFFFFu, ok && __vmaxs2(pb + kBias - v, tk) != tk);
+      md[i] = __ballot_sync(0xFFFFFFFFu, ok && __vmaxs2(v + kBias - pd, tk) != tk);
+      s_mem[kScoreOff + off0 + (i - 3) * kPairPitch] = 0u;
+    }
+    int total = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) total += __popc(mb[i]) + __popc(md[i]);
+    unsigned at = 0;
+    if (lane == 0 && total)  // one reservation per warp (plain PTX: no compiler-side re-aggregation)
+      asm volatile("atom.shared.add.u32 %0, [%1], %2;"
+                   : "=r"(at)
+                   : "r"((unsigned)__cvta_generic_to_shared(&s_qn)), "r"((unsigned)total)
+                   : "memory");
+    at = __shfl_sync(0xFFFFFFFFu, at, 0);
+    // item = plane byte offset of the centre pair | byte offset of its score word << 16
+    const unsigned item0 = (unsigned)(off0 * 4) | ((unsigned)((kScoreOff + off0 - 3 * kPairPitch) * 4) << 16);
+    constexpr unsigned kRowStep = (unsigned)(kPairPitch * 4) * 0x00010001u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if ((mb[i] >> lane) & 1u) s_q[at + __popc(mb[i] & lt)] = item0 + i * kRowStep;
+      at += __popc(mb[i]);
+      if ((md[i] >> lane) & 1u) s_q[at + __popc(md[i] & lt)] = item0 + i * kRowStep + 2 * kPlane * 4;
+      at += __popc(md[i]);
+    }
   }
   __syncthreads();
 
-  // strict 3x3 NMS in the same 16x2 form: horizontal 3-max of the rows above and below plus the two
-  // side neighbours, then one compare per pixel; border cull; emit score = s' + t - 1
-  const int sadd = g.fast_threshold - 1;
-  unsigned colmask0 = 0, colmask1 = 0;  // bit 15 = even pixel of the pair, bit 31 = odd pixel
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int col = 4 * c4 + j;
-    if (col >= 1 && col <= kFastTileW && gxs + j < Lw - kEdge) {
-      if (j < 2)
-        colmask0 |= 0x8000u << (16 * (j & 1));
-      else
-        colmask1 |= 0x8000u << (16 * (j & 1));
-    }
-  }
+  // 3. arc network on the queued items; a pixel cannot be a bright and a dark corner at once (2 x 9 > 16),
+  // so OR-ing the two polarities' results into the score word is the per-lane maximum
+  const unsigned nq = s_qn;
+  if (nq == 0) return;  // block-uniform: no corner in this tile
 #pragma unroll 1
-  for (int k = 0; k < 2; ++k) {
-    const int cy = (tid >> 4) + k * 16;
-    const int gy = y0 - 1 + cy;
-    if (cy < 1 || cy > kFastTileH || gy >= Lh - kEdge) continue;
-    const unsigned* base = s_sc + cy * kScPitch + 2 * c4;  // pairs (x-2,x-1) (x,x+1) (x+2,x+3) (x+4,x+5)
-    unsigned nb0, nb1, m0, m1;
-    {
-      const uint2 a = *reinterpret_cast<const uint2*>(base - kScPitch), b = *reinterpret_cast<const uint2*>(base - kScPitch + 2);
-      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
-      nb0 = max3x2(l0, a.y, l1);
-      nb1 = max3x2(l1, b.x, l2);
+  for (unsigned i = tid; i < nq; i += 256) {
+    const unsigned item = s_q[i];
+    const unsigned res =
+        fast_arc_score(reinterpret_cast<const unsigned*>(reinterpret_cast<const char*>(s_mem) + (item & 0xFFFFu)), tk);
+    if (res) atomicOr(reinterpret_cast<unsigned*>(reinterpret_cast<char*>(s_mem) + (item >> 16)), res);
+  }
+  __syncthreads();
+
+  // 4. strict 3x3 NMS in 16x2 form.  Warp w owns output rows 4w .. 4w+3 (clipped to the interior rows
+  // 1 .. 30 and to y < h - 31), lane j the pair (2j, 2j+1); rows roll through registers.  Per row:
+  // c = the pair, hs = max(left, right neighbours), h3 = max(hs, c); neighbourhood of row cy =
+  // max(h3[cy-1], h3[cy+1], hs[cy]).  Border cull; emit score = s' + t - 1.
+  const int sadd = g.fast_threshold - 1;
+  const int gxs = x0 - 1 + 2 * lane;  // image x of the pair's first pixel (score column 2 * lane)
+  unsigned colmask = 0;               // bit 15 = first pixel may be emitted, bit 31 = second pixel
+  if (lane >= 1 && gxs < Lw - kEdge) colmask |= 0x8000u;
+  if (lane <= 30 && gxs + 1 < Lw - kEdge) colmask |= 0x80000000u;
+  const int cy_lo = max(4 * warp, 1);
+  const int cy_hi = min(min(4 * warp + 3, kFastTileH), Lh - kEdge - y0);  // gy = y0 - 1 + cy < Lh - kEdge
+  if (cy_lo <= cy_hi) {
+    const unsigned* S = s_mem + kScoreOff + lane + 2;
+    unsigned c[6], h3[6], hs[6];  // rows 4w-1 .. 4w+4 (rows outside the tile only feed rows that are not emitted)
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const unsigned* p = S + min(max(4 * warp - 1 + k, 0), kScoreH - 1) * kPairPitch;
+      const unsigned pl = p[-1], pc = p[0], pr = p[1];
+      c[k] = pc;
+      hs[k] = __vmaxs2(__byte_perm(pl, pc, 0x5432), __byte_perm(pc, pr, 0x5432));
+      h3[k] = __vmaxs2(hs[k], pc);
     }
-    {
-      const uint2 a = *reinterpret_cast<const uint2*>(base + kScPitch), b = *reinterpret_cast<const uint2*>(base + kScPitch + 2);
-      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
-      nb0 = max3x2(nb0, max3x2(l0, a.y, l1), 0u);
-      nb1 = max3x2(nb1, max3x2(l1, b.x, l2), 0u);
+    // keep bit per lane: bit 15 / 31 of (nb | 0x8000) - m is clear iff nb < m (no borrow leaves a lane)
+    unsigned kacc = 0;  // bit 2i = first pixel of row 4w+i survives, bit 2i+1 = second pixel
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const unsigned nb = max3x2(h3[i], h3[i + 2], hs[i + 1]);
+      unsigned kb = ~((nb | 0x80008000u) - c[i + 1]) & colmask;
+      if (4 * warp + i < cy_lo || 4 * warp + i > cy_hi) kb = 0;
+      kacc |= (((kb >> 15) & 1u) | ((kb >> 30) & 2u)) << (2 * i);
     }
-    {
-      const uint2 a = *reinterpret_cast<const uint2*>(base), b = *reinterpret_cast<const uint2*>(base + 2);
-      const unsigned l0 = __byte_perm(a.x, a.y, 0x5432), l1 = __byte_perm(a.y, b.x, 0x5432), l2 = __byte_perm(b.x, b.y, 0x5432);
-      nb0 = max3x2(nb0, l0, l1);
-      nb1 = max3x2(nb1, l1, l2);
-      m0 = a.y;
-      m1 = b.x;
-    }
-    // keep bit per lane: bit 15 / 31 of (nb | 0x8000) - m is clear iff nb < m (no borrow leaves a lane);
-    // colmask has the same layout (interior columns 1..62, x < w - 31)
-    unsigned k0 = ~((nb0 | 0x80008000u) - m0) & colmask0;
-    unsigned k1 = ~((nb1 | 0x80008000u) - m1) & colmask1;
-    // survivors are rare (~3 % of pixels): a short divergent loop over the set bits
-    unsigned kb = ((k0 >> 15) & 1u) | ((k0 >> 30) & 2u) | ((k1 >> 13) & 4u) | ((k1 >> 28) & 8u);
-    while (kb) {
-      const int j = __ffs(kb) - 1;
-      kb &= kb - 1;
-      const unsigned mm = j < 2 ? m0 : m1;
-      const int sv = (int)((j & 1) ? (mm >> 16) : (mm & 0xFFFFu)) + sadd;
+    // survivors are rare (~3 % of pixels): a short divergent loop over the set bits, after all rows
+    while (kacc) {
+      const int bit = __ffs(kacc) - 1;
+      kacc &= kacc - 1;
+      const int cy = 4 * warp + (bit >> 1), hi = bit & 1;
+      const unsigned m = S[cy * kPairPitch];
+      const int sv = (int)(hi ? (m >> 16) : (m & 0xFFFFu)) + sadd;
       const uint32_t slot = atomicAdd(&s_n, 1u);
-      s_list[slot] = pack_cand(gxs + j, gy, sv);
+      s_list[slot] = pack_cand(gxs + hi, y0 - 1 + cy, sv);
       atomicAdd(&s_hist[sv], 1u);
     }
   }
