@@ -61,6 +61,20 @@ class ClockSampler:
         self.proc = None
 
     def start(self):
+        # NVML from a thread (one sample every ~2 ms: the timed region is tens of ms); nvidia-smi -lms as fallback
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.samples, self.mask, self.running = [], 0, True
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
@@ -70,11 +84,31 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        while self.running:
+            try:
+                self.samples.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                self.mask |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+            except Exception:
+                pass
+            time.sleep(0.002)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
+    def _stop_nvml(self):
+        self.running = False
+        self.thread.join(timeout=1)
+        bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+                "reasons": sorted(v for k, v in bits.items() if self.mask & k), "source": "nvml"}
+
     def stop(self):
+        if self.nvml:
+            return self._stop_nvml()
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -206,7 +240,7 @@ def run_ours(args, rank, world, local_rank):
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
                           ratio=RATIO, cross_check=True, overlap=args.overlap,
-                          host_chunk=args.host_chunk)
+                          host_chunk=args.host_chunk, dual=args.dual)
     frames_pinned = torch.from_numpy(frames).pin_memory()
     frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
     frames_dev[:, :, :W_IMG].copy_(frames_pinned)
@@ -358,7 +392,7 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "host_chunk": args.host_chunk,
+            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "host_chunk": args.host_chunk, "e2e_streams": 2 if args.dual else 1,
                        "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (T * H_IMG * fe.pitch / 1e6),
                        "keypoints_per_frame": K_mean, "fast_candidates_frame0": cand0,
                        "good_matches_per_pair": n_good / max(T - 1, 1)},
@@ -505,10 +539,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=T_SEQ, help="frames per GPU per step")
     ap.add_argument("--chunk", type=int, default=1000, help="frames per extraction launch (device-resident pass)")
-    ap.add_argument("--host-chunk", type=int, default=250,
+    ap.add_argument("--dual", type=int, default=1, help="1: alternate e2e pipeline stages between two streams")
+    ap.add_argument("--host-chunk", type=int, default=167,
                     help="frames per pipeline stage of the end-to-end pass (H2D / kernels / D2H overlap)")
-    ap.add_argument("--cpu-frames", type=int, default=100, help="frames of the sequence timed for cpu_baseline")
-    ap.add_argument("--ref-frames", type=int, default=60, help="frames per step of the reference arm")
+    ap.add_argument("--cpu-frames", type=int, default=500, help="frames of the sequence timed for cpu_baseline")
+    ap.add_argument("--ref-frames", type=int, default=250, help="frames per step of the reference arm")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "map"],
                     help="sequence = configs[1] (default, the metric's workload); map = configs[3] map-to-frame matching")

@@ -19,7 +19,8 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
-                 ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None):
+                 ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None,
+                 dual=False):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
@@ -63,16 +64,27 @@ class SequenceFrontEnd:
         self.mstream = torch.cuda.Stream(device=self.dev) if self.overlap else self.stream
         self.det.set_stream(self.stream.cuda_stream)
         self.matcher.set_stream(self.mstream.cuda_stream)
+        # dual=True: run_host alternates its pipeline stages between two detector / matcher handles on two
+        # streams, so the tail wave of every kernel of stage i overlaps kernels of stage i+1
+        self.dual = bool(dual)
+        if self.dual:
+            self.det2 = OrbDetector(nfeatures, device=device, max_width=self.w, max_height=self.h,
+                                    max_batch=self.host_chunk)
+            self.matcher2 = FeatureMatcher(device=device, cross_check=cross_check)
+            self.stream2 = torch.cuda.Stream(device=self.dev)
+            self.det2.set_stream(self.stream2.cuda_stream)
+            self.matcher2.set_stream(self.stream2.cuda_stream)
 
     # ------------------------------------------------------------------ stages
-    def extract(self, frames_dev, t0, t1):
+    def extract(self, frames_dev, t0, t1, det=None, step=None):
         """frames_dev: uint8 CUDA [T, h, pitch] (pitch >= w).  Extract frames t0..t1-1."""
-        for a in range(t0, t1, self.chunk):
-            b = min(a + self.chunk, t1)
-            self.det.detect_and_compute_device(frames_dev[a:b], self.kps[a:b], self.desc[a:b], self.n[a:b],
-                                               width=self.w)
+        det = det or self.det
+        step = step or self.chunk
+        for a in range(t0, t1, step):
+            b = min(a + step, t1)
+            det.detect_and_compute_device(frames_dev[a:b], self.kps[a:b], self.desc[a:b], self.n[a:b], width=self.w)
 
-    def match(self, t0, t1):
+    def match(self, t0, t1, matcher=None):
         """Match (t-1 -> t) for t in [max(t0,1), t1): result row t describes pair (t-1, t)."""
         a = max(t0, 1)
         if t1 <= a:
@@ -80,7 +92,7 @@ class SequenceFrontEnd:
         npairs = t1 - a
         cap = self.cap
         stride = cap * 32
-        m = self.matcher
+        m = matcher or self.matcher
         m.knn_match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs, cap,
                                  self.knn[a], self.n_per_q[a])
         m.ratio_test_batch_device(self.knn[a], self.n_per_q[a], self.n[a - 1:], npairs, cap, self.ratio, self.good[a],
@@ -139,13 +151,29 @@ class SequenceFrontEnd:
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
                 events.append(ev)
+        prev_extracted = None
         for i, (a, b) in enumerate(bounds):
-            self.stream.wait_event(events[i])
-            self.extract(self.frames_dev, a, b)
-            self.mstream.wait_stream(self.stream)
-            self.match(a, b)
+            if self.dual:
+                st, det, m = ((self.stream, self.det, self.matcher), (self.stream2, self.det2, self.matcher2))[i & 1]
+                if i < 2:
+                    st.wait_stream(cur)
+                st.wait_event(events[i])
+                self.extract(self.frames_dev, a, b, det=det, step=self.host_chunk)
+                ex = torch.cuda.Event()
+                ex.record(st)
+                if prev_extracted is not None:
+                    st.wait_event(prev_extracted)  # descriptors of frame a-1 come from the other stream
+                prev_extracted = ex
+                self.match(a, b, matcher=m)
+                last = st
+            else:
+                self.stream.wait_event(events[i])
+                self.extract(self.frames_dev, a, b)
+                self.mstream.wait_stream(self.stream)
+                self.match(a, b)
+                last = self.mstream
             # results of this chunk go back on the D2H stream while the next chunk computes
-            self.d2h_stream.wait_stream(self.mstream)
+            self.d2h_stream.wait_stream(last)
             with torch.cuda.stream(self.d2h_stream):
                 out["n"][a:b].copy_(self.n[a:b], non_blocking=True)
                 out["kps"][a:b].copy_(self.kps[a:b], non_blocking=True)
@@ -154,6 +182,8 @@ class SequenceFrontEnd:
                 out["n_good"][a:b].copy_(self.n_good[a:b], non_blocking=True)
         cur.wait_stream(self.stream)
         cur.wait_stream(self.mstream)
+        if self.dual:
+            cur.wait_stream(self.stream2)
         cur.wait_stream(self.d2h_stream)
         return T
 

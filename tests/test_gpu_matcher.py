@@ -191,6 +191,19 @@ def test_sequence_front_end_matches_per_frame_api(orbx):
         n = int(out["n"][t])
         assert np.array_equal(out["desc"][t, :n].numpy(), per[t][1])
     assert np.array_equal(out["n_good"][1:T].numpy(), fe.n_good[1:T].cpu().numpy())
+    # ... and so does the two-stream pipeline (stages alternate between two detector / matcher handles)
+    fe2 = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=2, dual=True)
+    out2 = fe2.alloc_host_outputs()
+    fe2.run_host(torch.from_numpy(seq).pin_memory(), out2)
+    torch.cuda.synchronize()
+    for key in ("n", "n_good"):
+        assert np.array_equal(out2[key].numpy(), out[key].numpy())
+    for t in range(T):
+        n, g = int(out["n"][t]), int(out["n_good"][t])
+        assert np.array_equal(out2["desc"][t, :n].numpy(), out["desc"][t, :n].numpy())
+        assert np.array_equal(out2["kps"][t, :n].numpy(), out["kps"][t, :n].numpy())
+        if t:
+            assert np.array_equal(out2["good"][t, :g].numpy(), out["good"][t, :g].numpy())
 
 
 def test_map_to_frame_matcher_class(orbx):
