@@ -236,6 +236,8 @@ def run_ours(args, rank, world, local_rank):
     synth = load_synth()
 
     T = args.frames
+    if world > 1 and args.numa_bind:
+        bind_near_gpu(local_rank)  # before the pinned buffers are first touched
     # every rank owns an independent sequence (canvas seed differs): weak scaling, no collective
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
@@ -531,9 +533,26 @@ def run_map(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def bind_near_gpu(index):
+    """Pin this rank to the CPUs NVML reports as local to its GPU, so that pinned host buffers are first
+    touched on that NUMA node (the end-to-end pass is host-memory / PCIe bound at 8 ranks)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 64) + 63) // 64)
+        cpus = {i * 64 + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 def main():
-    # the image exports NCCL_DEBUG=VERSION, which makes NCCL print a banner on stdout next to the JSON line
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    # this image's NCCL configuration prints a version banner on stdout next to the JSON line unless told otherwise
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
         os.environ["NCCL_DEBUG"] = "WARN"
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -548,6 +567,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=500, help="frames of the sequence timed for cpu_baseline")
     ap.add_argument("--ref-frames", type=int, default=250, help="frames per step of the reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--numa-bind", type=int, default=1, help="N>1: bind each rank to its GPU's local CPUs")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "map"],
                     help="sequence = configs[1] (default, the metric's workload); map = configs[3] map-to-frame matching")
     ap.add_argument("--map-fresh-frames", action="store_true", help="regenerate the map per query frame (slow)")
