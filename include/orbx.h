@@ -172,6 +172,20 @@ int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const i
                      const uint8_t* t, size_t t_stride, const int* nt_dev, int npairs, int max_rows,
                      orbx_dmatch* out, int* n_out_dev);
 
+/* replaces PoseEstimator::extract_matched_points (src/odometry/pose.rs:27-44; SURVEY.md §8 f2, first step):
+ * pts1[i] = kp1[matches[i].query_idx].pt, pts2[i] = kp2[matches[i].train_idx].pt as (x, y) fp32 pairs, match
+ * order preserved.  An index outside its keypoint array is the reference's `Vector::get(..)?` error:
+ * ORBX_E_BADARG (outputs unspecified).  Host or device arrays. */
+int orbx_extract_matched_points(orbx_matcher* m, const orbx_keypoint* kp1, int n1, const orbx_keypoint* kp2, int n2,
+                                const orbx_dmatch* matches, int n, float* pts1, float* pts2);
+/* batched device form (sequence front end): problem p reads kp1 + p*kp_stride (n1_dev[p] keypoints), kp2 +
+ * p*kp_stride (n2_dev[p]) and matches + p*max_rows (n_dev[p]); writes pts1 / pts2 + p*max_rows*2 floats;
+ * *bad_dev becomes non-zero if any index is out of range (the caller clears it).  Asynchronous. */
+int orbx_extract_matched_points_batch(orbx_matcher* m, const orbx_keypoint* kp1, const int* n1_dev,
+                                      const orbx_keypoint* kp2, const int* n2_dev, size_t kp_stride,
+                                      const orbx_dmatch* matches, const int* n_dev, int npairs, int max_rows,
+                                      float* pts1, float* pts2, int* bad_dev);
+
 /* matcher timing: accumulated ms / launches of the Hamming kernel */
 int orbx_matcher_set_timing(orbx_matcher* m, int enable);
 int orbx_matcher_timing(orbx_matcher* m, float* ms, int* launches, int reset);

@@ -87,6 +87,16 @@ class FeatureMatcher {
     out.resize(n);
     return out;
   }
+  // PoseEstimator::extract_matched_points (src/odometry/pose.rs:27-44): (x, y) pairs, match order; throws when a
+  // match index is outside its keypoint vector (the reference returns Err)
+  std::pair<std::vector<float>, std::vector<float>> extract_matched_points(const std::vector<orbx_keypoint>& kp1,
+                                                                          const std::vector<orbx_keypoint>& kp2,
+                                                                          const std::vector<orbx_dmatch>& m) {
+    std::vector<float> p1(2 * m.size()), p2(2 * m.size());
+    check(orbx_extract_matched_points(h_, kp1.data(), (int)kp1.size(), kp2.data(), (int)kp2.size(), m.data(),
+                                      (int)m.size(), p1.data(), p2.data()));
+    return {p1, p2};
+  }
 
  private:
   orbx_matcher* h_ = nullptr;

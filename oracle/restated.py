@@ -413,3 +413,16 @@ def map_find_matches(points, descs, has_desc, alive, R, t, intr, frame_desc):
         return np.zeros((0, 2), np.int64)
     good = filter_good_matches(match_k1(np.asarray(descs)[ids], frame_desc), 2.0)
     return np.stack([ids[good[:, 0]], good[:, 1]], 1) if len(good) else np.zeros((0, 2), np.int64)
+
+
+# ---------------------------------------------------------------- §8 f2 (first step): matched points
+def extract_matched_points(kp1_xy, kp2_xy, matches):
+    """/root/reference/src/odometry/pose.rs:27-44: for every match (query_idx, train_idx) push kp1[query_idx].pt
+    and kp2[train_idx].pt.  kp*_xy: float32 [n, 2]; matches: int [m, 2].  Raises IndexError like `Vector::get(..)?`."""
+    p1, p2 = [], []
+    for q, t in np.asarray(matches).reshape(-1, 2):
+        if not (0 <= q < len(kp1_xy)) or not (0 <= t < len(kp2_xy)):
+            raise IndexError("match index out of range")
+        p1.append(kp1_xy[q])
+        p2.append(kp2_xy[t])
+    return (np.asarray(p1, np.float32).reshape(-1, 2), np.asarray(p2, np.float32).reshape(-1, 2))

@@ -29,6 +29,8 @@ extern "C" {
     pub fn orbx_knn_match2(m: *mut orbx_matcher, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n_per_q: *mut c_int) -> c_int;
     pub fn orbx_ratio_test(m: *mut orbx_matcher, knn2: *const orbx_dmatch, n_per_q: *const c_int, nq: c_int, ratio: f32, out: *mut orbx_dmatch, n: *mut c_int) -> c_int;
     pub fn orbx_filter_good_matches(m: *mut orbx_matcher, inp: *const orbx_dmatch, n: c_int, ratio: f32, out: *mut orbx_dmatch, n_out: *mut c_int) -> c_int;
+    pub fn orbx_extract_matched_points(m: *mut orbx_matcher, kp1: *const orbx_keypoint, n1: c_int, kp2: *const orbx_keypoint, n2: c_int, matches: *const orbx_dmatch, n: c_int, pts1: *mut f32, pts2: *mut f32) -> c_int;
+    pub fn orbx_extract_matched_points_batch(m: *mut orbx_matcher, kp1: *const orbx_keypoint, n1_dev: *const c_int, kp2: *const orbx_keypoint, n2_dev: *const c_int, kp_stride: usize, matches: *const orbx_dmatch, n_dev: *const c_int, npairs: c_int, max_rows: c_int, pts1: *mut f32, pts2: *mut f32, bad_dev: *mut c_int) -> c_int;
     pub fn orbx_map_create(device: c_int, capacity: c_int, fx: f64, fy: f64, cx: f64, cy: f64, out: *mut *mut orbx_map) -> c_int;
     pub fn orbx_map_destroy(m: *mut orbx_map);
     pub fn orbx_map_size(m: *const orbx_map) -> c_int;

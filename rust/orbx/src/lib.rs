@@ -83,5 +83,15 @@ impl FeatureMatcher {
         out.truncate(n as usize);
         out
     }
+    /// odometry/pose.rs:27-44 (`PoseEstimator::extract_matched_points`): (points1, points2) as (x, y) pairs;
+    /// `Err` when a match index is outside its keypoint slice, like `Vector::get(..)?` in the reference.
+    pub fn extract_matched_points(&self, kp1: &[KeyPoint], kp2: &[KeyPoint], matches: &[DMatch]) -> Result<(Vec<[f32; 2]>, Vec<[f32; 2]>), Box<dyn Error>> {
+        let mut p1 = vec![[0f32; 2]; matches.len()];
+        let mut p2 = vec![[0f32; 2]; matches.len()];
+        if matches.is_empty() { return Ok((p1, p2)); }
+        let rc = unsafe { sys::orbx_extract_matched_points(self.h, kp1.as_ptr(), kp1.len() as i32, kp2.as_ptr(), kp2.len() as i32, matches.as_ptr(), matches.len() as i32, p1.as_mut_ptr() as *mut f32, p2.as_mut_ptr() as *mut f32) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((p1, p2))
+    }
 }
 impl Drop for FeatureMatcher { fn drop(&mut self) { unsafe { sys::orbx_matcher_destroy(self.h) } } }

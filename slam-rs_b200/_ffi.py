@@ -84,6 +84,8 @@ def _load():
         "orbx_ratio_test_batch": (i, [vp, vp, vp, vp, i, i, f, vp, vp]),
         "orbx_filter_good_matches": (i, [vp, vp, i, f, vp, vp]),
         "orbx_filter_good_matches_batch": (i, [vp, vp, vp, i, i, f, vp, vp]),
+        "orbx_extract_matched_points": (i, [vp, vp, i, vp, i, vp, i, vp, vp]),
+        "orbx_extract_matched_points_batch": (i, [vp, vp, vp, vp, vp, C.c_size_t, vp, vp, i, i, vp, vp, vp]),
         "orbx_matcher_set_timing": (i, [vp, i]),
         "orbx_matcher_timing": (i, [vp, C.POINTER(f), ip, i]),
         "orbx_last_error": (C.c_char_p, []),

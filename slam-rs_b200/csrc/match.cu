@@ -421,6 +421,31 @@ static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs, bool fused = fal
   return ORBX_OK;
 }
 
+
+// pts1[i] = kp1[matches[i].query_idx].pt, pts2[i] = kp2[matches[i].train_idx].pt  (pose.rs:36-41); problem p =
+// blockIdx.y.  Counts come from device arrays when given (batched form) or from the scalars.
+__global__ void matched_points_kernel(const orbx_keypoint* kp1, const int* n1_dev, int n1, const orbx_keypoint* kp2,
+                                      const int* n2_dev, int n2, size_t kp_stride, const orbx_dmatch* matches,
+                                      const int* n_dev, int n, int max_rows, float2* pts1, float2* pts2, int* bad) {
+  const int p = blockIdx.y;
+  const int nn = min(n_dev ? n_dev[p] : n, max_rows);
+  const unsigned c1 = (unsigned)(n1_dev ? n1_dev[p] : n1), c2 = (unsigned)(n2_dev ? n2_dev[p] : n2);
+  const orbx_keypoint* a = kp1 + (size_t)p * kp_stride;
+  const orbx_keypoint* b = kp2 + (size_t)p * kp_stride;
+  const size_t base = (size_t)p * max_rows;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nn; i += gridDim.x * blockDim.x) {
+    const orbx_dmatch m = matches[base + i];
+    if ((unsigned)m.query_idx >= c1 || (unsigned)m.train_idx >= c2) {  // Vector::get(..)? fails in the reference
+      atomicOr(bad, 1);
+      continue;
+    }
+    const orbx_keypoint& ka = a[m.query_idx];
+    const orbx_keypoint& kb = b[m.train_idx];
+    pts1[base + i] = make_float2(ka.x, ka.y);
+    pts2[base + i] = make_float2(kb.x, kb.y);
+  }
+}
+
 }  // namespace orbx
 
 using namespace orbx;
@@ -787,6 +812,67 @@ int orbx_filter_good_matches_batch(orbx_matcher* m, const orbx_dmatch* in, const
   ORBX_CUDA(cudaSetDevice(m->device));
   compact_kernel<<<npairs, kCompactThreads, 0, m->stream>>>(1, in, nullptr, nullptr, n_dev, 0, max_rows, ratio, out,
                                                            n_out_dev);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// SURVEY.md §8 f2 (first step): PoseEstimator::extract_matched_points
+// ------------------------------------------------------------------------------------------------
+int orbx_extract_matched_points(orbx_matcher* m, const orbx_keypoint* kp1, int n1, const orbx_keypoint* kp2, int n2,
+                                const orbx_dmatch* matches, int n, float* pts1, float* pts2) {
+  if (!m || n1 < 0 || n2 < 0 || n < 0 || (n > 0 && (!matches || !pts1 || !pts2 || !kp1 || !kp2))) {
+    set_error("orbx_extract_matched_points: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (n == 0) return ORBX_OK;
+  ORBX_CUDA(cudaSetDevice(m->device));
+  const void *d1, *d2, *dm;
+  int rc;
+  if ((rc = stage_in(m, B_Q, kp1, (size_t)n1 * sizeof(orbx_keypoint), &d1))) return rc;
+  if ((rc = stage_in(m, B_T, kp2, (size_t)n2 * sizeof(orbx_keypoint), &d2))) return rc;
+  if ((rc = stage_in(m, B_PART, matches, (size_t)n * sizeof(orbx_dmatch), &dm))) return rc;
+  const bool o1 = is_device_ptr(pts1), o2 = is_device_ptr(pts2);
+  if ((rc = ensure(m, B_CNT, sizeof(int)))) return rc;
+  if (!o1 && (rc = ensure(m, B_OUT, (size_t)n * sizeof(float2)))) return rc;
+  if (!o2 && (rc = ensure(m, B_OUT2, (size_t)n * sizeof(float2)))) return rc;
+  float2* p1 = o1 ? (float2*)pts1 : (float2*)m->buf[B_OUT];
+  float2* p2 = o2 ? (float2*)pts2 : (float2*)m->buf[B_OUT2];
+  ORBX_CUDA(cudaMemsetAsync(m->buf[B_CNT], 0, sizeof(int), m->stream));
+  matched_points_kernel<<<dim3(std::min(div_up(n, 256), 1024), 1), 256, 0, m->stream>>>(
+      (const orbx_keypoint*)d1, nullptr, n1, (const orbx_keypoint*)d2, nullptr, n2, 0, (const orbx_dmatch*)dm, nullptr,
+      n, n, p1, p2, (int*)m->buf[B_CNT]);
+  ORBX_LAUNCH_CHECK();
+  int bad = 0;
+  ORBX_CUDA(cudaMemcpyAsync(&bad, m->buf[B_CNT], sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+  if (!o1) ORBX_CUDA(cudaMemcpyAsync(pts1, p1, (size_t)n * sizeof(float2), cudaMemcpyDeviceToHost, m->stream));
+  if (!o2) ORBX_CUDA(cudaMemcpyAsync(pts2, p2, (size_t)n * sizeof(float2), cudaMemcpyDeviceToHost, m->stream));
+  ORBX_CUDA(cudaStreamSynchronize(m->stream));
+  if (bad) {
+    set_error("orbx_extract_matched_points: a match index is outside its keypoint array");
+    return ORBX_E_BADARG;
+  }
+  return ORBX_OK;
+}
+
+int orbx_extract_matched_points_batch(orbx_matcher* m, const orbx_keypoint* kp1, const int* n1_dev,
+                                      const orbx_keypoint* kp2, const int* n2_dev, size_t kp_stride,
+                                      const orbx_dmatch* matches, const int* n_dev, int npairs, int max_rows,
+                                      float* pts1, float* pts2, int* bad_dev) {
+  if (!m || npairs < 0 || max_rows < 0) {
+    set_error("orbx_extract_matched_points_batch: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (npairs == 0 || max_rows == 0) return ORBX_OK;
+  if (!is_device_ptr(kp1) || !is_device_ptr(kp2) || !is_device_ptr(n1_dev) || !is_device_ptr(n2_dev) ||
+      !is_device_ptr(matches) || !is_device_ptr(n_dev) || !is_device_ptr(pts1) || !is_device_ptr(pts2) ||
+      !is_device_ptr(bad_dev)) {
+    set_error("orbx_extract_matched_points_batch: device pointers required");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(m->device));
+  matched_points_kernel<<<dim3(std::min(div_up(max_rows, 256), 16), npairs), 256, 0, m->stream>>>(
+      kp1, n1_dev, 0, kp2, n2_dev, 0, kp_stride, matches, n_dev, 0, max_rows, (float2*)pts1, (float2*)pts2, bad_dev);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

@@ -254,7 +254,24 @@ class FeatureMatcher:
         check(lib.orbx_filter_good_matches(self._h, _ptr(m), len(m), ratio, _ptr(out), C.byref(n)))
         return out[:n.value]
 
+    def extract_matched_points(self, kp1, kp2, matches):
+        """pose.rs:27-44 — (points1, points2): float32 [n, 2] arrays, points1[i] = kp1[matches[i].query_idx].pt,
+        points2[i] = kp2[matches[i].train_idx].pt.  An out-of-range index raises (the reference returns Err)."""
+        k1, k2 = np.ascontiguousarray(kp1, KEYPOINT_DTYPE), np.ascontiguousarray(kp2, KEYPOINT_DTYPE)
+        m = np.ascontiguousarray(matches, DMATCH_DTYPE)
+        p1 = np.zeros((len(m), 2), np.float32)
+        p2 = np.zeros((len(m), 2), np.float32)
+        check(lib.orbx_extract_matched_points(self._h, _ptr(k1), len(k1), _ptr(k2), len(k2), _ptr(m), len(m),
+                                              _ptr(p1), _ptr(p2)))
+        return p1, p2
+
     # ------------------------------------------------------------------ device / batched interface
+    def extract_matched_points_batch_device(self, kp1, n1, kp2, n2, kp_stride, matches, n, npairs, max_rows, pts1,
+                                            pts2, bad):
+        check(lib.orbx_extract_matched_points_batch(self._h, _ptr(kp1), _ptr(n1), _ptr(kp2), _ptr(n2), kp_stride,
+                                                    _ptr(matches), _ptr(n), npairs, max_rows, _ptr(pts1), _ptr(pts2),
+                                                    _ptr(bad)))
+
     def knn_match_batch_device(self, q, q_stride, nq, t, t_stride, nt, npairs, max_rows, out, n_per_q):
         check(lib.orbx_knn_match2_batch(self._h, _ptr(q), q_stride, _ptr(nq), _ptr(t), t_stride, _ptr(nt), npairs,
                                         max_rows, _ptr(out), _ptr(n_per_q)))

@@ -20,7 +20,7 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
                  ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None,
-                 dual=False):
+                 dual=False, points=False):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
@@ -51,6 +51,12 @@ class SequenceFrontEnd:
             self.n_m1 = torch.zeros((T,), dtype=i32, device=self.dev)
             self.ref_good = torch.zeros((T, cap, 16), dtype=u8, device=self.dev)
             self.n_ref_good = torch.zeros((T,), dtype=i32, device=self.dev)
+        # points=True: also emit PoseEstimator::extract_matched_points (pose.rs:27-44) of every pair's good matches
+        self.points = bool(points)
+        if self.points:
+            self.pts1 = torch.zeros((T, cap, 2), dtype=torch.float32, device=self.dev)
+            self.pts2 = torch.zeros((T, cap, 2), dtype=torch.float32, device=self.dev)
+            self.bad_index = torch.zeros((1,), dtype=i32, device=self.dev)
         # staging for the host path
         self.frames_dev = torch.zeros((T, self.h, self.pitch), dtype=u8, device=self.dev)
         self.copy_stream = torch.cuda.Stream(device=self.dev)
@@ -97,6 +103,10 @@ class SequenceFrontEnd:
                                  self.knn[a], self.n_per_q[a])
         m.ratio_test_batch_device(self.knn[a], self.n_per_q[a], self.n[a - 1:], npairs, cap, self.ratio, self.good[a],
                                   self.n_good[a:])
+        if self.points:
+            m.extract_matched_points_batch_device(self.kps[a - 1], self.n[a - 1:], self.kps[a], self.n[a:], cap,
+                                                  self.good[a], self.n_good[a:], npairs, cap, self.pts1[a],
+                                                  self.pts2[a], self.bad_index)
         if self.reference_filter:
             m.match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs,
                                  cap, self.m1[a], self.n_m1[a:])
@@ -216,6 +226,11 @@ class SequenceFrontEnd:
         """Good matches of pair (t-1, t) as a numpy DMatch array (synchronises)."""
         n = int(self.n_good[t].item())
         return self.good[t, :n].cpu().numpy().view(DMATCH_DTYPE).reshape(-1)
+
+    def pair_points(self, t):
+        """(points1, points2) of pair (t-1, t): float32 [n_good, 2] each (synchronises)."""
+        n = int(self.n_good[t].item())
+        return self.pts1[t, :n].cpu().numpy(), self.pts2[t, :n].cpu().numpy()
 
     def pair_knn(self, t):
         nq = min(int(self.n[t - 1].item()), self.cap)

@@ -269,3 +269,45 @@ def test_cross_check_fused_vs_oracle(orbx, nq, nt, seed):
     if cv_ref.HAVE_CV2 and nt < 262144 and nq < 5000:
         x = cv_ref.match_k1(q, t, cross_check=True)
         assert np.array_equal(out["query_idx"], x[:, 0]) and np.array_equal(out["train_idx"], x[:, 1])
+
+
+def test_extract_matched_points(orbx):
+    """PoseEstimator::extract_matched_points (pose.rs:27-44) through the C ABI: host arrays, the batched device
+    form inside the sequence front end, the empty case and the reference's out-of-range error."""
+    import torch
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 5, 200, 320, 400
+    seq = synth.sequence(h, w, T, canvas_seed=91)
+    fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=T, points=True)
+    dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
+    dev[:, :, :w] = torch.from_numpy(seq).cuda()
+    fe.run_device(dev)
+    torch.cuda.synchronize()
+    assert int(fe.bad_index.item()) == 0
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics(718.856, 718.856, 607.1928, 185.2157))
+    assert pe.min_matches == 8
+    total = 0
+    for t in range(1, T):
+        k0, _ = fe.frame_result(t - 1)
+        k1, _ = fe.frame_result(t)
+        good = fe.pair_result(t)
+        xy0 = np.stack([k0["x"], k0["y"]], 1)
+        xy1 = np.stack([k1["x"], k1["y"]], 1)
+        want1, want2 = R.extract_matched_points(xy0, xy1, np.stack([good["query_idx"], good["train_idx"]], 1))
+        got1, got2 = fe.pair_points(t)                       # batched device form
+        assert np.array_equal(got1, want1) and np.array_equal(got2, want2)
+        h1, h2 = pe.extract_matched_points(k0, k1, good)     # host-array form, reference method name
+        assert np.array_equal(h1, want1) and np.array_equal(h2, want2)
+        total += len(good)
+    assert total > 50
+    # empty match list -> two empty lists
+    e1, e2 = pe.extract_matched_points(k0, k1, good[:0])
+    assert e1.shape == (0, 2) and e2.shape == (0, 2)
+    # an index past the keypoint array is an error in the reference (`kp1.get(idx)?`)
+    bad = good[:3].copy()
+    bad["train_idx"][1] = len(k1)
+    with pytest.raises(orbx.OrbxError):
+        pe.extract_matched_points(k0, k1, bad)
+    bad["train_idx"][1] = -1
+    with pytest.raises(orbx.OrbxError):
+        pe.extract_matched_points(k0, k1, bad)

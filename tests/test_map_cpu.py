@@ -36,3 +36,19 @@ def test_find_matches_semantics():
     want = [(i, int(D[k].argmin())) for k, i in enumerate(ids) if D[k].min() < thr]
     assert [tuple(r) for r in out.tolist()] == want
     assert len(R.map_find_matches(pts, mp, has, alive, np.eye(3), np.zeros(3), KITTI, fr[:0])) == 0
+
+
+def test_extract_matched_points_restatement():
+    """oracle/restated.py::extract_matched_points == pose.rs:27-44 (a plain gather; out of range -> error)."""
+    import pytest
+    kp1 = np.arange(10, dtype=np.float32).reshape(5, 2)
+    kp2 = 100 + np.arange(8, dtype=np.float32).reshape(4, 2)
+    m = np.array([[4, 0], [0, 3], [2, 2]])
+    p1, p2 = R.extract_matched_points(kp1, kp2, m)
+    assert np.array_equal(p1, kp1[[4, 0, 2]]) and np.array_equal(p2, kp2[[0, 3, 2]])
+    e1, e2 = R.extract_matched_points(kp1, kp2, m[:0])
+    assert e1.shape == (0, 2) and e2.shape == (0, 2)
+    with pytest.raises(IndexError):
+        R.extract_matched_points(kp1, kp2, np.array([[5, 0]]))
+    with pytest.raises(IndexError):
+        R.extract_matched_points(kp1, kp2, np.array([[0, -1]]))
