@@ -68,6 +68,8 @@ __device__ __forceinline__ float harris_from_words(const unsigned* wds, unsigned
 constexpr int kHarrisBlocksPerLevel = 4;
 constexpr int kHarrisWarps = 8;
 constexpr int kHarrisSlab = 27;  // 27 words per candidate; odd stride = conflict-free per-thread reads
+constexpr int kHarrisScan = 128;  // candidates scanned per warp iteration (4 independent loads per lane)
+constexpr int kHarrisQueue = 32 + kHarrisScan;
 
 // Largest bin b >= 1 of a 256-bin histogram with sum_{i >= b} hist[i] >= rem (0 if there is none), and the
 // count strictly above it.  Block-wide (>= 256 threads), replaces a 256-step serial scan by thread 0.
@@ -116,8 +118,9 @@ __device__ __forceinline__ void find_bin_desc(const uint32_t* hist, uint32_t rem
 __global__ void __launch_bounds__(kHarrisWarps * 32, 2) harris_kernel(DevGeom g) {
   __shared__ uint32_t s_hist[256];
   __shared__ uint32_t s_scratch[10];
-  __shared__ uint32_t s_queue[kHarrisWarps][64];
-  __shared__ unsigned s_win[kHarrisWarps][32 * kHarrisSlab];
+  __shared__ uint32_t s_queue[kHarrisWarps][kHarrisQueue];
+  extern __shared__ unsigned s_win_dyn[];  // [kHarrisWarps][2][32 * kHarrisSlab] window slabs (54 KB: opt-in size)
+  unsigned(*s_win)[2][32 * kHarrisSlab] = reinterpret_cast<unsigned(*)[2][32 * kHarrisSlab]>(s_win_dyn);
   const int l = blockIdx.y, frame = blockIdx.z;
   const DevLevel& L = g.lv[l];
   const size_t fl = (size_t)frame * kMaxLevels + l;
@@ -142,88 +145,112 @@ __global__ void __launch_bounds__(kHarrisWarps * 32, 2) harris_kernel(DevGeom g)
   const int pitch = L.pitch;
   const bool aligned = L.aligned4 != 0;
 
-  // slice of this warp (multiple of 32 candidates)
+  // slice of this warp (multiple of kHarrisScan candidates)
   const uint32_t nwarps = gridDim.x * kHarrisWarps;
-  const uint32_t per_warp = ((count + nwarps - 1) / nwarps + 31u) & ~31u;
+  const uint32_t per_warp = ((count + nwarps - 1) / nwarps + kHarrisScan - 1u) / kHarrisScan * kHarrisScan;
   const uint32_t begin = (blockIdx.x * kHarrisWarps + warp) * per_warp;
   const uint32_t end = min(count, begin + per_warp);
   if (begin >= end) return;
   uint32_t* q = s_queue[warp];
-  unsigned* win = s_win[warp];
-  const unsigned win_sa = (unsigned)__cvta_generic_to_shared(win);
+  const unsigned lt = (1u << lane) - 1u;
 
-  auto process = [&](int nloc) {
-    // candidates q[0 .. nloc) : cooperative window fetch, then one candidate per lane
-    uint32_t j = 0, cw = 0;
-    if (lane < nloc) {
-      j = q[lane];
-      cw = cand[j];
-    }
+  // Software pipeline per warp: scan (4 coalesced loads in flight per lane) until 32 survivors are queued,
+  // issue their window fetch into slab `buf` (27 cp.async per lane, no wait), then compute the batch fetched one
+  // round earlier from the other slab.  One issue site and one compute site keep the register count down.
+  uint32_t base = begin, qn = 0, qhead = 0;
+  int pend_n = 0, buf = 0;
+  uint32_t pend_j = 0, pend_cw = 0;
+  for (;;) {
+    while (qn < 32 && base < end) {
+      uint32_t cw4[kHarrisScan / 32];
 #pragma unroll
-    for (int t = 0; t < 27; ++t) {
-      const int i = lane + 32 * t;
-      const int cidx = i / 27, wd = i - cidx * 27;
-      const int wrow = wd / 3, wword = wd - wrow * 3;
-      const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
-      if (cidx < nloc) {
-        const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
-        const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
-        if (aligned) {
-          const uint8_t* src = p - ((uintptr_t)p & 3) + 4 * wword;
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(win_sa + 4 * i), "l"(src));
-        } else {
-          const uint8_t* b = p + 4 * wword;
-          win[i] = (unsigned)__ldg(b) | ((unsigned)__ldg(b + 1) << 8) | ((unsigned)__ldg(b + 2) << 16) |
-                   ((unsigned)__ldg(b + 3) << 24);
+      for (int k = 0; k < kHarrisScan / 32; ++k) {
+        const uint32_t i = base + 32 * k + lane;
+        cw4[k] = i < end ? cand[i] : 0u;
+      }
+#pragma unroll
+      for (int k = 0; k < kHarrisScan / 32; ++k) {
+        const uint32_t i = base + 32 * k + lane;
+        const bool pass = i < end && (int)(cw4[k] >> 24) >= thr;
+        if (i < end && !pass) key[i] = 0;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
+        if (pass) q[qhead + qn + __popc(bal & lt)] = i;
+        qn += __popc(bal);
+      }
+      base += kHarrisScan;
+      __syncwarp();
+    }
+    const int take = (int)min(qn, 32u);
+    uint32_t j = 0, cw = 0;
+    if (take) {
+      // candidates q[qhead .. qhead + take): cooperative window fetch (word i = lane + 32t -> candidate i/27,
+      // row (i%27)/3, aligned word (i%27)%3)
+      if (lane < take) {
+        j = q[qhead + lane];
+        cw = cand[j];
+      }
+      unsigned* win = s_win[warp][buf];
+      const unsigned win_sa = (unsigned)__cvta_generic_to_shared(win);
+#pragma unroll
+      for (int t = 0; t < 27; ++t) {
+        const int i = lane + 32 * t;
+        const int cidx = i / 27, wd = i - cidx * 27;
+        const int wrow = wd / 3, wword = wd - wrow * 3;
+        const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
+        if (cidx < take) {
+          const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
+          const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
+          if (aligned) {
+            const uint8_t* src = p - ((uintptr_t)p & 3) + 4 * wword;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(win_sa + 4 * i), "l"(src));
+          } else {
+            const uint8_t* b = p + 4 * wword;
+            win[i] = (unsigned)__ldg(b) | ((unsigned)__ldg(b + 1) << 8) | ((unsigned)__ldg(b + 2) << 16) |
+                     ((unsigned)__ldg(b + 3) << 24);
+          }
         }
       }
+      asm volatile("cp.async.commit_group;\n" ::);
+      qhead += take;
+      qn -= take;
     }
-    asm volatile("cp.async.commit_group;\n" ::);
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-    __syncwarp();
-    if (lane < nloc) {
-      const int x = (int)(cw & 0xFFF), y = (int)((cw >> 12) & 0xFFF);
-      const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
-      const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
-      key[j] = float_key(harris_from_words(win + lane * kHarrisSlab, boff));
-    }
-    __syncwarp();
-  };
-
-  uint32_t qn = 0;
-  for (uint32_t base = begin;; base += 32) {
-    const bool more = base < end;
-    if (more) {
-      const uint32_t i = base + lane;
-      bool pass = false;
-      if (i < end) {
-        pass = (int)(cand[i] >> 24) >= thr;
-        if (!pass) key[i] = 0;
+    if (pend_n) {
+      if (take)
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+      else
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+      __syncwarp();
+      if (lane < pend_n) {
+        const int x = (int)(pend_cw & 0xFFF), y = (int)((pend_cw >> 12) & 0xFFF);
+        const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
+        const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
+        key[pend_j] = float_key(harris_from_words(s_win[warp][buf ^ 1] + lane * kHarrisSlab, boff));
       }
-      const unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
-      if (pass) q[qn + __popc(bal & ((1u << lane) - 1u))] = i;
-      qn += __popc(bal);
       __syncwarp();
     }
-    if (qn >= 32 || (!more && qn > 0)) {
-      const uint32_t take = min(qn, 32u);
-      process((int)take);
-      const uint32_t rest = qn - take;
+    if (!take) break;  // input exhausted, queue empty, pipeline drained
+    pend_n = take;
+    pend_j = j;
+    pend_cw = cw;
+    buf ^= 1;
+    // keep the queue short: move the (< 32) leftovers to the front once the head has advanced
+    if (qn < 32 && qhead) {
       uint32_t tmp = 0;
-      if (lane < rest) tmp = q[32 + lane];
+      if (lane < qn) tmp = q[qhead + lane];
       __syncwarp();
-      if (lane < rest) q[lane] = tmp;
-      qn = rest;
+      if (lane < qn) q[lane] = tmp;
+      qhead = 0;
       __syncwarp();
     }
-    if (!more && qn == 0) break;
   }
 }
 
 int launch_harris(const DevGeom& g, cudaStream_t s) {
   if (g.batch == 0) return ORBX_OK;
   dim3 grid(kHarrisBlocksPerLevel, g.nlevels, g.batch);
-  harris_kernel<<<grid, 256, 0, s>>>(g);
+  constexpr int kSmem = kHarrisWarps * 2 * 32 * kHarrisSlab * (int)sizeof(unsigned);
+  ORBX_CUDA(cudaFuncSetAttribute(harris_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  harris_kernel<<<grid, 256, kSmem, s>>>(g);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }
