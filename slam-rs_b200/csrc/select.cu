@@ -110,6 +110,104 @@ __device__ __forceinline__ void find_bin_desc(const uint32_t* hist, uint32_t rem
   above = scratch[9];
 }
 
+// Per-warp body of harris_kernel (ALIGNED: the level's base, pitch and frame stride are 4-byte aligned, so window
+// words can be fetched with cp.async; otherwise they are assembled from byte loads).
+template <bool ALIGNED>
+__device__ __forceinline__ void harris_warp_loop(const uint32_t* __restrict__ cand, uint32_t* __restrict__ key,
+                                                 const uint8_t* __restrict__ img, int pitch, int thr, uint32_t begin,
+                                                 uint32_t end, uint32_t* q, unsigned* win0, int lane) {
+  const unsigned lt = (1u << lane) - 1u;
+
+  // Software pipeline per warp: scan (4 coalesced loads in flight per lane) until 32 survivors are queued,
+  // issue their window fetch into slab `buf` (27 cp.async per lane, no wait), then compute the batch fetched one
+  // round earlier from the other slab.  One issue site and one compute site keep the register count down.
+  uint32_t base = begin, qn = 0, qhead = 0;
+  int pend_n = 0, buf = 0;
+  uint32_t pend_j = 0;
+  unsigned pend_boff = 0;
+  for (;;) {
+    while (qn < 32 && base < end) {
+      uint32_t cw4[kHarrisScan / 32];
+#pragma unroll
+      for (int k = 0; k < kHarrisScan / 32; ++k) {
+        const uint32_t i = base + 32 * k + lane;
+        cw4[k] = i < end ? cand[i] : 0u;
+      }
+#pragma unroll
+      for (int k = 0; k < kHarrisScan / 32; ++k) {
+        const uint32_t i = base + 32 * k + lane;
+        const bool pass = i < end && (int)(cw4[k] >> 24) >= thr;
+        if (i < end && !pass) key[i] = 0;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
+        if (pass) q[qhead + qn + __popc(bal & lt)] = i;
+        qn += __popc(bal);
+      }
+      base += kHarrisScan;
+      __syncwarp();
+    }
+    const int take = (int)min(qn, 32u);
+    uint32_t j = 0, cw = 0;
+    unsigned off0 = 0;  // byte offset of the window's top-left pixel from img
+    if (take) {
+      // candidates q[qhead .. qhead + take): cooperative window fetch (word i = lane + 32t -> candidate i/27,
+      // row (i%27)/3, aligned word (i%27)%3)
+      if (lane < take) {
+        j = q[qhead + lane];
+        cw = cand[j];
+        off0 = (unsigned)(((int)((cw >> 12) & 0xFFF) - 4) * pitch + (int)(cw & 0xFFF) - 4);
+      }
+      unsigned* win = win0 + buf * (32 * kHarrisSlab);
+      const unsigned win_sa = (unsigned)__cvta_generic_to_shared(win);
+#pragma unroll
+      for (int t = 0; t < 27; ++t) {
+        const int i = lane + 32 * t;
+        const int cidx = i / 27, wd = i - cidx * 27;
+        const int wrow = wd / 3, wword = wd - wrow * 3;
+        const unsigned o = __shfl_sync(0xFFFFFFFFu, off0, cidx);
+        if (cidx < take) {
+          if (ALIGNED) {
+            // img, pitch and the frame stride are 4-byte aligned: the aligned word holding the pixel
+            const uint8_t* src = img + ((o & ~3u) + (unsigned)(wrow * pitch + 4 * wword));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(win_sa + 4 * i), "l"(src));
+          } else {
+            const uint8_t* b = img + (o + (unsigned)(wrow * pitch + 4 * wword));
+            win[i] = (unsigned)__ldg(b) | ((unsigned)__ldg(b + 1) << 8) | ((unsigned)__ldg(b + 2) << 16) |
+                     ((unsigned)__ldg(b + 3) << 24);
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;\n" ::);
+      qhead += take;
+      qn -= take;
+    }
+    if (pend_n) {
+      if (take)
+        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+      else
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+      __syncwarp();
+      if (lane < pend_n) {
+        key[pend_j] = float_key(harris_from_words(win0 + (buf ^ 1) * (32 * kHarrisSlab) + lane * kHarrisSlab, pend_boff));
+      }
+      __syncwarp();
+    }
+    if (!take) break;  // input exhausted, queue empty, pipeline drained
+    pend_n = take;
+    pend_j = j;
+    pend_boff = ALIGNED ? (off0 & 3u) : 0u;
+    buf ^= 1;
+    // keep the queue short: move the (< 32) leftovers to the front once the head has advanced
+    if (qn < 32 && qhead) {
+      uint32_t tmp = 0;
+      if (lane < qn) tmp = q[qhead + lane];
+      __syncwarp();
+      if (lane < qn) q[lane] = tmp;
+      qhead = 0;
+      __syncwarp();
+    }
+  }
+}
+
 // S3 threshold from the score histogram (parallel suffix scan), then Harris on the survivors.  After the
 // threshold every warp works alone on its slice of the candidate list: ballot-compacts survivors into a
 // warp-private queue and, 32 at a time, fetches the 9x9 windows with cp.async (word i = lane + 32t ->
@@ -151,98 +249,10 @@ __global__ void __launch_bounds__(kHarrisWarps * 32, 2) harris_kernel(DevGeom g)
   const uint32_t begin = (blockIdx.x * kHarrisWarps + warp) * per_warp;
   const uint32_t end = min(count, begin + per_warp);
   if (begin >= end) return;
-  uint32_t* q = s_queue[warp];
-  const unsigned lt = (1u << lane) - 1u;
-
-  // Software pipeline per warp: scan (4 coalesced loads in flight per lane) until 32 survivors are queued,
-  // issue their window fetch into slab `buf` (27 cp.async per lane, no wait), then compute the batch fetched one
-  // round earlier from the other slab.  One issue site and one compute site keep the register count down.
-  uint32_t base = begin, qn = 0, qhead = 0;
-  int pend_n = 0, buf = 0;
-  uint32_t pend_j = 0, pend_cw = 0;
-  for (;;) {
-    while (qn < 32 && base < end) {
-      uint32_t cw4[kHarrisScan / 32];
-#pragma unroll
-      for (int k = 0; k < kHarrisScan / 32; ++k) {
-        const uint32_t i = base + 32 * k + lane;
-        cw4[k] = i < end ? cand[i] : 0u;
-      }
-#pragma unroll
-      for (int k = 0; k < kHarrisScan / 32; ++k) {
-        const uint32_t i = base + 32 * k + lane;
-        const bool pass = i < end && (int)(cw4[k] >> 24) >= thr;
-        if (i < end && !pass) key[i] = 0;
-        const unsigned bal = __ballot_sync(0xFFFFFFFFu, pass);
-        if (pass) q[qhead + qn + __popc(bal & lt)] = i;
-        qn += __popc(bal);
-      }
-      base += kHarrisScan;
-      __syncwarp();
-    }
-    const int take = (int)min(qn, 32u);
-    uint32_t j = 0, cw = 0;
-    if (take) {
-      // candidates q[qhead .. qhead + take): cooperative window fetch (word i = lane + 32t -> candidate i/27,
-      // row (i%27)/3, aligned word (i%27)%3)
-      if (lane < take) {
-        j = q[qhead + lane];
-        cw = cand[j];
-      }
-      unsigned* win = s_win[warp][buf];
-      const unsigned win_sa = (unsigned)__cvta_generic_to_shared(win);
-#pragma unroll
-      for (int t = 0; t < 27; ++t) {
-        const int i = lane + 32 * t;
-        const int cidx = i / 27, wd = i - cidx * 27;
-        const int wrow = wd / 3, wword = wd - wrow * 3;
-        const uint32_t cwc = __shfl_sync(0xFFFFFFFFu, cw, cidx);
-        if (cidx < take) {
-          const int x = (int)(cwc & 0xFFF), y = (int)((cwc >> 12) & 0xFFF);
-          const uint8_t* p = img + (size_t)(y - 4 + wrow) * pitch + (x - 4);
-          if (aligned) {
-            const uint8_t* src = p - ((uintptr_t)p & 3) + 4 * wword;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(win_sa + 4 * i), "l"(src));
-          } else {
-            const uint8_t* b = p + 4 * wword;
-            win[i] = (unsigned)__ldg(b) | ((unsigned)__ldg(b + 1) << 8) | ((unsigned)__ldg(b + 2) << 16) |
-                     ((unsigned)__ldg(b + 3) << 24);
-          }
-        }
-      }
-      asm volatile("cp.async.commit_group;\n" ::);
-      qhead += take;
-      qn -= take;
-    }
-    if (pend_n) {
-      if (take)
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-      else
-        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-      __syncwarp();
-      if (lane < pend_n) {
-        const int x = (int)(pend_cw & 0xFFF), y = (int)((pend_cw >> 12) & 0xFFF);
-        const uint8_t* p0 = img + (size_t)(y - 4) * pitch + (x - 4);
-        const unsigned boff = aligned ? (unsigned)((uintptr_t)p0 & 3) : 0u;
-        key[pend_j] = float_key(harris_from_words(s_win[warp][buf ^ 1] + lane * kHarrisSlab, boff));
-      }
-      __syncwarp();
-    }
-    if (!take) break;  // input exhausted, queue empty, pipeline drained
-    pend_n = take;
-    pend_j = j;
-    pend_cw = cw;
-    buf ^= 1;
-    // keep the queue short: move the (< 32) leftovers to the front once the head has advanced
-    if (qn < 32 && qhead) {
-      uint32_t tmp = 0;
-      if (lane < qn) tmp = q[qhead + lane];
-      __syncwarp();
-      if (lane < qn) q[lane] = tmp;
-      qhead = 0;
-      __syncwarp();
-    }
-  }
+  if (aligned)
+    harris_warp_loop<true>(cand, key, img, pitch, thr, begin, end, s_queue[warp], s_win[warp][0], lane);
+  else
+    harris_warp_loop<false>(cand, key, img, pitch, thr, begin, end, s_queue[warp], s_win[warp][0], lane);
 }
 
 int launch_harris(const DevGeom& g, cudaStream_t s) {
