@@ -405,7 +405,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kOrientWarps = 8;
-constexpr int kOrientPerWarp = 4;
+constexpr int kOrientPerWarp = 8;
 
 __device__ __forceinline__ int dp4a_us(unsigned a, unsigned b_signed_bytes, int c) {
   int d;
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
     cm[k] = wm;
   }
 
-  __shared__ unsigned s_patch[kOrientWarps][31 * 9 + 1];
+  __shared__ unsigned s_patch[kOrientWarps][2][31 * 9 + 1];  // two slabs: keypoint it+1 is fetched while it computes
   // staging geometry of this lane: word i = lane + 32t of the 31 x 9 patch
   int st_row[9], st_word[9];
 #pragma unroll
@@ -461,46 +461,69 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
     st_word[t] = i - st_row[t] * 9;
   }
 
-  for (int it = 0; it < kOrientPerWarp; ++it) {
-    const uint32_t j = (blockIdx.x * kOrientPerWarp + it) * kOrientWarps + warp;
-    if (j >= limit) return;
-    int l = 0;
-    uint32_t first = 0;
+  // keypoint `it` of this warp: look it up and start the fetch of its patch (cp.async, one group per keypoint;
+  // an empty group when there is nothing to fetch, so that "all but the newest group" always means "mine")
+  struct Item {
+    unsigned long long e;
+    uint32_t j;
+    int l, x, y;
+    unsigned off;
+    bool valid, aligned;
+  };
+  auto fetch = [&](int it) {
+    Item k;
+    k.j = (blockIdx.x * kOrientPerWarp + it) * kOrientWarps + warp;
+    k.valid = it < kOrientPerWarp && k.j < limit;
+    k.l = 0, k.x = 0, k.y = 0, k.off = 0, k.e = 0, k.aligned = false;
+    if (k.valid) {
+      uint32_t first = 0;
 #pragma unroll
-    for (int i = 1; i < kMaxLevels; ++i)
-      if (j >= pre[i]) {
-        l = i;
-        first = pre[i];
+      for (int i = 1; i < kMaxLevels; ++i)
+        if (k.j >= pre[i]) {
+          k.l = i;
+          first = pre[i];
+        }
+      const DevLevel& L = g.lv[k.l];
+      k.e = L.sel[(size_t)frame * L.sel_cap + (k.j - first)];
+      const uint32_t pos = 0xFFFFFFu - (uint32_t)(k.e & 0xFFFFFFu);
+      k.x = (int)(pos & 0xFFF), k.y = (int)(pos >> 12);
+      k.aligned = L.aligned4 != 0;
+      if (k.aligned) {
+        // all rows share the alignment of row 0 (pitch and stride are multiples of 4)
+        const int pitch = L.pitch;
+        const uint8_t* seg0 = L.img + (size_t)frame * L.frame_stride + (size_t)(k.y - 15) * pitch + (k.x - 15);
+        k.off = (unsigned)((uintptr_t)seg0 & 3);
+        const uint8_t* base = seg0 - k.off;
+        const unsigned sa = (unsigned)__cvta_generic_to_shared(&s_patch[warp][it & 1][lane]);
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+          if (t < 8 || lane < 279 - 256)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sa + 128 * t),
+                         "l"(base + (size_t)st_row[t] * pitch + 4 * st_word[t]));
       }
-    const DevLevel& L = g.lv[l];
-    const unsigned long long e = L.sel[(size_t)frame * L.sel_cap + (j - first)];
-    const uint32_t pos = 0xFFFFFFu - (uint32_t)(e & 0xFFFFFFu);
-    const int x = (int)(pos & 0xFFF), y = (int)(pos >> 12);
-    const int pitch = L.pitch;
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+    return k;
+  };
 
-    const uint8_t* seg = L.img + (size_t)frame * L.frame_stride + (size_t)(y + v) * pitch + (x - 15);
+  Item cur = fetch(0);
+#pragma unroll 1
+  for (int it = 0; it < kOrientPerWarp; ++it) {
+    const Item nxt = fetch(it + 1);
+    if (!cur.valid) return;  // j grows with it: nothing further either
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+    __syncwarp();
+    const DevLevel& L = g.lv[cur.l];
+    const int x = cur.x, y = cur.y, l = cur.l;
     unsigned a[8];
-    if (L.aligned4) {
-      // all rows share the alignment of row 0 (pitch and stride are multiples of 4)
-      const uint8_t* seg0 = L.img + (size_t)frame * L.frame_stride + (size_t)(y - 15) * pitch + (x - 15);
-      const unsigned off = (unsigned)((uintptr_t)seg0 & 3);
-      const uint8_t* base = seg0 - off;
-      unsigned stg[9];
-#pragma unroll
-      for (int t = 0; t < 9; ++t)
-        if (t < 8 || lane < 279 - 256)
-          stg[t] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)st_row[t] * pitch) + st_word[t]);
-      __syncwarp();  // previous keypoint's reads are done
-#pragma unroll
-      for (int t = 0; t < 9; ++t)
-        if (t < 8 || lane < 279 - 256) s_patch[warp][lane + 32 * t] = stg[t];
-      __syncwarp();
+    if (cur.aligned) {
       unsigned w[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) w[k] = s_patch[warp][min(lane, 30) * 9 + k];
+      for (int k = 0; k < 9; ++k) w[k] = s_patch[warp][it & 1][min(lane, 30) * 9 + k];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) a[k] = __funnelshift_r(w[k], w[k + 1], 8 * off);
+      for (int k = 0; k < 8; ++k) a[k] = __funnelshift_r(w[k], w[k + 1], 8 * cur.off);
     } else {
+      const uint8_t* seg = L.img + (size_t)frame * L.frame_stride + (size_t)(y + v) * L.pitch + (x - 15);
 #pragma unroll
       for (int k = 0; k < 8; ++k)
         a[k] = (unsigned)__ldg(seg + 4 * k) | ((unsigned)__ldg(seg + 4 * k + 1) << 8) |
@@ -515,7 +538,7 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
     const int m10 = __reduce_add_sync(0xFFFFFFFFu, ru);
     const int m01 = __reduce_add_sync(0xFFFFFFFFu, v * rs);
     if (lane == 0) {
-      const float response = key_float((uint32_t)(e >> 32));
+      const float response = key_float((uint32_t)(cur.e >> 32));
       orbx_keypoint kp;
       kp.x = __fmul_rn((float)x, L.scale);
       kp.y = __fmul_rn((float)y, L.scale);
@@ -524,9 +547,11 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
       kp.response = response;
       kp.octave = l;
       kp.class_id = -1;
-      o.kps[(size_t)frame * o.cap + j] = kp;
-      o.kp_lvl[(size_t)frame * o.lvl_cap + j] = ((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+      o.kps[(size_t)frame * o.cap + cur.j] = kp;
+      o.kp_lvl[(size_t)frame * o.lvl_cap + cur.j] = ((uint32_t)l << 24) | ((uint32_t)y << 12) | (uint32_t)x;
     }
+    __syncwarp();  // slab it & 1 is free for keypoint it + 2
+    cur = nxt;
   }
 }
 
