@@ -24,22 +24,90 @@ __device__ __forceinline__ int reflect101(int i, int n) {
   return min(max(i, 0), n - 1);
 }
 
-// Blur tile = 128 x 32 output pixels owned by ONE warp (4 independent warps per block, no block barrier):
-// the warp stages the 136 x 38 byte source footprint (reflect-101 applied while staging, aligned 32-bit
-// loads wherever the word lies inside the row) in its private shared-memory slab, then every lane walks
-// down its 4-pixel column: per source row 3 LDS.32 -> 10 bytes -> fp32 (PRMT into the mantissa of 2^23,
+// Blur tile = 128 x 35 output pixels owned by ONE warp (4 independent warps per block, no block barrier):
+// the warp stages the 136 x 41 byte source footprint in its private shared-memory slab - every aligned word
+// that lies inside the row's allocation goes global -> shared with cp.async (all rows in flight at once),
+// the reflect-101 columns of border tiles are then patched shared -> shared by lane = row - and every lane
+// walks down its 4-pixel column: per source row 3 LDS.32 -> 10 bytes -> fp32 (PRMT into the mantissa of 2^23,
 // one FADD), the 7-tap row pass for 4 pixels (28 FMA-pipe ops), and - from a 7-row register window - the
 // symmetric column pass, round-half-even by the 1.5*2^23 magic add, and one coalesced 32-bit store.
-// FMA-pipe bound at ~19 fp32 ops per pixel; HBM traffic is read P + write P.
+// 41 = 6 + 5 * 7 source rows: a full tile runs the 7-way unrolled steady loop without per-row bounds checks.
+// FMA-pipe / issue bound at ~19 fp32 ops per pixel; HBM traffic is read P + write P.
 constexpr int kBlurWarps = 4;
-constexpr int kBlurSrcRows = kBlurTileH + 6;       // 38
+constexpr int kBlurSrcRows = kBlurTileH + 6;       // 41
 constexpr int kBlurSrcWords = kBlurTileW / 4 + 2;  // 34 words: image columns x0-4 .. x0+131
+static_assert(kBlurTileH % 7 == 0, "the steady loop is unrolled over the 7-row register window");
 
 __device__ __forceinline__ float byte_to_float(unsigned w, int i) {
   return __fsub_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650 + i)), 8388608.0f);
 }
 
-__global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
+// row pass (OpenCV order) of the 4 pixels of this lane: acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc), j = 1..6
+__device__ __forceinline__ void blur_row_pass(const unsigned* p, float (&r)[4], float k0, float k1, float k2, float k3) {
+  const unsigned w0 = p[0], w1 = p[1], w2 = p[2];
+  float f[10];
+  f[0] = byte_to_float(w0, 1);
+  f[1] = byte_to_float(w0, 2);
+  f[2] = byte_to_float(w0, 3);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) f[3 + i] = byte_to_float(w1, i);
+  f[7] = byte_to_float(w2, 0);
+  f[8] = byte_to_float(w2, 1);
+  f[9] = byte_to_float(w2, 2);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float acc = __fmul_rn(k0, f[i]);
+    acc = __fmaf_rn(k1, f[i + 1], acc);
+    acc = __fmaf_rn(k2, f[i + 2], acc);
+    acc = __fmaf_rn(k3, f[i + 3], acc);
+    acc = __fmaf_rn(k2, f[i + 4], acc);
+    acc = __fmaf_rn(k1, f[i + 5], acc);
+    acc = __fmaf_rn(k0, f[i + 6], acc);
+    r[i] = acc;
+  }
+}
+
+// the walk down the slab: 6 rows of row pass, then `nout` steps of (row pass of source row 6 + o, column pass,
+// store of output row o).  FULL: nout == kBlurTileH, no bounds checks.
+template <bool FULL>
+__device__ __forceinline__ void blur_walk(const unsigned* p, uint8_t* out, int blur_pitch, int nout, bool store) {
+  const float k0 = c_gauss[0], k1 = c_gauss[1], k2 = c_gauss[2], k3 = c_gauss[3];
+  float R[7][4];
+#pragma unroll
+  for (int u = 0; u < 6; ++u) blur_row_pass(p + u * kBlurSrcWords, R[u], k0, k1, k2, k3);
+  p += 6 * kBlurSrcWords;
+#pragma unroll 1
+  for (int ob = 0; ob < (FULL ? kBlurTileH : nout); ob += 7) {
+#pragma unroll
+    for (int u = 0; u < 7; ++u) {
+      if (FULL || ob + u < nout) {
+        constexpr int kDummy = 0;
+        (void)kDummy;
+        const int s = (6 + u) % 7;  // window slot of source row 6 + ob + u (ob is a multiple of 7)
+        blur_row_pass(p + u * kBlurSrcWords, R[s], k0, k1, k2, k3);
+        // column pass over window rows s-6 .. s (centre s-3, indices mod 7), symmetric pairs
+        unsigned b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float acc = __fmul_rn(k3, R[(s + 4) % 7][i]);
+          acc = __fmaf_rn(k2, __fadd_rn(R[(s + 5) % 7][i], R[(s + 3) % 7][i]), acc);
+          acc = __fmaf_rn(k1, __fadd_rn(R[(s + 6) % 7][i], R[(s + 2) % 7][i]), acc);
+          acc = __fmaf_rn(k0, __fadd_rn(R[s][i], R[(s + 1) % 7][i]), acc);
+          // round half to even: acc in [0, 255.01) so the low byte of acc + 1.5*2^23 is rint(acc)
+          b[i] = __float_as_uint(__fadd_rn(acc, 12582912.0f));
+        }
+        if (store) {
+          const unsigned lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
+          *reinterpret_cast<unsigned*>(out) = __byte_perm(lo, hi, 0x5410);
+        }
+        out += blur_pitch;
+      }
+    }
+    p += 7 * kBlurSrcWords;
+  }
+}
+
+__global__ void __launch_bounds__(kBlurWarps * 32, 6) blur7_kernel(DevGeom g) {
   __shared__ unsigned s_src[kBlurWarps][kBlurSrcRows * kBlurSrcWords];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tile = blockIdx.x * kBlurWarps + warp;
@@ -56,102 +124,78 @@ __global__ void __launch_bounds__(kBlurWarps * 32) blur7_kernel(DevGeom g) {
   const int w = L.w, h = L.h, pitch = L.pitch, blur_pitch = L.blur_pitch;
   const uint8_t* img = L.img + (size_t)frame * L.frame_stride;
   uint8_t* out = L.blur + (size_t)frame * L.blur_stride + (size_t)y0 * blur_pitch + x0 + 4 * lane;
+  unsigned* slab = s_src[warp];
 
-  // staging: lane owns word column `lane` (image x0-4+4*lane ..+3); lanes 0,1 also own columns 32,33.
-  // Words that lie inside the row go global -> shared with cp.async (all rows in flight at once, no
-  // register staging); a second, usually skipped, loop assembles border words from reflected bytes.
-  const int nrows = min(kBlurSrcRows, h - y0 + 6);  // source rows needed for the output rows inside the image
-  {
-    const int xa = x0 - 4 + 4 * lane, xb = xa + 128;
-    const bool fa = L.aligned4 && xa >= 0 && xa + 3 < w;
-    const bool fb = lane < 2 && L.aligned4 && xb + 3 < w;
-    const bool slow_a = !fa, slow_b = lane < 2 && !fb;
-    const unsigned sa = (unsigned)__cvta_generic_to_shared(&s_src[warp][lane]);
-    for (int r = 0; r < nrows; ++r) {
-      int ry = y0 - 3 + r;
-      ry = ry < 0 ? -ry : ry;
-      ry = ry >= h ? 2 * h - 2 - ry : ry;
-      const uint8_t* row = img + (size_t)ry * pitch;
-      const unsigned dst = sa + r * (kBlurSrcWords * 4);
-      if (fa) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(row + xa));
-      if (fb) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 128), "l"(row + xb));
+  // staging: lane owns word column `lane` (image x0-4+4*lane ..+3); lanes 0,1 also own columns 32,33
+  const int nout = min(kBlurTileH, h - y0);  // output rows inside the image
+  const int nrows = nout + 6;
+  const int xa = x0 - 4 + 4 * lane, xb = xa + 128;
+  if (L.aligned4 && w >= 16) {
+    // words inside the row's allocation (they may run past w into the pitch padding: those bytes are either
+    // patched below or only feed pad columns); rows are reflected here, columns afterwards
+    const bool fa = xa >= 0 && xa + 3 < pitch && xa < w;
+    const bool fb = lane < 2 && xb + 3 < pitch && xb < w;
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(slab + lane);
+    if (y0 >= 3 && y0 + nout + 3 <= h) {  // no vertical reflection: one pointer walks down
+      const uint8_t* ga = img + ((ptrdiff_t)(y0 - 3) * pitch + xa);
+      unsigned d = sa;
+      for (int r = 0; r < nrows; ++r) {
+        if (fa) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(ga));
+        if (fb) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d + 128), "l"(ga + 128));
+        ga += pitch;
+        d += kBlurSrcWords * 4;
+      }
+    } else {
+      for (int r = 0; r < nrows; ++r) {
+        const uint8_t* ga = img + (ptrdiff_t)(reflect101(y0 - 3 + r, h) * pitch + xa);  // xa may be -4
+        const unsigned d = sa + r * (kBlurSrcWords * 4);
+        if (fa) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(ga));
+        if (fb) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d + 128), "l"(ga + 128));
+      }
     }
     asm volatile("cp.async.commit_group;\n" ::);
-    if (__any_sync(0xFFFFFFFFu, slow_a || slow_b)) {
-      int ca[4], cb[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        ca[k] = reflect101(xa + k, w);
-        cb[k] = reflect101(xb + k, w);
-      }
-      for (int r = 0; r < nrows; ++r) {
-        const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
-        if (slow_a)
-          s_src[warp][r * kBlurSrcWords + lane] = (unsigned)__ldg(row + ca[0]) | ((unsigned)__ldg(row + ca[1]) << 8) |
-                                                  ((unsigned)__ldg(row + ca[2]) << 16) |
-                                                  ((unsigned)__ldg(row + ca[3]) << 24);
-        if (slow_b)
-          s_src[warp][r * kBlurSrcWords + 32 + lane] = (unsigned)__ldg(row + cb[0]) | ((unsigned)__ldg(row + cb[1]) << 8) |
-                                                       ((unsigned)__ldg(row + cb[2]) << 16) |
-                                                       ((unsigned)__ldg(row + cb[3]) << 24);
-      }
-    }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncwarp();
+    // reflect-101 columns of border tiles, shared -> shared, lane = row
+    const bool left = x0 == 0, right = x0 + kBlurTileW + 3 >= w;
+    if (left || right) {
+      for (int r = lane; r < nrows; r += 32) {
+        unsigned* row = slab + r * kBlurSrcWords;
+        // x = -4..-1 mirror x = 4, 3, 2, 1: byte 0 of word 2, bytes 3, 2, 1 of word 1
+        if (left) row[0] = __byte_perm(row[1], row[2], 0x1234);
+        if (right) {
+          uint8_t* rb = reinterpret_cast<uint8_t*>(row);
+          const int last = min(w + 2, x0 + kBlurTileW + 3);  // last column any in-image output reads
+          for (int x = w; x <= last; ++x) rb[x - (x0 - 4)] = rb[(2 * w - 2 - x) - (x0 - 4)];
+        }
+      }
+      __syncwarp();
+    }
+  } else {
+    // unaligned external level 0 (or a level narrower than 16 px): every word assembled from reflected bytes
+    int ca[4], cb[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      ca[k] = reflect101(xa + k, w);
+      cb[k] = reflect101(xb + k, w);
+    }
+    for (int r = 0; r < nrows; ++r) {
+      const uint8_t* row = img + (size_t)reflect101(y0 - 3 + r, h) * pitch;
+      slab[r * kBlurSrcWords + lane] = (unsigned)__ldg(row + ca[0]) | ((unsigned)__ldg(row + ca[1]) << 8) |
+                                       ((unsigned)__ldg(row + ca[2]) << 16) | ((unsigned)__ldg(row + ca[3]) << 24);
+      if (lane < 2)
+        slab[r * kBlurSrcWords + 32 + lane] = (unsigned)__ldg(row + cb[0]) | ((unsigned)__ldg(row + cb[1]) << 8) |
+                                              ((unsigned)__ldg(row + cb[2]) << 16) |
+                                              ((unsigned)__ldg(row + cb[3]) << 24);
+    }
+    __syncwarp();
   }
-  __syncwarp();
 
   const bool store = x0 + 4 * lane < w;  // pad columns inside the 128-byte aligned pitch may receive don't-care bytes
-  const float k0 = c_gauss[0], k1 = c_gauss[1], k2 = c_gauss[2], k3 = c_gauss[3];
-  float R[7][4];
-#pragma unroll 1
-  for (int rb = 0; rb < nrows; rb += 7) {
-#pragma unroll
-    for (int u = 0; u < 7; ++u) {
-      const int r = rb + u;
-      if (r < nrows) {
-        const unsigned* p = &s_src[warp][r * kBlurSrcWords + lane];
-        const unsigned w0 = p[0], w1 = p[1], w2 = p[2];
-        float f[10];
-        f[0] = byte_to_float(w0, 1);
-        f[1] = byte_to_float(w0, 2);
-        f[2] = byte_to_float(w0, 3);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) f[3 + i] = byte_to_float(w1, i);
-        f[7] = byte_to_float(w2, 0);
-        f[8] = byte_to_float(w2, 1);
-        f[9] = byte_to_float(w2, 2);
-        // row pass (OpenCV order): acc = k0*p[x-3]; acc = fma(k_j, p[x-3+j], acc), j = 1..6
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float acc = __fmul_rn(k0, f[i]);
-          acc = __fmaf_rn(k1, f[i + 1], acc);
-          acc = __fmaf_rn(k2, f[i + 2], acc);
-          acc = __fmaf_rn(k3, f[i + 3], acc);
-          acc = __fmaf_rn(k2, f[i + 4], acc);
-          acc = __fmaf_rn(k1, f[i + 5], acc);
-          acc = __fmaf_rn(k0, f[i + 6], acc);
-          R[u][i] = acc;
-        }
-        // column pass for output row r-6 (window rows u-6..u, centre u-3, indices mod 7)
-        if (r >= 6) {
-          unsigned b[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float acc = __fmul_rn(k3, R[(u + 4) % 7][i]);
-            acc = __fmaf_rn(k2, __fadd_rn(R[(u + 5) % 7][i], R[(u + 3) % 7][i]), acc);
-            acc = __fmaf_rn(k1, __fadd_rn(R[(u + 6) % 7][i], R[(u + 2) % 7][i]), acc);
-            acc = __fmaf_rn(k0, __fadd_rn(R[u][i], R[(u + 1) % 7][i]), acc);
-            // round half to even: acc in [0, 255.01) so the low byte of acc + 1.5*2^23 is rint(acc)
-            b[i] = __float_as_uint(__fadd_rn(acc, 12582912.0f));
-          }
-          if (store) {
-            const unsigned lo = __byte_perm(b[0], b[1], 0x0040), hi = __byte_perm(b[2], b[3], 0x0040);
-            *reinterpret_cast<unsigned*>(out + (r - 6) * blur_pitch) = __byte_perm(lo, hi, 0x5410);
-          }
-        }
-      }
-    }
-  }
+  if (nout == kBlurTileH)
+    blur_walk<true>(slab + lane, out, blur_pitch, nout, store);
+  else
+    blur_walk<false>(slab + lane, out, blur_pitch, nout, store);
 }
 
 int launch_blur(const DevGeom& g, cudaStream_t s) {

@@ -8,8 +8,8 @@ namespace orbx {
 constexpr int kEdge = 31;        // edgeThreshold: keypoints live in [31, w-31) x [31, h-31)
 constexpr int kFastTileW = 62;   // interior pixels per FAST tile (score region = 64 x 32)
 constexpr int kFastTileH = 30;
-constexpr int kBlurTileW = 128;  // one warp blurs a 128 x 32 tile
-constexpr int kBlurTileH = 32;
+constexpr int kBlurTileW = 128;  // one warp blurs a 128 x 35 tile (35 = 5 x the 7-row register window)
+constexpr int kBlurTileH = 35;
 constexpr int kResizeTileW = 128;
 constexpr int kResizeTileH = 32;
 
