@@ -211,11 +211,18 @@ int launch_blur(const DevGeom& g, cudaStream_t s) {
 // slab with row-contiguous aligned 32-bit loads (~3 rows per load instruction), so the 512 scattered
 // samples hit shared memory instead of issuing 16 fully divergent global loads per lane.
 constexpr int kBriefWarps = 8;
-constexpr int kBriefPerWarp = 4;
+constexpr int kBriefPerWarp = 8;
 
 // cvRound for |x| < 2^22 without the XU-pipe F2I: the fp32 add rounds half to even at integer granularity
 __device__ __forceinline__ int rint_small(float x) {
   return (int)__float_as_uint(__fadd_rn(x, 12582912.0f)) - 0x4B400000;
+}
+// same rounding, bias left in: 0x4B400000 + cvRound(x) (callers fold the bias into an address)
+__device__ __forceinline__ unsigned rint_raw(float x) { return __float_as_uint(__fadd_rn(x, 12582912.0f)); }
+__device__ __forceinline__ unsigned lds_u8(unsigned shared_addr) {
+  unsigned v;
+  asm volatile("ld.shared.u8 %0, [%1];\n" : "=r"(v) : "r"(shared_addr));
+  return v;
 }
 constexpr int kBriefRows = 39;
 constexpr int kBriefWords = 11;                              // 44 bytes per row
@@ -224,7 +231,8 @@ constexpr int kBriefLoads = (kBriefRows * kBriefWords + 31) / 32;  // 14
 __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutArgs o) {
   // pattern as fp32 (I2F and F2I are quarter-rate XU-pipe conversions: keep them out of the inner loop)
   __shared__ float4 s_pat[256];
-  __shared__ unsigned s_patch[kBriefWarps][kBriefRows * kBriefWords + 3];
+  // two slabs per warp: the neighbourhood of keypoint it+1 is fetched (cp.async) while keypoint it is sampled
+  __shared__ unsigned s_patch[kBriefWarps][2][kBriefRows * kBriefWords + 3];
   {
     const char4 c = c_pattern[threadIdx.x];
     s_pat[threadIdx.x] = make_float4((float)c.x, (float)c.y, (float)c.z, (float)c.w);
@@ -233,14 +241,13 @@ __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutA
   const int frame = blockIdx.y;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n = min(o.n[frame], min(o.cap, o.lvl_cap));
-  int st_off[kBriefLoads];  // row * 65536 + word of staged word i = lane + 32t
+  int st_row[kBriefLoads], st_col[kBriefLoads];  // row and byte column of staged word i = lane + 32t
 #pragma unroll
   for (int t = 0; t < kBriefLoads; ++t) {
     const int i = lane + 32 * t;
-    const int r = i / kBriefWords;
-    st_off[t] = (r << 16) | (i - r * kBriefWords);
+    st_row[t] = i / kBriefWords;
+    st_col[t] = 4 * (i - st_row[t] * kBriefWords);
   }
-  const uint8_t* sp = reinterpret_cast<const uint8_t*>(s_patch[warp]);
   // lane k < kBriefPerWarp prepares keypoint k of this warp: position word and (float)cos/sin((double)theta).
   // The double-precision sin/cos (~150 instructions) is evaluated once per warp for all of its keypoints
   // instead of once per keypoint by all 32 lanes.
@@ -256,44 +263,61 @@ __global__ void __launch_bounds__(kBriefWarps * 32) brief_kernel(DevGeom g, OutA
       b_mine = (float)sin((double)th);
     }
   }
+  // start the fetch of keypoint `it` (one cp.async group per keypoint, empty when there is none); returns the
+  // byte offset of the neighbourhood's first pixel inside its first aligned word
+  auto fetch = [&](int it) -> int {
+    int off = 0;
+    const int j = (blockIdx.x * kBriefPerWarp + it) * kBriefWarps + warp;
+    if (it < kBriefPerWarp && j < n) {
+      const uint32_t lv = __shfl_sync(0xFFFFFFFFu, lv_mine, it);
+      const int l = (int)(lv >> 24), cx = (int)(lv & 0xFFF), cy = (int)((lv >> 12) & 0xFFF);
+      const DevLevel& L = g.lv[l];
+      const int bp = L.blur_pitch;
+      // blurred planes are internal: base, pitch and frame stride are multiples of 128
+      const int o0 = (cy - 19) * bp + (cx - 19);
+      off = o0 & 3;
+      const uint8_t* base = L.blur + (size_t)frame * L.blur_stride + (o0 - off);
+      const unsigned sa = (unsigned)__cvta_generic_to_shared(&s_patch[warp][it & 1][lane]);
+#pragma unroll
+      for (int t = 0; t < kBriefLoads; ++t)
+        if (lane + 32 * t < kBriefRows * kBriefWords)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(sa + 128 * t),
+                       "l"(base + (st_row[t] * bp + st_col[t])));
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+    return off;
+  };
+
+  int off = fetch(0);
+#pragma unroll 1
   for (int it = 0; it < kBriefPerWarp; ++it) {
     const int j = (blockIdx.x * kBriefPerWarp + it) * kBriefWarps + warp;
-    if (j >= n) return;
-    const uint32_t lv = __shfl_sync(0xFFFFFFFFu, lv_mine, it);
+    if (j >= n) return;  // warp-uniform; j grows with it
+    const int off_next = fetch(it + 1);
     const float a = __shfl_sync(0xFFFFFFFFu, a_mine, it), b = __shfl_sync(0xFFFFFFFFu, b_mine, it);
-    const int l = (int)(lv >> 24), cx = (int)(lv & 0xFFF), cy = (int)((lv >> 12) & 0xFFF);
-    const DevLevel& L = g.lv[l];
-    const int bp = L.blur_pitch;
-    // blurred planes are internal: base, pitch and frame stride are multiples of 128
-    const uint8_t* p0 = L.blur + (size_t)frame * L.blur_stride + (size_t)(cy - 19) * bp + (cx - 19);
-    const int off = (int)((uintptr_t)p0 & 3);
-    const uint8_t* base = p0 - off;
-    unsigned stg[kBriefLoads];
-#pragma unroll
-    for (int t = 0; t < kBriefLoads; ++t)
-      if (lane + 32 * t < kBriefRows * kBriefWords)
-        stg[t] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)(st_off[t] >> 16) * bp) + (st_off[t] & 0xFFFF));
-    __syncwarp();  // the previous keypoint's samples have been read
-#pragma unroll
-    for (int t = 0; t < kBriefLoads; ++t)
-      if (lane + 32 * t < kBriefRows * kBriefWords) s_patch[warp][lane + 32 * t] = stg[t];
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");
     __syncwarp();
-    const uint8_t* centre = sp + 19 * (kBriefWords * 4) + 19 + off;
+    // sample address = centre + iy * 44 + ix with ix, iy = cvRound(rotated offset).  The magic-add rounding
+    // leaves 0x4B400000 + i in the register; the two biases are folded into the (32-bit, wrapping) base address.
+    const unsigned centre = (unsigned)__cvta_generic_to_shared(&s_patch[warp][it & 1][0]) + 19 * (kBriefWords * 4) + 19 +
+                            (unsigned)off - 0x4B400000u * (unsigned)(kBriefWords * 4 + 1);
     uint32_t word = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float4 p = s_pat[k * 32 + lane];
       const float ax = p.x, ay = p.y, bx = p.z, by = p.w;
-      const int iax = rint_small(__fsub_rn(__fmul_rn(ax, a), __fmul_rn(ay, b)));
-      const int iay = rint_small(__fadd_rn(__fmul_rn(ax, b), __fmul_rn(ay, a)));
-      const int ibx = rint_small(__fsub_rn(__fmul_rn(bx, a), __fmul_rn(by, b)));
-      const int iby = rint_small(__fadd_rn(__fmul_rn(bx, b), __fmul_rn(by, a)));
-      const int va = centre[iay * (kBriefWords * 4) + iax];
-      const int vb = centre[iby * (kBriefWords * 4) + ibx];
+      const unsigned iax = rint_raw(__fsub_rn(__fmul_rn(ax, a), __fmul_rn(ay, b)));
+      const unsigned iay = rint_raw(__fadd_rn(__fmul_rn(ax, b), __fmul_rn(ay, a)));
+      const unsigned ibx = rint_raw(__fsub_rn(__fmul_rn(bx, a), __fmul_rn(by, b)));
+      const unsigned iby = rint_raw(__fadd_rn(__fmul_rn(bx, b), __fmul_rn(by, a)));
+      const unsigned va = lds_u8(centre + iay * (kBriefWords * 4) + iax);
+      const unsigned vb = lds_u8(centre + iby * (kBriefWords * 4) + ibx);
       const uint32_t bal = __ballot_sync(0xFFFFFFFFu, va < vb);
       if (lane == k) word = bal;
     }
     if (lane < 8) reinterpret_cast<uint32_t*>(o.desc + ((size_t)frame * o.cap + j) * 32)[lane] = word;
+    __syncwarp();  // slab it & 1 is free for keypoint it + 2
+    off = off_next;
   }
 }
 
