@@ -239,20 +239,26 @@ __global__ void __launch_bounds__(256, 6) fast_nms_kernel(DevGeom g) {
       hs[k] = __vmaxs2(__byte_perm(pl, pc, 0x5432), __byte_perm(pc, pr, 0x5432));
       h3[k] = __vmaxs2(hs[k], pc);
     }
-    // keep bit per lane: bit 15 / 31 of (nb | 0x8000) - m is clear iff nb < m (no borrow leaves a lane)
-    unsigned kacc = 0;  // bit 2i = first pixel of row 4w+i survives, bit 2i+1 = second pixel
+    // keep bit per lane: bit 15 / 31 of (nb | 0x8000) - m is clear iff nb < m (no borrow leaves a lane);
+    // row i of this warp parks its two bits at 15 - i and 31 - i
+    unsigned kacc = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const unsigned nb = max3x2(h3[i], h3[i + 2], hs[i + 1]);
-      unsigned kb = ~((nb | 0x80008000u) - c[i + 1]) & colmask;
-      if (4 * warp + i < cy_lo || 4 * warp + i > cy_hi) kb = 0;
-      kacc |= (((kb >> 15) & 1u) | ((kb >> 30) & 2u)) << (2 * i);
+      kacc |= (~((nb | 0x80008000u) - c[i + 1]) & colmask) >> i;
+    }
+    // rows outside cy_lo .. cy_hi (tile ring, image border) are dropped here: i in [ilo, ihi]
+    {
+      const int ilo = cy_lo - 4 * warp, ihi = cy_hi - 4 * warp;
+      const unsigned rows16 = ((2u << (ihi - ilo)) - 1u) << (15 - ihi);
+      kacc &= rows16 * 0x00010001u;
     }
     // survivors are rare (~3 % of pixels): a short divergent loop over the set bits, after all rows
     while (kacc) {
       const int bit = __ffs(kacc) - 1;
       kacc &= kacc - 1;
-      const int cy = 4 * warp + (bit >> 1), hi = bit & 1;
+      const int hi = bit >> 4;
+      const int cy = 4 * warp + 15 + 16 * hi - bit;
       const unsigned m = S[cy * kPairPitch];
       const int sv = (int)(hi ? (m >> 16) : (m & 0xFFFFu)) + sadd;
       const uint32_t slot = atomicAdd(&s_n, 1u);
