@@ -130,6 +130,14 @@ __device__ __forceinline__ void best_update(unsigned& b1, unsigned& b2, unsigned
   }
 }
 
+// two keys at once (keys are unique: they carry the train row): 5 min/max instead of 6
+__device__ __forceinline__ void best_update2(unsigned& b1, unsigned& b2, unsigned k0, unsigned k1) {
+  const unsigned m = min(k0, k1), M = max(k0, k1);
+  const unsigned t = max(b1, m);
+  b1 = min(b1, m);
+  b2 = __vimin3_u32(t, b2, M);
+}
+
 template <int K, bool FUSED>
 __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
   __shared__ uint4 tile[2][kTile * 2];
@@ -184,15 +192,21 @@ __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
     int j = 0;
 #pragma unroll 1
     for (; j + 4 <= rows; j += 4) {
+      unsigned key[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint4 x = tt[(j + u) * 2], y = tt[(j + u) * 2 + 1];
         const unsigned d = hamming256(qa, qb, x, y);
-        best_update<K>(b1, b2, (d << 16) + (unsigned)(base_local + j + u));
+        key[u] = (d << 16) + (unsigned)(base_local + j + u);
+        if (K == 1) best_update<1>(b1, b2, key[u]);
         if (FUSED) {
           const unsigned r = __reduce_min_sync(0xFFFFFFFFu, (d << 16) + qoff);
           if (lane0) s_col[warp][j + u] = r;
         }
+      }
+      if (K == 2) {
+        best_update2(b1, b2, key[0], key[1]);
+        best_update2(b1, b2, key[2], key[3]);
       }
     }
     for (; j < rows; ++j) {
