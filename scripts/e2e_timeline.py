@@ -8,6 +8,8 @@ from slam_rs_b200.frontend import SequenceFrontEnd
 
 T, H, W = 1000, 376, 1241
 hc = int(sys.argv[1]) if len(sys.argv) > 1 else 250
+do_h2d = "noh2d" not in sys.argv
+do_d2h = "nod2h" not in sys.argv
 frames = synth.sequence(H, W, T)
 fe = SequenceFrontEnd(W, H, nfeatures=2000, max_frames=T, chunk=1000, host_chunk=hc)
 pin = torch.from_numpy(frames).pin_memory()
@@ -32,13 +34,16 @@ for s in (fe.stream, fe.copy_stream, fe.d2h_stream): s.wait_stream(cur)
 h2d, comp, d2h = [], [], []
 with torch.cuda.stream(fe.copy_stream):
     for a, b in bounds:
-        fe.frames_dev[a:b, :, :W].copy_(pin[a:b], non_blocking=True); h2d.append(ev(fe.copy_stream))
+        if do_h2d:
+            fe.frames_dev[a:b, :, :W].copy_(pin[a:b], non_blocking=True)
+        h2d.append(ev(fe.copy_stream))
 for i, (a, b) in enumerate(bounds):
     fe.stream.wait_event(h2d[i]); fe.extract(fe.frames_dev, a, b); fe.match(a, b); comp.append(ev(fe.stream))
     fe.d2h_stream.wait_stream(fe.stream)
     with torch.cuda.stream(fe.d2h_stream):
         for k in ("n", "kps", "desc", "good", "n_good"):
-            out[k][a:b].copy_(getattr(fe, k)[a:b], non_blocking=True)
+            if do_d2h:
+                out[k][a:b].copy_(getattr(fe, k)[a:b], non_blocking=True)
         d2h.append(ev(fe.d2h_stream))
 torch.cuda.synchronize()
 for i, (a, b) in enumerate(bounds):

@@ -6,6 +6,7 @@ import pytest
 
 from oracle import restated as R, synth, cv_ref, c_oracle
 from tests.test_oracle_cpu import GOLD
+from tests.util import compare_orb
 
 pytestmark = pytest.mark.gpu
 
@@ -311,3 +312,59 @@ def test_extract_matched_points(orbx):
     bad["train_idx"][1] = -1
     with pytest.raises(orbx.OrbxError):
         pe.extract_matched_points(k0, k1, bad)
+
+
+@pytest.mark.skipif(not cv_ref.HAVE_CV2, reason="cv2 not importable")
+def test_kitti_shaped_sequence_full_size(orbx):
+    """BASELINE configs[1] at full frame size (1241x376, nfeatures 2000) on a 48-frame stretch of the bench's own
+    sequence, through every front-end path (one launch set, chunked, two-stream host pipeline): sampled frames
+    and pairs are compared with cv2 (the OpenCV code the reference binds), all frames / pairs with the
+    size-independent properties of the path."""
+    import torch
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 48, 376, 1241, 2000
+    seq = synth.sequence(h, w, T)
+    fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=10, dual=True, points=True)
+    dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
+    dev[:, :, :w] = torch.from_numpy(seq).cuda()
+    fe.run_device(dev)
+    torch.cuda.synchronize()
+    n = fe.n.cpu().numpy()
+    n_good = fe.n_good.cpu().numpy()
+    assert np.all(n == nf) and int(fe.bad_index.item()) == 0       # dense texture: every quota is filled
+    desc_all = fe.desc.cpu().numpy()
+    for t in (0, 17, T - 1):                                         # extraction vs cv2, bit for bit
+        k, d = fe.frame_result(t)
+        st = compare_orb(k, d, cv_ref.orb_detect_and_compute(seq[t], nf), h, w)
+        assert st["missing"] == 0 and st["extra"] == 0 and st["desc_bits_diff"] == 0, st
+        assert st["resp_eq"] == st["angle_eq"] == st["pt_eq"] == st["common"] == nf, st
+    for t in (1, 30):                                                # matching vs cv2 BFMatcher on the same rows
+        d0, d1 = desc_all[t - 1, :nf], desc_all[t, :nf]
+        idx, dist, c = cv_ref.knn2(d0, d1)
+        mutual = np.zeros(nf, bool)
+        mutual[cv_ref.match_k1(d0, d1, cross_check=True)[:, 0]] = True
+        keep = R.ratio_test(idx, dist, c, 0.75) & mutual
+        good = fe.pair_result(t)
+        assert np.array_equal(good["query_idx"], np.nonzero(keep)[0])
+        assert np.array_equal(good["train_idx"], idx[keep, 0])
+        assert np.array_equal(good["distance"], dist[keep, 0].astype(np.float32))
+    for t in range(1, T):                                            # properties of every pair
+        g = fe.pair_result(t)
+        assert len(g) == n_good[t] > 0
+        assert np.all(np.diff(g["query_idx"]) > 0)                   # query order, one match per query
+        assert len(np.unique(g["train_idx"])) == len(g)              # cross-check => injective
+        q, tr = desc_all[t - 1][g["query_idx"]], desc_all[t][g["train_idx"]]
+        assert np.array_equal(np.unpackbits(q ^ tr, axis=1).sum(1), g["distance"].astype(np.int64))
+    # chunked launch sets and the two-stream host pipeline return the same bytes
+    ref = {k: getattr(fe, k).cpu().numpy().copy() for k in ("n", "kps", "desc", "good", "n_good")}
+    fe2 = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=7)
+    fe2.run_device(dev)
+    out = fe.alloc_host_outputs()
+    fe.run_host(torch.from_numpy(seq).pin_memory(), out)
+    torch.cuda.synchronize()
+    for t in range(T):
+        for name, m in (("kps", n[t]), ("desc", n[t]), ("good", n_good[t] if t else 0)):
+            a = ref[name][t, :m]
+            assert np.array_equal(getattr(fe2, name)[t, :m].cpu().numpy(), a), (name, t)
+            assert np.array_equal(out[name][t, :m].numpy(), a), (name, t)
+    assert np.array_equal(out["n"].numpy(), n) and np.array_equal(out["n_good"][1:].numpy(), n_good[1:])
