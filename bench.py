@@ -560,6 +560,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=T_SEQ, help="frames per GPU per step")
+    ap.add_argument("--size", default="kitti", choices=["kitti", "hd"],
+                    help="hd: 1920x1080 frames, nfeatures=5000 (BASELINE configs[2] shape; not the headline metric)")
     ap.add_argument("--chunk", type=int, default=1000, help="frames per extraction launch (device-resident pass)")
     ap.add_argument("--dual", type=int, default=1, help="1: alternate e2e pipeline stages between two streams")
     ap.add_argument("--host-chunk", type=int, default=167,
@@ -574,6 +576,11 @@ def main():
     ap.add_argument("--overlap", action="store_true",
                     help="run matching on a second stream (about +2 %% frames/s, but per-stage event times then overlap)")
     args = ap.parse_args()
+    if args.size == "hd":
+        global W_IMG, H_IMG, NFEAT, WORKLOAD
+        W_IMG, H_IMG, NFEAT = 1920, 1080, 5000
+        WORKLOAD = WORKLOAD.replace("C2 KITTI-shaped synthetic sequence 1241x376", "C3-shaped synthetic sequence 1920x1080") \
+                           .replace("nfeatures=2000", "nfeatures=5000")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -65,7 +65,7 @@ __device__ __forceinline__ float harris_from_words(const unsigned* wds, unsigned
   return __fmul_rn(__fsub_rn(t1, t2), s4);
 }
 
-constexpr int kHarrisBlocksPerLevel = 4;
+constexpr int kHarrisBlocksPerLevel = 1;
 constexpr int kHarrisWarps = 8;
 constexpr int kHarrisSlab = 27;  // 27 words per candidate; odd stride = conflict-free per-thread reads
 constexpr int kHarrisScan = 128;  // candidates scanned per warp iteration (4 independent loads per lane)
@@ -257,7 +257,11 @@ __global__ void __launch_bounds__(kHarrisWarps * 32, 2) harris_kernel(DevGeom g)
 
 int launch_harris(const DevGeom& g, cudaStream_t s) {
   if (g.batch == 0) return ORBX_OK;
-  dim3 grid(kHarrisBlocksPerLevel, g.nlevels, g.batch);
+  // one block per (level, frame) amortises the threshold scan and keeps the warp pipelines long; small batches
+  // get more blocks per level so that the grid still fills the 148 SMs (2 resident blocks each)
+  const int lf = g.nlevels * g.batch;
+  const int bpl = lf >= 1184 ? kHarrisBlocksPerLevel : (lf >= 592 ? 2 * kHarrisBlocksPerLevel : 4 * kHarrisBlocksPerLevel);
+  dim3 grid(bpl, g.nlevels, g.batch);
   constexpr int kSmem = kHarrisWarps * 2 * 32 * kHarrisSlab * (int)sizeof(unsigned);
   ORBX_CUDA(cudaFuncSetAttribute(harris_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   harris_kernel<<<grid, 256, kSmem, s>>>(g);
@@ -405,7 +409,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kOrientWarps = 8;
-constexpr int kOrientPerWarp = 8;
+constexpr int kOrientPerWarp = 16;
 
 __device__ __forceinline__ int dp4a_us(unsigned a, unsigned b_signed_bytes, int c) {
   int d;
