@@ -224,6 +224,35 @@ int orbx_map_stable_count(orbx_map* m, int* count);
 /* test hook: observation counts and alive flags of the first n slots (host outputs, either may be NULL) */
 int orbx_map_read_observations(orbx_map* m, int* obs, uint8_t* alive, int n);
 
+/* ------------------------------------------------------------------ Triangulator
+ * Device form of mapping::Triangulator (src/mapping/triangulation.rs:52-198).  Poses are world-to-camera
+ * (R 3x3 ROW-major, t 3), points are (x, y) fp32 pairs as produced by orbx_extract_matched_points. */
+typedef struct orbx_triangulator orbx_triangulator;
+/* Triangulator::new(intrinsics) (triangulation.rs:62-68); max_points bounds n of one call */
+int orbx_triangulator_create(int device, int max_points, double fx, double fy, double cx, double cy,
+                             orbx_triangulator** out);
+void orbx_triangulator_destroy(orbx_triangulator* t);
+/* with_min_parallax / with_max_reproj_error (triangulation.rs:71-80): stored and returned, not applied — the
+ * reference does not apply them either (:138 "skipping this check") */
+int orbx_triangulator_set_thresholds(orbx_triangulator* t, double min_parallax_deg, double max_reproj_error);
+int orbx_triangulator_get_thresholds(const orbx_triangulator* t, double* min_parallax_deg, double* max_reproj_error);
+/* Triangulator::triangulate (triangulation.rs:92-158): P = K [R | t] (:161-183), cv::triangulatePoints (4x4 DLT
+ * system per correspondence, right singular vector of the smallest singular value, rounded to fp32 like the
+ * CV_32F result the reference reads), skip |w| < 1e-10 (:127), X = (x, y, z) / w in f64 (:131), keep points in
+ * front of both cameras (:134-139).  Survivors keep their input order; ids[k] = input index i (:140);
+ * has_desc[k] = 1 and out_desc row k = desc row i when i < desc_rows (:141-150), else 0 / zeros.
+ * n1 != n2 is the reference's "Point arrays must have the same length" error (ORBX_E_BADARG); n == 0 returns 0
+ * points.  points4d (n x 4 fp32, optional) receives the homogeneous points of ALL n inputs (sign is arbitrary,
+ * as in any SVD) — parity hook.  Every array may be host or device memory; device outputs need cap >= n.
+ * *n_out > cap -> ORBX_E_CAPACITY. */
+int orbx_triangulate(orbx_triangulator* t, const double* R1, const double* t1, const double* R2, const double* t2,
+                     const float* pts1, int n1, const float* pts2, int n2, const uint8_t* desc, int desc_rows,
+                     int32_t* ids, double* xyz, uint8_t* out_desc, uint8_t* has_desc, float* points4d, int cap,
+                     int* n_out);
+/* transform_points_to_world (examples/point_cloud.rs:522-544), the step between triangulate and Map::add_points:
+ * xyz[i] = R^T * xyz[i] + (-R^T * t), in place (host or device), nalgebra's accumulation order, unfused f64 */
+int orbx_transform_points_to_world(orbx_triangulator* t, const double* R, const double* tv, double* xyz, int n);
+
 /* ------------------------------------------------------------------ misc */
 const char* orbx_last_error(void);
 const char* orbx_version(void);

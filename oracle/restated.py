@@ -426,3 +426,65 @@ def extract_matched_points(kp1_xy, kp2_xy, matches):
         p1.append(kp1_xy[q])
         p2.append(kp2_xy[t])
     return (np.asarray(p1, np.float32).reshape(-1, 2), np.asarray(p2, np.float32).reshape(-1, 2))
+
+
+# ---------------------------------------------------------------- §8 f4: mapping::Triangulator
+def projection_matrix(intr, R, t):
+    """Triangulator::build_projection_matrix (/root/reference/src/mapping/triangulation.rs:161-183): P = K [R | t]
+    by cv::gemm (f64; small matrices take OpenCV's own loop: k ascending, no fused multiply-add).  K's zero
+    entries contribute exact zeros, so row 0 = fx*Rt[0] + cx*Rt[2], row 1 = fy*Rt[1] + cy*Rt[2], row 2 = Rt[2]."""
+    fx, fy, cx, cy = intr
+    Rt = np.hstack([np.asarray(R, np.float64).reshape(3, 3), np.asarray(t, np.float64).reshape(3, 1)])
+    return np.stack([fx * Rt[0] + cx * Rt[2], fy * Rt[1] + cy * Rt[2], Rt[2]])
+
+
+def triangulate_points4d(P1, P2, pts1, pts2):
+    """cv::triangulatePoints as the reference calls it (triangulation.rs:114): per correspondence the 4x4 system
+    rows (x*P[2] - P[0], y*P[2] - P[1]) for both views in f64, SVD, last right singular vector, stored as CV_32F
+    (the inputs are Point2f).  Returns float32 [n, 4]; the overall sign of each row is arbitrary."""
+    p1 = np.asarray(pts1, np.float32).reshape(-1, 2).astype(np.float64)
+    p2 = np.asarray(pts2, np.float32).reshape(-1, 2).astype(np.float64)
+    A = np.stack([p1[:, 0:1] * P1[2] - P1[0], p1[:, 1:2] * P1[2] - P1[1],
+                  p2[:, 0:1] * P2[2] - P2[0], p2[:, 1:2] * P2[2] - P2[1]], 1)
+    if len(A) == 0:
+        return np.zeros((0, 4), np.float32)
+    return np.linalg.svd(A)[2][:, 3, :].astype(np.float32)
+
+
+def triangulate(intr, pose1, pose2, pts1, pts2, descriptors=None):
+    """Triangulator::triangulate (triangulation.rs:92-158).  Returns (ids, xyz float64 [m, 3], desc uint8 [m, 32],
+    has_desc bool [m]): points with |w| >= 1e-10 (:127) in front of both cameras (:134-139, nalgebra's
+    ((r20*x + r21*y) + r22*z) + t2 > 0), in input order with id = input index (:140) and descriptor row i attached
+    when i < rows (:141-150).  Raises ValueError when the point arrays differ in length (:100-102)."""
+    pts1 = np.asarray(pts1, np.float32).reshape(-1, 2)
+    pts2 = np.asarray(pts2, np.float32).reshape(-1, 2)
+    if len(pts1) != len(pts2):
+        raise ValueError("Point arrays must have the same length")
+    n = len(pts1)
+    if n == 0:
+        return np.zeros(0, np.int32), np.zeros((0, 3)), np.zeros((0, 32), np.uint8), np.zeros(0, bool)
+    (R1, t1), (R2, t2) = [(np.asarray(r, np.float64).reshape(3, 3), np.asarray(t, np.float64).reshape(3)) for r, t in (pose1, pose2)]
+    h = triangulate_points4d(projection_matrix(intr, R1, t1), projection_matrix(intr, R2, t2), pts1, pts2).astype(np.float64)
+    w = h[:, 3]
+    ok = ~(np.abs(w) < 1e-10)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        X = h[:, :3] / w[:, None]
+    for R, t in ((R1, t1), (R2, t2)):
+        ok &= (((R[2, 0] * X[:, 0] + R[2, 1] * X[:, 1]) + R[2, 2] * X[:, 2]) + t[2]) > 0.0
+    ids = np.nonzero(ok)[0].astype(np.int32)
+    rows = 0 if descriptors is None else len(descriptors)
+    desc = np.zeros((len(ids), 32), np.uint8)
+    has = ids < rows
+    if rows:
+        desc[has] = np.asarray(descriptors, np.uint8).reshape(rows, 32)[ids[has]]
+    return ids, X[ids], desc, has
+
+
+def transform_points_to_world(xyz, pose):
+    """transform_points_to_world (/root/reference/examples/point_cloud.rs:522-544): r_ctw = R^T, t_ctw = -r_ctw * t,
+    p_world = r_ctw * p + t_ctw; nalgebra accumulates the columns left to right in f64, unfused."""
+    R, t = np.asarray(pose[0], np.float64).reshape(3, 3), np.asarray(pose[1], np.float64).reshape(3)
+    rc = R.T
+    tc = ((-rc[:, 0]) * t[0] + (-rc[:, 1]) * t[1]) + (-rc[:, 2]) * t[2]
+    p = np.asarray(xyz, np.float64).reshape(-1, 3)
+    return ((rc[:, 0] * p[:, 0:1] + rc[:, 1] * p[:, 1:2]) + rc[:, 2] * p[:, 2:3]) + tc

@@ -6,7 +6,7 @@ The directory name contains a hyphen, so the importable alias is the sibling pac
 """
 from ._ffi import lib, OrbxError, LIB_PATH, SYMBOLS  # noqa: F401
 from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE  # noqa: F401
-from .mapping import Map, CameraIntrinsics  # noqa: F401
+from .mapping import Map, CameraIntrinsics, Triangulator  # noqa: F401
 from .odometry import PoseEstimator  # noqa: F401
 
 

@@ -72,6 +72,12 @@ def _load():
         "orbx_map_prune_outliers": (i, [vp, ip]),
         "orbx_map_stable_count": (i, [vp, ip]),
         "orbx_map_read_observations": (i, [vp, vp, vp, i]),
+        "orbx_triangulator_create": (i, [i, i, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(vp)]),
+        "orbx_triangulator_destroy": (None, [vp]),
+        "orbx_triangulator_set_thresholds": (i, [vp, C.c_double, C.c_double]),
+        "orbx_triangulator_get_thresholds": (i, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "orbx_triangulate": (i, [vp, vp, vp, vp, vp, vp, i, vp, i, vp, i, vp, vp, vp, vp, vp, i, ip]),
+        "orbx_transform_points_to_world": (i, [vp, vp, vp, vp, i]),
         "orbx_matcher_create": (i, [i, i, C.POINTER(vp)]),
         "orbx_matcher_destroy": (None, [vp]),
         "orbx_matcher_sync": (i, [vp]),

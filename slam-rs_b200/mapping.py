@@ -122,3 +122,77 @@ class Map:
         alive = np.zeros(max(n, 1), np.uint8)
         check(lib.orbx_map_read_observations(self._h, _ptr(obs), _ptr(alive), n))
         return obs[:n], alive[:n] != 0
+
+
+class Triangulator:
+    """``mapping::Triangulator`` (/root/reference/src/mapping/triangulation.rs:52-198) over liborbx
+    (csrc/triangulate.cu).  ``triangulate`` returns arrays instead of ``Vec<MapPoint>``: ``(ids, positions
+    float64 [m, 3], descriptors uint8 [m, 32], has_descriptor bool [m])`` — id = index of the correspondence, like
+    ``MapPoint::new(point_3d, i)`` (:140); observations start at 1 (``Map.add_points`` default)."""
+
+    def __init__(self, intrinsics, max_points=1 << 16, device=0):
+        self._h = C.c_void_p()
+        self.intrinsics = intrinsics
+        self.max_points = int(max_points)
+        check(lib.orbx_triangulator_create(int(device), self.max_points, intrinsics.fx, intrinsics.fy, intrinsics.cx,
+                                           intrinsics.cy, C.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib.orbx_triangulator_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def _thresholds(self):
+        a, b = C.c_double(0), C.c_double(0)
+        check(lib.orbx_triangulator_get_thresholds(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    @property
+    def min_parallax_deg(self):
+        return self._thresholds()[0]
+
+    @property
+    def max_reproj_error(self):
+        return self._thresholds()[1]
+
+    def with_min_parallax(self, deg):
+        """triangulation.rs:71-74 (builder: returns self)"""
+        check(lib.orbx_triangulator_set_thresholds(self._h, float(deg), self.max_reproj_error))
+        return self
+
+    def with_max_reproj_error(self, error):
+        """triangulation.rs:77-80"""
+        check(lib.orbx_triangulator_set_thresholds(self._h, self.min_parallax_deg, float(error)))
+        return self
+
+    def triangulate(self, pose1, pose2, points1, points2, descriptors=None, return_points4d=False):
+        """triangulation.rs:92-158.  Raises ``OrbxError`` ("Point arrays must have the same length") on mismatched
+        inputs, returns empty arrays for empty inputs."""
+        r1, t1 = Map._pose(pose1)
+        r2, t2 = Map._pose(pose2)
+        p1 = np.ascontiguousarray(points1, np.float32).reshape(-1, 2)
+        p2 = np.ascontiguousarray(points2, np.float32).reshape(-1, 2)
+        n1, n2 = len(p1), len(p2)
+        d = None if descriptors is None else np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        cap = max(n1, 1)
+        ids = np.zeros(cap, np.int32)
+        xyz = np.zeros((cap, 3), np.float64)
+        od = np.zeros((cap, 32), np.uint8)
+        hd = np.zeros(cap, np.uint8)
+        p4 = np.zeros((cap, 4), np.float32) if return_points4d else None
+        m = C.c_int(0)
+        check(lib.orbx_triangulate(self._h, _ptr(r1), _ptr(t1), _ptr(r2), _ptr(t2), _ptr(p1), n1, _ptr(p2), n2,
+                                   _ptr(d), 0 if d is None else len(d), _ptr(ids), _ptr(xyz), _ptr(od), _ptr(hd),
+                                   _ptr(p4), cap, C.byref(m)))
+        k = m.value
+        out = (ids[:k], xyz[:k], od[:k], hd[:k] != 0)
+        return out + (p4[:n1],) if return_points4d else out
+
+    def transform_points_to_world(self, positions, pose):
+        """examples/point_cloud.rs:522-544 — camera-frame points of ``triangulate`` to the world frame."""
+        r, t = Map._pose(pose)
+        xyz = np.array(positions, np.float64).reshape(-1, 3)
+        check(lib.orbx_transform_points_to_world(self._h, _ptr(r), _ptr(t), _ptr(xyz), len(xyz)))
+        return xyz
