@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <atomic>
 #include <string>
 #include <vector>
@@ -23,10 +24,21 @@ extern std::atomic<uint64_t> g_launches;
     }                                                                                         \
   } while (0)
 
+// ORBX_DEBUG_SYNC=1 in the environment: synchronise the device after every launch so that a faulting kernel is
+// reported at its own launch site
+inline bool debug_sync() {
+  static const bool on = [] {
+    const char* v = getenv("ORBX_DEBUG_SYNC");
+    return v && *v && *v != '0';
+  }();
+  return on;
+}
+
 #define ORBX_LAUNCH_CHECK()                                                                  \
   do {                                                                                       \
     orbx::g_launches.fetch_add(1, std::memory_order_relaxed);                                \
     cudaError_t e_ = cudaGetLastError();                                                     \
+    if (e_ == cudaSuccess && orbx::debug_sync()) e_ = cudaDeviceSynchronize();               \
     if (e_ != cudaSuccess) {                                                                 \
       orbx::set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
       return ORBX_E_CUDA;                                                                    \

@@ -240,7 +240,7 @@ int orbx_map_create(int device, int capacity, double fx, double fy, double cx, d
   if (!rc) rc = map_alloc(&m->good, cap);
   if (!rc) rc = map_alloc(&m->pairs, cap * 2);
   if (!rc) rc = map_alloc(&m->pose, 12);
-  if (!rc && cudaMemset(m->flags, 0, cap) != cudaSuccess) rc = ORBX_E_CUDA;
+  if (!rc && (cudaMemset(m->flags, 0, cap) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess)) rc = ORBX_E_CUDA;
   if (rc) {
     orbx_map_destroy(m);
     return rc;

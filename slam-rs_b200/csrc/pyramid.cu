@@ -156,6 +156,12 @@ int launch_resize(const ResizeArgs& a, int batch, cudaStream_t s) {
   }
   dim3 grid(div_up(a.dw, kResizeTileW), div_up(a.dh, kResizeTileH), batch);
   resize_exact_kernel<<<grid, kResizeThreads, 0, s>>>(a);
+  if (debug_sync() && cudaDeviceSynchronize() != cudaSuccess) {
+    set_error("resize debug: src=%p dst=%p sstride=%zu dstride=%zu sw=%d sh=%d sp=%d dw=%d dh=%d dp=%d align=%d batch=%d xtab=%p ytab=%p",
+              (const void*)a.src, (void*)a.dst, a.src_stride, a.dst_stride, a.sw, a.sh, a.spitch, a.dw, a.dh, a.dpitch,
+              a.src_align, batch, (const void*)a.xtab, (const void*)a.ytab);
+    return ORBX_E_CUDA;
+  }
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

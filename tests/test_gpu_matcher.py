@@ -368,3 +368,39 @@ def test_kitti_shaped_sequence_full_size(orbx):
             assert np.array_equal(getattr(fe2, name)[t, :m].cpu().numpy(), a), (name, t)
             assert np.array_equal(out[name][t, :m].numpy(), a), (name, t)
     assert np.array_equal(out["n"].numpy(), n) and np.array_equal(out["n_good"][1:].numpy(), n_good[1:])
+
+
+def test_hd_pipeline_fresh_handles_host_first(orbx):
+    """1920x1080, nfeatures=5000 (BASELINE configs[2] shape) through the two-stream host pipeline on FRESH handles
+    while the copy engine is busy with the queued frame uploads: the first launch of a new detector must already see
+    its resize / FAST tables (regression: the tables used to be uploaded by a legacy-stream cudaMemcpy from pageable
+    memory, which is not ordered against the non-blocking stream the kernels run on).  Level 0 has pitch == width
+    here (1920 is a multiple of 128), unlike the 1241-wide case."""
+    import torch
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 48, 1080, 1920, 5000
+    seq = synth.sequence(h, w, T, canvas_seed=201)
+    pinned = torch.from_numpy(seq).pin_memory()
+    fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=12, dual=True)
+    out = fe.alloc_host_outputs()
+    fe.run_host(pinned, out)                                                   # first use of both detector handles
+    torch.cuda.synchronize()
+    fe2 = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, chunk=T)
+    dev = torch.zeros((T, h, fe2.pitch), dtype=torch.uint8, device="cuda")
+    dev[:, :, :w].copy_(pinned)
+    fe2.run_device(dev)
+    torch.cuda.synchronize()
+    assert np.array_equal(out["n"].numpy(), fe2.n.cpu().numpy())
+    assert np.array_equal(out["n_good"][1:].numpy(), fe2.n_good[1:].cpu().numpy())
+    for t in range(T):
+        n, g = int(out["n"][t]), int(out["n_good"][t])
+        assert np.array_equal(out["kps"][t, :n].numpy(), fe2.kps[t, :n].cpu().numpy())
+        assert np.array_equal(out["desc"][t, :n].numpy(), fe2.desc[t, :n].cpu().numpy())
+        if t:
+            assert np.array_equal(out["good"][t, :g].numpy(), fe2.good[t, :g].cpu().numpy())
+    for t in (0, 3, 13, T - 1):                                                # first frame of a handle's first batch too
+        n = int(out["n"][t])
+        k = out["kps"][t, :n].numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+        ref = cv_ref.orb_detect_and_compute(seq[t], nf)
+        st = compare_orb(k, out["desc"][t, :n].numpy(), ref, h, w)
+        assert st["missing"] == 0 and st["extra"] == 0 and st["desc_bits_diff"] == 0, st
