@@ -1,0 +1,75 @@
+"""CPU: the oracle's restatement of the OpenCV calls behind odometry::PoseEstimator (oracle/pose_restated.py,
+SURVEY.md §8 f2; /root/reference/src/odometry/pose.rs:47-114) pinned against cv2 itself: five-point solutions,
+findEssentialMat (same RANSAC draws, same winner, same mask) and recoverPose."""
+import numpy as np
+import pytest
+
+from oracle import pose_restated as PR
+
+cv2 = pytest.importorskip("cv2")
+KITTI = (718.856, 718.856, 607.1928, 185.2157)
+K = np.array([[KITTI[0], 0, KITTI[2]], [0, KITTI[1], KITTI[3]], [0, 0, 1.0]])
+
+
+def two_view_scene(n, seed, outliers=0.25, noise=0.3):
+    rng = np.random.default_rng(seed)
+    R = cv2.Rodrigues(rng.normal(0, 0.02, 3))[0]
+    t = rng.normal(0, 0.3, 3) + [0, 0, 1.0]
+    X = np.stack([rng.uniform(-10, 10, n), rng.uniform(-3, 3, n), rng.uniform(4, 40, n)], 1)
+
+    def proj(Rm, tv):
+        c = X @ Rm.T + tv
+        return c[:, :2] / c[:, 2:] * [K[0, 0], K[1, 1]] + [K[0, 2], K[1, 2]]
+    p1 = (proj(np.eye(3), np.zeros(3)) + rng.normal(0, noise, (n, 2))).astype(np.float32)
+    p2 = (proj(R, t) + rng.normal(0, noise, (n, 2))).astype(np.float32)
+    out = rng.random(n) < outliers
+    p2[out] += rng.normal(0, 30, (int(out.sum()), 2)).astype(np.float32)
+    return p1, p2, R, t
+
+
+def test_five_point_vs_cv2():
+    rng = np.random.default_rng(0)
+    close, total = 0, 0
+    for _ in range(60):
+        R = cv2.Rodrigues(rng.normal(0, 0.2, 3))[0]
+        t = rng.normal(0, 1, 3)
+        X = np.stack([rng.uniform(-3, 3, 5), rng.uniform(-2, 2, 5), rng.uniform(3, 12, 5)], 1)
+        x1 = X[:, :2] / X[:, 2:]
+        c = X @ R.T + t
+        x2 = c[:, :2] / c[:, 2:]
+        sols = PR.five_point(x1, x2)
+        want = cv2.findEssentialMat(x1.copy(), x2.copy(), np.eye(3), cv2.RANSAC, 0.999, 1.0)[0].reshape(-1, 3, 3)
+        assert len(sols) == len(want)                                          # same number of real solutions
+        for E in want:
+            d = min(min(np.abs(E - S).max(), np.abs(E + S).max()) for S in sols)
+            close += d < 1e-6
+            total += 1
+    assert close >= 0.97 * total
+
+
+def test_cv_rng_samples_are_distinct_and_deterministic():
+    s = PR.ransac_samples(37, 200)
+    assert s.shape == (200, 5) and s.min() >= 0 and s.max() < 37
+    assert all(len(set(r)) == 5 for r in s.tolist())
+    assert np.array_equal(s, PR.ransac_samples(37, 200))
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_find_essential_mat_vs_cv2(seed):
+    p1, p2, _, _ = two_view_scene(500, seed)
+    Ecv, mcv = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    E, m, iters = PR.find_essential_mat(p1, p2, KITTI)
+    assert iters < 1000
+    assert min(np.abs(E - Ecv).max(), np.abs(E + Ecv).max()) < 1e-6            # the same hypothesis wins
+    assert np.array_equal(m, mcv.ravel().astype(bool))
+
+
+@pytest.mark.parametrize("seed", [4, 5])
+def test_recover_pose_vs_cv2(seed):
+    p1, p2, Rt, tt = two_view_scene(400, seed, outliers=0.1)
+    Ecv, _ = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    n, Rcv, tcv, mcv = cv2.recoverPose(Ecv, p1, p2, K)
+    R, t, m, good = PR.recover_pose(Ecv, p1, p2, KITTI)
+    assert good == n and np.array_equal(m, mcv.ravel() != 0)
+    assert np.abs(R - Rcv).max() < 1e-9 and np.abs(t - tcv.ravel()).max() < 1e-9
+    assert np.abs(R - Rt).max() < 0.02                                         # and it is the true motion
