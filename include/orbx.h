@@ -33,6 +33,7 @@ extern "C" {
 #define ORBX_E_CAPACITY (-2) /* result larger than the caller's buffer; count outputs hold the needed size */
 #define ORBX_E_CUDA (-3)
 #define ORBX_E_NOMEM (-4)
+#define ORBX_E_DATA (-5) /* valid call, unusable data: the reference's Err(String) cases (pose.rs:52-59,75-77,104-106) */
 
 #define ORBX_HARRIS_SCORE 0
 
@@ -223,6 +224,38 @@ int orbx_map_prune_outliers(orbx_map* m, int* removed);
 int orbx_map_stable_count(orbx_map* m, int* count);
 /* test hook: observation counts and alive flags of the first n slots (host outputs, either may be NULL) */
 int orbx_map_read_observations(orbx_map* m, int* obs, uint8_t* alive, int n);
+
+/* ------------------------------------------------------------------ PoseEstimator
+ * Device form of odometry::PoseEstimator::compute_essential_matrix / recover_pose (src/odometry/pose.rs:47-114):
+ * cv::findEssentialMat(points1, points2, K, RANSAC, 0.999, 1.0, 1000, mask) and cv::recoverPose(E, points1, points2,
+ * K, R, t, mask), reproduced down to the RANSAC index draws (cv::RNG seeded as OpenCV seeds it), so the winning
+ * hypothesis is OpenCV's; see csrc/pose.cu.  Points are (x, y) fp32 pairs (orbx_extract_matched_points). */
+typedef struct orbx_pose_estimator orbx_pose_estimator;
+enum { ORBX_POSE_OK = 0, ORBX_POSE_INSUFFICIENT_POINTS = 1, ORBX_POSE_NO_MODEL = 2, ORBX_POSE_TOO_FEW_INLIERS = 3 };
+/* PoseEstimator::new(intrinsics) (pose.rs:17-23; min_matches = 8).  max_points bounds n of one problem,
+ * max_problems the batch of orbx_estimate_pose_batch. */
+int orbx_pose_estimator_create(int device, int max_points, int max_problems, double fx, double fy, double cx, double cy,
+                               orbx_pose_estimator** out);
+void orbx_pose_estimator_destroy(orbx_pose_estimator* pe);
+int orbx_pose_estimator_set_stream(orbx_pose_estimator* pe, void* cuda_stream);
+int orbx_pose_estimator_sync(orbx_pose_estimator* pe);
+/* compute_essential_matrix (pose.rs:47-80).  E: 9 doubles, row major, unit Frobenius norm (as OpenCV returns it);
+ * mask (n bytes, optional): RANSAC inliers; *iterations (optional): RANSAC iterations run.  Fewer than 8 points is
+ * the reference's "Insufficient points" error, no model its "Failed to compute essential matrix": ORBX_E_DATA.
+ * pts / mask may be host or device memory. */
+int orbx_compute_essential_matrix(orbx_pose_estimator* pe, const float* pts1, int n1, const float* pts2, int n2,
+                                  double* E, uint8_t* mask, int* n_inliers, int* iterations);
+/* recover_pose (pose.rs:83-114): R 9 doubles row major, t 3 doubles (unit), mask (optional) = points in front of both
+ * cameras and nearer than 50 for the chosen (R, t); *n_good < 8 is the reference's "Too few inliers" (ORBX_E_DATA,
+ * R and t are still written). */
+int orbx_recover_pose(orbx_pose_estimator* pe, const double* E, const float* pts1, int n1, const float* pts2, int n2,
+                      double* R, double* t, uint8_t* mask, int* n_good);
+/* both steps for a batch of frame pairs (visual_odometry.rs:111-117 over a sequence), device pointers, asynchronous:
+ * problem p reads pts1 / pts2 + p*max_rows*2 floats (n_dev[p] points) and writes E + 9p, R + 9p, t + 3p,
+ * n_inliers[p], n_good[p], status[p] (ORBX_POSE_*), masks + p*max_rows (optional). */
+int orbx_estimate_pose_batch(orbx_pose_estimator* pe, const float* pts1, const float* pts2, const int* n_dev, int npairs,
+                             int max_rows, double* E, double* R, double* t, int* n_inliers, int* n_good, int* status,
+                             uint8_t* ransac_mask, uint8_t* pose_mask);
 
 /* ------------------------------------------------------------------ Triangulator
  * Device form of mapping::Triangulator (src/mapping/triangulation.rs:52-198).  Poses are world-to-camera

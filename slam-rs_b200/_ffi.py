@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "liborbx.so")
 
-OK, E_BADARG, E_CAPACITY, E_CUDA, E_NOMEM = 0, -1, -2, -3, -4
+OK, E_BADARG, E_CAPACITY, E_CUDA, E_NOMEM, E_DATA = 0, -1, -2, -3, -4, -5
 STAGES = ("pyramid", "fast", "harris", "select", "orient", "blur", "brief")
 
 
@@ -72,6 +72,13 @@ def _load():
         "orbx_map_prune_outliers": (i, [vp, ip]),
         "orbx_map_stable_count": (i, [vp, ip]),
         "orbx_map_read_observations": (i, [vp, vp, vp, i]),
+        "orbx_pose_estimator_create": (i, [i, i, i, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(vp)]),
+        "orbx_pose_estimator_destroy": (None, [vp]),
+        "orbx_pose_estimator_set_stream": (i, [vp, vp]),
+        "orbx_pose_estimator_sync": (i, [vp]),
+        "orbx_compute_essential_matrix": (i, [vp, vp, i, vp, i, vp, vp, ip, ip]),
+        "orbx_recover_pose": (i, [vp, vp, vp, i, vp, i, vp, vp, vp, ip]),
+        "orbx_estimate_pose_batch": (i, [vp, vp, vp, vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp]),
         "orbx_triangulator_create": (i, [i, i, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(vp)]),
         "orbx_triangulator_destroy": (None, [vp]),
         "orbx_triangulator_set_thresholds": (i, [vp, C.c_double, C.c_double]),

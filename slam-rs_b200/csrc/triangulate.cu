@@ -8,10 +8,12 @@
 // accumulation, unfused).  A second single-block kernel compacts the survivors in input order (id = i) and
 // attaches descriptor row i when i < desc_rows (:141-150).
 #include "common.cuh"
+#include "jacobi.cuh"
 
 using orbx::div_up;
 using orbx::g_launches;
 using orbx::is_device_ptr;
+using orbx::null_vector4;
 using orbx::set_error;
 
 struct orbx_triangulator {
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(128) triangulate_kernel(const float* __restric
                                                          double* __restrict__ xyz_all, uint8_t* __restrict__ keep) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  double a[4][4], v[4][4];
+  double a[4][4];
   {
     const double x1 = (double)pts1[2 * i], y1 = (double)pts1[2 * i + 1];
     const double x2 = (double)pts2[2 * i], y2 = (double)pts2[2 * i + 1];
@@ -63,59 +65,9 @@ __global__ void __launch_bounds__(128) triangulate_kernel(const float* __restric
       a[3][k] = __dsub_rn(__dmul_rn(y2, cams.P2[8 + k]), cams.P2[4 + k]);
     }
   }
-#pragma unroll
-  for (int r = 0; r < 4; ++r)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) v[r][c] = r == c ? 1.0 : 0.0;
-
-  // one-sided Jacobi (Hestenes): rotate column pairs of A until they are mutually orthogonal; V collects
-  // the rotations, the column of smallest norm is the null direction.
-  for (int sweep = 0; sweep < 16; ++sweep) {  // converges in 4-5 sweeps
-    bool rotated = false;
-#pragma unroll
-    for (int p = 0; p < 3; ++p) {
-#pragma unroll
-      for (int q = p + 1; q < 4; ++q) {
-        double alpha = 0, beta = 0, gamma = 0;
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          alpha += a[r][p] * a[r][p];
-          beta += a[r][q] * a[r][q];
-          gamma += a[r][p] * a[r][q];
-        }
-        if (fabs(gamma) <= 1e-15 * sqrt(alpha * beta) || gamma == 0.0) continue;
-        rotated = true;
-        const double zeta = (beta - alpha) / (2.0 * gamma);
-        const double t = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const double ap = a[r][p], aq = a[r][q];
-          a[r][p] = c * ap - s * aq;
-          a[r][q] = s * ap + c * aq;
-          const double vp = v[r][p], vq = v[r][q];
-          v[r][p] = c * vp - s * vq;
-          v[r][q] = s * vp + c * vq;
-        }
-      }
-    }
-    if (!rotated) break;
-  }
-  int best = 0;
-  double bn = 0;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    double nn = 0;
-#pragma unroll
-    for (int r = 0; r < 4; ++r) nn += a[r][c] * a[r][c];
-    if (c == 0 || nn < bn) bn = nn, best = c;
-  }
   double h[4];
-#pragma unroll
-  for (int r = 0; r < 4; ++r) h[r] = best == 0 ? v[r][0] : best == 1 ? v[r][1] : best == 2 ? v[r][2] : v[r][3];
-  // LAPACK returns a unit vector; the rotations keep V orthonormal to rounding, renormalise anyway
-  const double inv = 1.0 / sqrt(h[0] * h[0] + h[1] * h[1] + h[2] * h[2] + h[3] * h[3]);
-  const float fx = (float)(h[0] * inv), fy = (float)(h[1] * inv), fz = (float)(h[2] * inv), fw = (float)(h[3] * inv);
+  null_vector4(a, h);
+  const float fx = (float)h[0], fy = (float)h[1], fz = (float)h[2], fw = (float)h[3];
   if (p4) reinterpret_cast<float4*>(p4)[i] = make_float4(fx, fy, fz, fw);
 
   // triangulation.rs:121-136 in f64 on the f32 values

@@ -1,0 +1,124 @@
+"""GPU: csrc/pose.cu (PoseEstimator::compute_essential_matrix / recover_pose, pose.rs:47-114) through
+the C ABI vs cv2.findEssentialMat / cv2.recoverPose — the OpenCV functions the reference calls (cv2 is the oracle here;
+its numpy restatement is pinned in tests/test_pose_cpu.py).
+
+Floating point, so the bar is a tolerance: the kernels replay OpenCV's RANSAC draws, so on every scene the SAME
+hypothesis must win — E equal up to sign to 1e-6 (different five-point arithmetic: Gauss-Jordan + bisection here, SVD +
+companion eigenvalues there), identical inlier masks except points whose fp32 Sampson error sits within 1e-4 relative
+of the threshold, R / t within 1e-6.
+"""
+import numpy as np
+import pytest
+
+from tests.test_pose_cpu import two_view_scene, K, KITTI
+
+pytestmark = pytest.mark.gpu
+cv2 = pytest.importorskip("cv2")
+
+
+@pytest.fixture(scope="module")
+def orbx():
+    import slam_rs_b200 as s
+    return s
+
+
+def e_diff(a, b):
+    return min(np.abs(a - b).max(), np.abs(a + b).max())
+
+
+@pytest.mark.parametrize("n,seed,outliers", [(500, 1, 0.25), (2000, 2, 0.3), (64, 3, 0.1), (1500, 4, 0.5), (9, 5, 0.0)])
+def test_essential_matrix_vs_cv2(orbx, n, seed, outliers):
+    p1, p2, _, _ = two_view_scene(n, seed, outliers=outliers)
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics.kitti(), max_points=4096)
+    E = pe.compute_essential_matrix(p1, p2)
+    Ecv, mcv = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    assert Ecv.shape == (3, 3)
+    assert e_diff(E, Ecv) < 1e-6, (E, Ecv)
+    mcv = mcv.ravel() != 0
+    assert abs(np.linalg.norm(E) - 1.0) < 1e-12
+    assert (pe.last_mask != mcv).sum() <= max(1, n // 500)
+    assert abs(pe.last_inliers - int(mcv.sum())) <= max(1, n // 500)
+    assert 0 < pe.last_iterations <= 1000
+
+
+@pytest.mark.parametrize("seed", [6, 7, 8])
+def test_recover_pose_vs_cv2(orbx, seed):
+    p1, p2, Rt, tt = two_view_scene(800, seed, outliers=0.15)
+    Ecv, _ = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    good, Rcv, tcv, mcv = cv2.recoverPose(Ecv, p1, p2, K)
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics.kitti(), max_points=1024)
+    R, t = pe.recover_pose(Ecv, p1, p2)
+    assert np.abs(R - Rcv).max() < 1e-6 and np.abs(t - tcv.ravel()).max() < 1e-6
+    assert pe.last_good == good and np.array_equal(pe.last_pose_mask, mcv.ravel() != 0)
+    assert np.abs(R - Rt).max() < 0.02 and abs(np.linalg.det(R) - 1.0) < 1e-9
+
+
+def test_full_chain_like_visual_odometry(orbx):
+    """visual_odometry.rs:111-117: matched points -> E -> (R, t), from our own E."""
+    p1, p2, Rt, tt = two_view_scene(1200, 9, outliers=0.2)
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics.kitti(), max_points=2048)
+    E = pe.compute_essential_matrix(p1, p2)
+    R, t = pe.recover_pose(E, p1, p2)
+    Ecv, _ = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    _, Rcv, tcv, _ = cv2.recoverPose(Ecv, p1, p2, K)
+    assert np.abs(R - Rcv).max() < 1e-5 and np.abs(t - tcv.ravel()).max() < 1e-5
+    tn = tt / np.linalg.norm(tt)
+    assert np.abs(R - Rt).max() < 0.02 and np.abs(t - tn).max() < 0.05
+
+
+def test_reference_error_cases(orbx):
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics.kitti(), max_points=256)
+    p = np.zeros((7, 2), np.float32)
+    with pytest.raises(orbx.OrbxError, match="Insufficient points: 7"):        # pose.rs:52-59
+        pe.compute_essential_matrix(p, p)
+    # degenerate input: all points identical -> cv2 returns a model or none; ours must not crash and must say which
+    q = np.tile(np.array([[100.0, 100.0]], np.float32), (20, 1))
+    try:
+        pe.compute_essential_matrix(q, q)
+    except orbx.OrbxError as e:
+        assert e.code == -5
+    # recover_pose with points that cannot be in front of any candidate: "Too few inliers" (pose.rs:104-106)
+    p1, p2, _, _ = two_view_scene(200, 10, outliers=0.0)
+    Ecv, _ = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    with pytest.raises(orbx.OrbxError, match="Too few inliers"):
+        pe.recover_pose(Ecv, p1[:4], p2[:4])
+    with pytest.raises(orbx.OrbxError):
+        pe.compute_essential_matrix(np.zeros((300, 2), np.float32), np.zeros((300, 2), np.float32))   # > max_points
+
+
+def test_batch_device_matches_single_calls(orbx):
+    import torch
+    npairs, rows = 12, 700
+    cam = orbx.CameraIntrinsics.kitti()
+    pe = orbx.PoseEstimator(cam, max_points=rows, max_problems=npairs)
+    single = orbx.PoseEstimator(cam, max_points=rows)
+    P1 = np.zeros((npairs, rows, 2), np.float32)
+    P2 = np.zeros((npairs, rows, 2), np.float32)
+    ns = np.zeros(npairs, np.int32)
+    for p in range(npairs):
+        n = [650, 300, 5, 700, 40][p % 5]                                      # one problem has too few points
+        a, b, _, _ = two_view_scene(n, 100 + p, outliers=0.2)
+        P1[p, :n], P2[p, :n], ns[p] = a, b, n
+    dev = torch.device("cuda", 0)
+    d1, d2, dn = torch.from_numpy(P1).to(dev), torch.from_numpy(P2).to(dev), torch.from_numpy(ns).to(dev)
+    E = torch.zeros((npairs, 3, 3), dtype=torch.float64, device=dev)
+    R = torch.zeros((npairs, 3, 3), dtype=torch.float64, device=dev)
+    t = torch.zeros((npairs, 3), dtype=torch.float64, device=dev)
+    ni = torch.zeros(npairs, dtype=torch.int32, device=dev)
+    ng = torch.zeros(npairs, dtype=torch.int32, device=dev)
+    st = torch.zeros(npairs, dtype=torch.int32, device=dev)
+    rm = torch.zeros((npairs, rows), dtype=torch.uint8, device=dev)
+    pe.estimate_pose_batch_device(d1, d2, dn, npairs, rows, E, R, t, ni, ng, st, rm, None)
+    torch.cuda.synchronize()
+    for p in range(npairs):
+        n = int(ns[p])
+        if n < 8:
+            assert int(st[p]) == 1
+            continue
+        Es = single.compute_essential_matrix(P1[p, :n], P2[p, :n])
+        Rs, ts = single.recover_pose(Es, P1[p, :n], P2[p, :n])
+        assert int(st[p]) == 0
+        assert np.array_equal(E[p].cpu().numpy(), Es) and int(ni[p]) == single.last_inliers
+        assert np.array_equal(rm[p, :n].cpu().numpy() != 0, single.last_mask)
+        assert np.array_equal(R[p].cpu().numpy(), Rs) and np.array_equal(t[p].cpu().numpy(), ts)
+        assert int(ng[p]) == single.last_good

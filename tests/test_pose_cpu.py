@@ -73,3 +73,51 @@ def test_recover_pose_vs_cv2(seed):
     assert good == n and np.array_equal(m, mcv.ravel() != 0)
     assert np.abs(R - Rcv).max() < 1e-9 and np.abs(t - tcv.ravel()).max() < 1e-9
     assert np.abs(R - Rt).max() < 0.02                                         # and it is the true motion
+
+
+def _host_solver():
+    """The five-point solver and root finder of csrc/pose.cu (the section between the ORBX_HOST_TESTABLE markers is
+    plain C++) compiled for the host — a test harness for the device code's arithmetic, not a product path."""
+    import ctypes as C
+    import os
+    import subprocess
+    import tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    s = open(os.path.join(root, "slam-rs_b200", "csrc", "pose.cu")).read()
+    tables = s[s.index("// ORBX_HOST_TESTABLE_BEGIN"):s.index("// ORBX_HOST_TESTABLE_SPLIT")]
+    body = s[s.index("// ORBX_HOST_TESTABLE_RESUME"):s.index("// ORBX_HOST_TESTABLE_END")]
+    src = ("#include <math.h>\n#include <algorithm>\n#define __device__\n#define __constant__ static const\n"
+           "#define __forceinline__ inline\n#define __restrict__\nconstexpr int kPoseMaxModels = 10;\n" + tables + body +
+           "extern \"C\" int solve5(const double* x1, const double* x2, double* m) { double a[5][2], b[5][2];\n"
+           "  for (int i = 0; i < 5; ++i) { a[i][0] = x1[2*i]; a[i][1] = x1[2*i+1]; b[i][0] = x2[2*i]; b[i][1] = x2[2*i+1]; }\n"
+           "  return five_point_solve(a, b, m); }\n"
+           "extern \"C\" int roots(const double* c, int deg, double* r) { return real_roots(c, deg, r); }\n")
+    d = tempfile.mkdtemp(prefix="orbx_pose_host_")
+    open(os.path.join(d, "host.cpp"), "w").write(src)
+    subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-o", os.path.join(d, "libhost.so"), os.path.join(d, "host.cpp")])
+    return C.CDLL(os.path.join(d, "libhost.so"))
+
+
+def test_device_solver_arithmetic_on_host():
+    import ctypes as C
+    lib = _host_solver()
+    rng = np.random.default_rng(0)
+    for _ in range(200):                                                       # real roots of random degree-10 polynomials
+        c = rng.normal(0, 1, 11)
+        r = np.zeros(10)
+        n = lib.roots(C.c_void_p(c.ctypes.data), 10, C.c_void_p(r.ctypes.data))
+        ref = np.roots(c[::-1])
+        ref = np.sort(ref[np.abs(ref.imag) < 1e-10].real)
+        assert n == len(ref) and (n == 0 or np.abs((r[:n] - ref) / np.maximum(1, np.abs(ref))).max() < 1e-8)
+
+    def solve(x1, x2):
+        out = np.zeros((10, 9))
+        n = lib.solve5(C.c_void_p(np.ascontiguousarray(x1).ctypes.data), C.c_void_p(np.ascontiguousarray(x2).ctypes.data),
+                       C.c_void_p(out.ctypes.data))
+        return [out[i].reshape(3, 3) for i in range(n)]
+    for seed in (11, 12):                                                      # the whole RANSAC with this solver == cv2
+        p1, p2, _, _ = two_view_scene(500, seed)
+        Ecv, mcv = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+        E, m, _ = PR.find_essential_mat(p1, p2, KITTI, solver=solve)
+        assert min(np.abs(E - Ecv).max(), np.abs(E + Ecv).max()) < 1e-6
+        assert np.array_equal(m, mcv.ravel().astype(bool))
