@@ -242,7 +242,8 @@ def run_ours(args, rank, world, local_rank):
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
                           ratio=RATIO, cross_check=True, overlap=args.overlap,
-                          host_chunk=args.host_chunk, dual=args.dual)
+                          host_chunk=args.host_chunk, dual=args.dual,
+                          pose=orbx.CameraIntrinsics.kitti() if args.pose else None)
     frames_pinned = torch.from_numpy(frames).pin_memory()
     frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
     frames_dev[:, :, :W_IMG].copy_(frames_pinned)
@@ -394,7 +395,7 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "host_chunk": args.host_chunk, "e2e_streams": 2 if args.dual else 1,
+            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "pose_stage": bool(args.pose), "host_chunk": args.host_chunk, "e2e_streams": 2 if args.dual else 1,
                        "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (T * H_IMG * fe.pitch / 1e6),
                        "keypoints_per_frame": K_mean, "fast_candidates_frame0": cand0,
                        "good_matches_per_pair": n_good / max(T - 1, 1)},
@@ -569,6 +570,9 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=500, help="frames of the sequence timed for cpu_baseline")
     ap.add_argument("--ref-frames", type=int, default=250, help="frames per step of the reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--pose", action="store_true",
+                    help="also run PoseEstimator (essential-matrix RANSAC + recoverPose, SURVEY 8 f2) on every pair inside the "
+                         "timed region; not part of the headline metric")
     ap.add_argument("--numa-bind", type=int, default=1, help="N>1: bind each rank to its GPU's local CPUs")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "map"],
                     help="sequence = configs[1] (default, the metric's workload); map = configs[3] map-to-frame matching")

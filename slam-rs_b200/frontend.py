@@ -20,7 +20,7 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
                  ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None,
-                 dual=False, points=False):
+                 dual=False, points=False, pose=None):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
@@ -52,11 +52,23 @@ class SequenceFrontEnd:
             self.ref_good = torch.zeros((T, cap, 16), dtype=u8, device=self.dev)
             self.n_ref_good = torch.zeros((T,), dtype=i32, device=self.dev)
         # points=True: also emit PoseEstimator::extract_matched_points (pose.rs:27-44) of every pair's good matches
-        self.points = bool(points)
+        # pose=CameraIntrinsics: also run compute_essential_matrix + recover_pose (pose.rs:47-114) on every pair's
+        # matched points (visual_odometry.rs:111-117), batched on the device (implies points=True)
+        self.pose_intrinsics = pose
+        self.points = bool(points) or pose is not None
         if self.points:
             self.pts1 = torch.zeros((T, cap, 2), dtype=torch.float32, device=self.dev)
             self.pts2 = torch.zeros((T, cap, 2), dtype=torch.float32, device=self.dev)
             self.bad_index = torch.zeros((1,), dtype=i32, device=self.dev)
+        if pose is not None:
+            f64 = torch.float64
+            self.pose_E = torch.zeros((T, 3, 3), dtype=f64, device=self.dev)
+            self.pose_R = torch.zeros((T, 3, 3), dtype=f64, device=self.dev)
+            self.pose_t = torch.zeros((T, 3), dtype=f64, device=self.dev)
+            self.pose_inliers = torch.zeros((T,), dtype=i32, device=self.dev)
+            self.pose_good = torch.zeros((T,), dtype=i32, device=self.dev)
+            self.pose_status = torch.zeros((T,), dtype=i32, device=self.dev)
+            self._pose_chunk = int(min(self.chunk, 256))
         # staging for the host path
         self.frames_dev = torch.zeros((T, self.h, self.pitch), dtype=u8, device=self.dev)
         self.copy_stream = torch.cuda.Stream(device=self.dev)
@@ -80,6 +92,16 @@ class SequenceFrontEnd:
             self.stream2 = torch.cuda.Stream(device=self.dev)
             self.det2.set_stream(self.stream2.cuda_stream)
             self.matcher2.set_stream(self.stream2.cuda_stream)
+        if pose is not None:
+            from .odometry import PoseEstimator
+            # one estimator (scratch + stream) per pipeline stream
+            self.pose_est = PoseEstimator(pose, device=device, matcher=self.matcher, max_points=cap,
+                                          max_problems=self._pose_chunk)
+            self.pose_est.set_stream(self.mstream.cuda_stream)
+            if self.dual:
+                self.pose_est2 = PoseEstimator(pose, device=device, matcher=self.matcher2, max_points=cap,
+                                               max_problems=self._pose_chunk)
+                self.pose_est2.set_stream(self.stream2.cuda_stream)
 
     # ------------------------------------------------------------------ stages
     def extract(self, frames_dev, t0, t1, det=None, step=None):
@@ -107,6 +129,14 @@ class SequenceFrontEnd:
             m.extract_matched_points_batch_device(self.kps[a - 1], self.n[a - 1:], self.kps[a], self.n[a:], cap,
                                                   self.good[a], self.n_good[a:], npairs, cap, self.pts1[a],
                                                   self.pts2[a], self.bad_index)
+        if self.pose_intrinsics is not None:
+            pe = self.pose_est2 if (self.dual and m is self.matcher2) else self.pose_est
+            for b0 in range(0, npairs, self._pose_chunk):
+                nb = min(self._pose_chunk, npairs - b0)
+                t0_ = a + b0
+                pe.estimate_pose_batch_device(self.pts1[t0_], self.pts2[t0_], self.n_good[t0_:], nb, cap,
+                                              self.pose_E[t0_], self.pose_R[t0_], self.pose_t[t0_],
+                                              self.pose_inliers[t0_:], self.pose_good[t0_:], self.pose_status[t0_:])
         if self.reference_filter:
             m.match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs,
                                  cap, self.m1[a], self.n_m1[a:])
@@ -231,6 +261,11 @@ class SequenceFrontEnd:
         """(points1, points2) of pair (t-1, t): float32 [n_good, 2] each (synchronises)."""
         n = int(self.n_good[t].item())
         return self.pts1[t, :n].cpu().numpy(), self.pts2[t, :n].cpu().numpy()
+
+    def pair_pose(self, t):
+        """(E, R, t, ransac_inliers, points_in_front, status) of pair (t-1, t) (synchronises); status = ORBX_POSE_*."""
+        return (self.pose_E[t].cpu().numpy(), self.pose_R[t].cpu().numpy(), self.pose_t[t].cpu().numpy(),
+                int(self.pose_inliers[t].item()), int(self.pose_good[t].item()), int(self.pose_status[t].item()))
 
     def pair_knn(self, t):
         nq = min(int(self.n[t - 1].item()), self.cap)

@@ -10,6 +10,7 @@ of the threshold, R / t within 1e-6.
 import numpy as np
 import pytest
 
+from oracle import pose_restated as PR
 from tests.test_pose_cpu import two_view_scene, K, KITTI
 
 pytestmark = pytest.mark.gpu
@@ -122,3 +123,65 @@ def test_batch_device_matches_single_calls(orbx):
         assert np.array_equal(rm[p, :n].cpu().numpy() != 0, single.last_mask)
         assert np.array_equal(R[p].cpu().numpy(), Rs) and np.array_equal(t[p].cpu().numpy(), ts)
         assert int(ng[p]) == single.last_good
+
+
+def test_sequence_front_end_pose(orbx):
+    """SequenceFrontEnd(pose=intrinsics): frames -> keypoints -> matches -> matched points -> E -> (R, t) without leaving
+    the device; every pair agrees with cv2 run on the same matched points (both pipeline forms)."""
+    import torch
+    from oracle import synth
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 9, 376, 1241, 1000
+    # 24 px of image shift per frame: depth f / 24 = 30 baselines, inside cv::recoverPose's distance threshold of 50
+    # (the 3 px / frame of the benchmark sequence puts every point at 240 and OpenCV, like us, keeps none)
+    seq = synth.sequence(h, w, T, canvas_seed=31, shift=24)
+    cam = orbx.CameraIntrinsics.kitti()
+    same = pairs = 0
+    for kwargs in ({"chunk": T}, {"chunk": T, "host_chunk": 3, "dual": True}):
+        fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, pose=cam, **kwargs)
+        if "dual" in kwargs:
+            out = fe.alloc_host_outputs()
+            fe.run_host(torch.from_numpy(seq).pin_memory(), out)
+        else:
+            dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
+            dev[:, :, :w] = torch.from_numpy(seq).cuda()
+            fe.run_device(dev)
+        torch.cuda.synchronize()
+        for t in range(1, T):
+            p1, p2 = fe.pair_points(t)
+            E, R, tv, ninl, good, status = fe.pair_pose(t)
+            assert status == 0 and len(p1) >= 8, (status, len(p1), good)
+            Ecv, mcv = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+            # The synthetic scene is ONE fronto-parallel plane: the degenerate case of the five-point problem.  Every
+            # sample has two valid solutions (the planar two-fold ambiguity) that explain all points equally well, the
+            # first one in solver order keeps the lead (strict >), and OpenCV's solution order (that of cv::solvePoly's
+            # roots) is not reproduced.  So: either the same model (E within 1e-4, conditioning shows) and then the same
+            # pose, or a tie — our model has as many inliers under the oracle's own error function as cv2's has.
+            ncv = int(mcv.sum())
+            assert abs(ninl - ncv) <= max(2, len(p1) // 100)
+            if e_diff(E, Ecv) < 1e-4:
+                same += 1
+                g, Rcv, tcv, _ = cv2.recoverPose(Ecv, p1, p2, K)
+                assert np.abs(R - Rcv).max() < 1e-3 and np.abs(tv - tcv.ravel()).max() < 1e-3
+                assert abs(good - g) <= max(2, len(p1) // 100)
+            else:
+                x1, x2 = PR.normalize_points(p1, KITTI), PR.normalize_points(p2, KITTI)
+                thr = np.float32((1.0 / KITTI[0]) ** 2)
+                assert int((PR.sampson_errors(E, x1, x2) <= thr).sum()) >= ncv - max(2, len(p1) // 100)
+                g, Rm, tm, _ = cv2.recoverPose(E, p1, p2, K)                    # our E through OpenCV's recoverPose
+                assert np.abs(R - Rm).max() < 1e-3 and np.abs(tv - tm.ravel()).max() < 1e-3
+            pairs += 1
+    assert same >= pairs // 2, (same, pairs)
+    # the benchmark sequence itself (3 px / frame): every point is farther than 50 baselines, so cv::recoverPose keeps
+    # none and the reference reports "Too few inliers" (pose.rs:104-106) — same here
+    seq3 = synth.sequence(h, w, 3, canvas_seed=31)
+    fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=3, pose=cam, chunk=3)
+    dev = torch.zeros((3, h, fe.pitch), dtype=torch.uint8, device="cuda")
+    dev[:, :, :w] = torch.from_numpy(seq3).cuda()
+    fe.run_device(dev)
+    torch.cuda.synchronize()
+    p1, p2 = fe.pair_points(1)
+    E, R, tv, ninl, good, status = fe.pair_pose(1)
+    Ecv, mcv = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, 1000)
+    g, _, _, _ = cv2.recoverPose(Ecv, p1, p2, K)
+    assert abs(ninl - int(mcv.sum())) <= max(2, len(p1) // 100) and (status == 3) == (g < 8)
