@@ -8,7 +8,7 @@ fn main() {
     let out = PathBuf::from(env::var("OUT_DIR").unwrap());
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     let mut objs = vec![];
-    for f in ["api", "match", "detector", "pyramid", "fast", "select", "brief", "ingest", "mapstore", "triangulate"] {
+    for f in ["api", "match", "detector", "pyramid", "fast", "select", "brief", "ingest", "mapstore", "triangulate", "pose"] {
         let src = csrc.join(format!("{f}.cu"));
         let obj = out.join(format!("{f}.o"));
         let st = Command::new(&nvcc)

@@ -13,6 +13,8 @@ pub enum orbx_detector {}
 pub enum orbx_matcher {}
 pub enum orbx_map {}
 pub enum orbx_triangulator {}
+pub enum orbx_pose_estimator {}
+pub const ORBX_E_DATA: c_int = -5;
 pub const ORBX_OK: c_int = 0;
 pub const ORBX_E_CAPACITY: c_int = -2;
 
@@ -41,6 +43,13 @@ extern "C" {
     pub fn orbx_map_update_observations(m: *mut orbx_map, pairs: *const c_int, n: c_int) -> c_int;
     pub fn orbx_map_prune_outliers(m: *mut orbx_map, removed: *mut c_int) -> c_int;
     pub fn orbx_map_stable_count(m: *mut orbx_map, count: *mut c_int) -> c_int;
+    pub fn orbx_pose_estimator_create(device: c_int, max_points: c_int, max_problems: c_int, fx: f64, fy: f64, cx: f64, cy: f64, out: *mut *mut orbx_pose_estimator) -> c_int;
+    pub fn orbx_pose_estimator_destroy(pe: *mut orbx_pose_estimator);
+    pub fn orbx_pose_estimator_set_stream(pe: *mut orbx_pose_estimator, stream: *mut c_void) -> c_int;
+    pub fn orbx_pose_estimator_sync(pe: *mut orbx_pose_estimator) -> c_int;
+    pub fn orbx_compute_essential_matrix(pe: *mut orbx_pose_estimator, pts1: *const f32, n1: c_int, pts2: *const f32, n2: c_int, e: *mut f64, mask: *mut u8, n_inliers: *mut c_int, iterations: *mut c_int) -> c_int;
+    pub fn orbx_recover_pose(pe: *mut orbx_pose_estimator, e: *const f64, pts1: *const f32, n1: c_int, pts2: *const f32, n2: c_int, r: *mut f64, t: *mut f64, mask: *mut u8, n_good: *mut c_int) -> c_int;
+    pub fn orbx_estimate_pose_batch(pe: *mut orbx_pose_estimator, pts1: *const f32, pts2: *const f32, n_dev: *const c_int, npairs: c_int, max_rows: c_int, e: *mut f64, r: *mut f64, t: *mut f64, n_inliers: *mut c_int, n_good: *mut c_int, status: *mut c_int, ransac_mask: *mut u8, pose_mask: *mut u8) -> c_int;
     pub fn orbx_triangulator_create(device: c_int, max_points: c_int, fx: f64, fy: f64, cx: f64, cy: f64, out: *mut *mut orbx_triangulator) -> c_int;
     pub fn orbx_triangulator_destroy(t: *mut orbx_triangulator);
     pub fn orbx_triangulator_set_thresholds(t: *mut orbx_triangulator, min_parallax_deg: f64, max_reproj_error: f64) -> c_int;

@@ -406,44 +406,59 @@ __device__ __forceinline__ float sampson_f32(const double* E, double ax, double 
   return (float)__ddiv_rn(__dmul_rn(num, num), den);
 }
 
-// one block per hypothesis: inlier count of each of its models over all points
-__global__ void __launch_bounds__(128) pose_count_kernel(const PoseState* __restrict__ st, int wave, PoseParams pp,
+// sampson_f32(...) <= thr without the f64 division except next to the threshold
+__device__ __forceinline__ bool sampson_inlier(const double* E, double ax, double ay, double bx, double by, float thr,
+                                               double bound) {
+  const double e0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], ax), __dmul_rn(E[1], ay)), E[2]);
+  const double e1 = __dadd_rn(__dadd_rn(__dmul_rn(E[3], ax), __dmul_rn(E[4], ay)), E[5]);
+  const double e2 = __dadd_rn(__dadd_rn(__dmul_rn(E[6], ax), __dmul_rn(E[7], ay)), E[8]);
+  const double t0 = __dadd_rn(__dadd_rn(__dmul_rn(E[0], bx), __dmul_rn(E[3], by)), E[6]);
+  const double t1 = __dadd_rn(__dadd_rn(__dmul_rn(E[1], bx), __dmul_rn(E[4], by)), E[7]);
+  const double num = __dadd_rn(__dadd_rn(__dmul_rn(bx, e0), __dmul_rn(by, e1)), e2);
+  const double den = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(e0, e0), __dmul_rn(e1, e1)), __dmul_rn(t0, t0)), __dmul_rn(t1, t1));
+  const double n2 = __dmul_rn(num, num), lim = bound * den;
+  if (n2 < lim * (1.0 - 1e-9)) return true;
+  if (n2 > lim * (1.0 + 1e-9) || !(den > 0.0)) return den > 0.0 ? false : (float)__ddiv_rn(n2, den) <= thr;
+  return (float)__ddiv_rn(n2, den) <= thr;
+}
+
+// blocks loop over the hypotheses of the wave: inlier count of each of a hypothesis' models over all points
+__global__ void __launch_bounds__(128, 8) pose_count_kernel(const PoseState* __restrict__ st, int wave, PoseParams pp,
                                                         const double* __restrict__ x1, const double* __restrict__ x2,
                                                         const double* __restrict__ models, const int* __restrict__ nmodels,
                                                         int* __restrict__ counts) {
   __shared__ double s_E[kPoseMaxModels * 9];
   __shared__ int s_cnt[kPoseMaxModels];
   const int p = blockIdx.y;
-  const int it = c_wave[wave] + blockIdx.x;
-  if (it >= st[p].niters) return;
+  const int n = st[p].n;
+  const int it_end = min(c_wave[wave + 1], st[p].niters);
+  const float thr = (float)pp.thr2f;
+  // (float)(num^2 / den) <= thr  <=>  num^2 / den < thr + half an fp32 ulp (thr's mantissa is odd or even: the tie
+  // case is decided by the exact path); the division is only needed within 1e-9 of that bound
+  const double bound = (double)thr + 0.5 * ((double)nextafterf(thr, 2.0f * thr) - (double)thr);
+  for (int it = c_wave[wave] + blockIdx.x; it < it_end; it += gridDim.x) {
   const size_t h = (size_t)p * kPoseMaxIters + it;
   const int nm = nmodels[h];
-  if (nm == 0) return;
-  const int n = st[p].n;
+  if (nm == 0) continue;
+  __syncthreads();
   if (threadIdx.x < nm * 9) s_E[threadIdx.x] = models[h * (kPoseMaxModels * 9) + threadIdx.x];
   if (threadIdx.x < kPoseMaxModels) s_cnt[threadIdx.x] = 0;
   __syncthreads();
-  const float thr = (float)pp.thr2f;
-  int cnt[kPoseMaxModels];
-#pragma unroll
-  for (int m = 0; m < kPoseMaxModels; ++m) cnt[m] = 0;
   const size_t base = (size_t)p * pp.max_rows;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const double ax = x1[2 * (base + i)], ay = x1[2 * (base + i) + 1];
-    const double bx = x2[2 * (base + i)], by = x2[2 * (base + i) + 1];
-#pragma unroll
-    for (int m = 0; m < kPoseMaxModels; ++m)
-      if (m < nm) cnt[m] += sampson_f32(s_E + 9 * m, ax, ay, bx, by) <= thr;
-  }
-#pragma unroll
-  for (int m = 0; m < kPoseMaxModels; ++m) {
-    if (m >= nm) break;
-    int v = cnt[m];
+  for (int m = 0; m < nm; ++m) {
+    const double* E = s_E + 9 * m;
+    int v = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const double2 a = reinterpret_cast<const double2*>(x1)[base + i];
+      const double2 b = reinterpret_cast<const double2*>(x2)[base + i];
+      v += sampson_inlier(E, a.x, a.y, b.x, b.y, thr, bound);
+    }
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[m], v);
   }
   __syncthreads();
   if (threadIdx.x < nm) counts[h * kPoseMaxModels + threadIdx.x] = s_cnt[threadIdx.x];
+  }
 }
 
 // RANSACUpdateNumIters
@@ -690,7 +705,7 @@ int run_essential(orbx_pose_estimator* pe, const float* pts1, const float* pts2,
     pose_solve_kernel<<<dim3(div_up(len, 32), np), 32, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->samples, pe->models,
                                                              pe->nmodels);
     ORBX_LAUNCH_CHECK();
-    pose_count_kernel<<<dim3(len, np), 128, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->models, pe->nmodels, pe->counts);
+    pose_count_kernel<<<dim3(std::min(len, 32), np), 128, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->models, pe->nmodels, pe->counts);
     ORBX_LAUNCH_CHECK();
     pose_scan_kernel<<<np, 32, 0, s>>>(pe->state, w, pp, pe->nmodels, pe->counts);
     ORBX_LAUNCH_CHECK();
