@@ -122,47 +122,57 @@ __global__ void pose_sample_kernel(PoseState* __restrict__ st, int wave, int* __
 
 // ------------------------------------------------------------------------------------------------ five-point
 // ORBX_HOST_TESTABLE_RESUME
-__device__ __forceinline__ double horner(const double* c, int deg, double z) {
-  double v = c[deg];
-  for (int i = deg - 1; i >= 0; --i) v = v * z + c[i];
+// The solver's large per-thread arrays live in a strided scratch area: element k of a thread is sm[k * SS].  On the
+// device SS = 32 and sm points into shared memory at the thread's lane (conflict-free for any per-thread index; the
+// arrays are indexed dynamically, so the alternative is local memory that falls out of L1); the host harness uses
+// SS = 1.  Layout (doubles): M 10x20 at 0 (aliased first by the 5x9 epipolar system, later by the derivative table
+// of the root finder), EEt 3x3x10 at 200, the null-space basis 4x9 at 290.
+constexpr int kSolveScratch = 326;
+
+template <int SS>
+__device__ __forceinline__ double horner_s(const double* c, int deg, double z) {
+  double v = c[deg * SS];
+  for (int i = deg - 1; i >= 0; --i) v = v * z + c[i * SS];
   return v;
 }
 
+__device__ __forceinline__ double horner(const double* c, int deg, double z) { return horner_s<1>(c, deg, z); }
+
 // real roots of a polynomial of degree <= 10 (ascending coefficients): between consecutive real roots of p' the
 // polynomial is monotonic, so the roots of p^(k) bracket those of p^(k-1); every bracket with a sign change is
-// bisected.  Returns the number of roots written (ascending).
-__device__ int real_roots(const double* coef, int deg, double* roots) {
+// bisected.  d: scratch for the derivative table (11 x 11, strided).  Returns the number of roots (ascending).
+template <int SS>
+__device__ int real_roots(const double* coef, int deg, double* roots, double* d) {
   while (deg > 0 && coef[deg] == 0.0) --deg;
   if (deg <= 0) return 0;
-  double d[11][11];  // d[k] = coefficients of the k-th derivative (degree deg - k)
-  for (int i = 0; i <= deg; ++i) d[0][i] = coef[i];
+#define D_(k, i) d[((k) * 11 + (i)) * SS]
+  for (int i = 0; i <= deg; ++i) D_(0, i) = coef[i];
   for (int k = 1; k < deg; ++k)
-    for (int i = 0; i <= deg - k; ++i) d[k][i] = d[k - 1][i + 1] * (double)(i + 1);
+    for (int i = 0; i <= deg - k; ++i) D_(k, i) = D_(k - 1, i + 1) * (double)(i + 1);
   double prev[10], cur[10];
-  int nprev = 0;
-  // linear polynomial d[deg - 1]
-  prev[0] = -d[deg - 1][0] / d[deg - 1][1];
-  nprev = 1;
+  int nprev = 1;
+  prev[0] = -D_(deg - 1, 0) / D_(deg - 1, 1);  // the linear one
   for (int k = deg - 2; k >= 0; --k) {
     const int dg = deg - k;
-    const double* c = d[k];
-    // Cauchy bound of this polynomial
-    double mx = 0;
-    for (int i = 0; i < dg; ++i) mx = fmax(mx, fabs(c[i] / c[dg]));
+    const double* c = &D_(k, 0);
+    double mx = 0;  // Cauchy bound of this polynomial
+    for (int i = 0; i < dg; ++i) mx = fmax(mx, fabs(c[i * SS] / c[dg * SS]));
     const double B = 1.0 + mx;
     int ncur = 0;
-    double lo = -B, flo = horner(c, dg, lo);
+    double lo = -B, flo = horner_s<SS>(c, dg, lo);
     for (int j = 0; j <= nprev; ++j) {
-      double hi = j < nprev ? fmin(fmax(prev[j], -B), B) : B;
-      double fhi = horner(c, dg, hi);
+      const double hi = j < nprev ? fmin(fmax(prev[j], -B), B) : B;
+      const double fhi = horner_s<SS>(c, dg, hi);
       if (flo == 0.0) {
         if (ncur == 0 || cur[ncur - 1] != lo) cur[ncur++] = lo;
       } else if ((flo < 0.0) != (fhi < 0.0) && fhi != 0.0) {
+        // 34 bisection steps (2^-34 of the bracket is plenty for the critical points, which only serve as brackets of
+        // the next level), then - for the polynomial itself - Newton steps inside the bracket down to rounding
         double a = lo, b = hi, fa = flo;
-        for (int itr = 0; itr < 200; ++itr) {
+        for (int itr = 0; itr < 34; ++itr) {
           const double m = 0.5 * (a + b);
           if (m == a || m == b) break;
-          const double fm = horner(c, dg, m);
+          const double fm = horner_s<SS>(c, dg, m);
           if (fm == 0.0) {
             a = b = m;
             break;
@@ -171,6 +181,22 @@ __device__ int real_roots(const double* coef, int deg, double* roots) {
             a = m, fa = fm;
           else
             b = m;
+        }
+        if (k == 0 && a != b) {
+          double x = 0.5 * (a + b);
+          for (int itr = 0; itr < 6; ++itr) {
+            double f = c[dg * SS], df = 0.0;
+            for (int i = dg - 1; i >= 0; --i) {
+              df = df * x + f;
+              f = f * x + c[i * SS];
+            }
+            const double xn = x - f / df;
+            if (!(xn >= a && xn <= b)) break;  // also catches df == 0
+            const bool done = fabs(xn - x) <= 4.5e-16 * fabs(xn);
+            x = xn;
+            if (done) break;
+          }
+          a = b = x;
         }
         cur[ncur++] = 0.5 * (a + b);
       }
@@ -181,177 +207,219 @@ __device__ int real_roots(const double* coef, int deg, double* roots) {
     if (flo == 0.0 && ncur < dg && (ncur == 0 || cur[ncur - 1] != lo)) cur[ncur++] = lo;
     nprev = ncur;
     for (int j = 0; j < ncur; ++j) prev[j] = cur[j];
-    if (nprev == 0 && k > 0) {
-      // no critical point at this level: the next polynomial is monotonic over the whole line; keep going with an
-      // empty bracket list (one interval [-B, B])
-    }
   }
+#undef D_
   for (int j = 0; j < nprev; ++j) roots[j] = prev[j];
   return nprev;
 }
 
 // x1, x2: the five normalised correspondences.  Writes up to 10 unit-norm essential matrices (row major).
-__device__ int five_point_solve(const double (&x1)[5][2], const double (&x2)[5][2], double* __restrict__ models) {
+template <int SS>
+__device__ int five_point_solve(const double (&x1)[5][2], const double (&x2)[5][2], double* __restrict__ models,
+                                double* __restrict__ sm) {
+#define Q_(i, j) sm[((i) * 9 + (j)) * SS]
+#define M_(i, j) sm[((i) * 20 + (j)) * SS]
+#define EET_(i, j, m) sm[(200 + ((i) * 3 + (j)) * 10 + (m)) * SS]
+#define EB_(k, j) sm[(290 + (k) * 9 + (j)) * SS]
   // ---- null space of the 5 x 9 epipolar system by Gauss-Jordan with full pivoting, then Gram-Schmidt
-  double q[5][9];
   for (int i = 0; i < 5; ++i) {
     const double a = x1[i][0], b = x1[i][1], c = x2[i][0], d = x2[i][1];
-    q[i][0] = c * a, q[i][1] = c * b, q[i][2] = c;
-    q[i][3] = d * a, q[i][4] = d * b, q[i][5] = d;
-    q[i][6] = a, q[i][7] = b, q[i][8] = 1.0;
+    Q_(i, 0) = c * a, Q_(i, 1) = c * b, Q_(i, 2) = c;
+    Q_(i, 3) = d * a, Q_(i, 4) = d * b, Q_(i, 5) = d;
+    Q_(i, 6) = a, Q_(i, 7) = b, Q_(i, 8) = 1.0;
   }
   int pc[5];
-  bool is_pivot[9] = {false, false, false, false, false, false, false, false, false};
+  unsigned pivots = 0;  // bit j: column j holds a pivot
   for (int r = 0; r < 5; ++r) {
     int br = r, bc = -1;
     double bv = 0;
     for (int i = r; i < 5; ++i)
-      for (int j = 0; j < 9; ++j)
-        if (!is_pivot[j] && fabs(q[i][j]) > bv) bv = fabs(q[i][j]), br = i, bc = j;
+      for (int j = 0; j < 9; ++j) {
+        const double v = fabs(Q_(i, j));
+        if (!((pivots >> j) & 1u) && v > bv) bv = v, br = i, bc = j;
+      }
     if (bc < 0 || bv == 0.0) return 0;  // rank-deficient sample
     for (int j = 0; j < 9; ++j) {
-      const double t = q[r][j];
-      q[r][j] = q[br][j];
-      q[br][j] = t;
+      const double t = Q_(r, j);
+      Q_(r, j) = Q_(br, j);
+      Q_(br, j) = t;
     }
     pc[r] = bc;
-    is_pivot[bc] = true;
-    const double inv = 1.0 / q[r][bc];
-    for (int j = 0; j < 9; ++j) q[r][j] *= inv;
+    pivots |= 1u << bc;
+    const double inv = 1.0 / Q_(r, bc);
+    for (int j = 0; j < 9; ++j) Q_(r, j) *= inv;
     for (int i = 0; i < 5; ++i) {
       if (i == r) continue;
-      const double f = q[i][bc];
+      const double f = Q_(i, bc);
       if (f != 0.0)
-        for (int j = 0; j < 9; ++j) q[i][j] -= f * q[r][j];
+        for (int j = 0; j < 9; ++j) Q_(i, j) -= f * Q_(r, j);
     }
   }
-  double eb[4][9];
   {
     int k = 0;
     for (int f = 0; f < 9; ++f) {
-      if (is_pivot[f]) continue;
-      for (int j = 0; j < 9; ++j) eb[k][j] = 0.0;
-      eb[k][f] = 1.0;
-      for (int r = 0; r < 5; ++r) eb[k][pc[r]] = -q[r][f];
+      if ((pivots >> f) & 1u) continue;
+      for (int j = 0; j < 9; ++j) EB_(k, j) = 0.0;
+      EB_(k, f) = 1.0;
+      for (int r = 0; r < 5; ++r) EB_(k, pc[r]) = -Q_(r, f);
       ++k;
     }
     for (int a = 0; a < 4; ++a) {  // modified Gram-Schmidt
       for (int b = 0; b < a; ++b) {
         double dot = 0;
-        for (int j = 0; j < 9; ++j) dot += eb[a][j] * eb[b][j];
-        for (int j = 0; j < 9; ++j) eb[a][j] -= dot * eb[b][j];
+        for (int j = 0; j < 9; ++j) dot += EB_(a, j) * EB_(b, j);
+        for (int j = 0; j < 9; ++j) EB_(a, j) -= dot * EB_(b, j);
       }
       double nn = 0;
-      for (int j = 0; j < 9; ++j) nn += eb[a][j] * eb[a][j];
+      for (int j = 0; j < 9; ++j) nn += EB_(a, j) * EB_(a, j);
       const double inv = 1.0 / sqrt(nn);
-      for (int j = 0; j < 9; ++j) eb[a][j] *= inv;
+      for (int j = 0; j < 9; ++j) EB_(a, j) *= inv;
     }
   }
-  // ---- the ten cubic constraints on E = x E1 + y E2 + z E3 + E4: entry (r, c) is the linear form eb[.][3r + c]
-  double M[10][20];
+  // ---- the ten cubic constraints on E = x E1 + y E2 + z E3 + E4: entry (r, c) is the linear form EB_(., 3r + c)
+#define LIN_(r, c, k) EB_(k, 3 * (r) + (c))
   for (int i = 0; i < 10; ++i)
-    for (int j = 0; j < 20; ++j) M[i][j] = 0.0;
-  auto lin = [&](int r, int c, int k) { return eb[k][3 * r + c]; };
-  // EEt (symmetric, quadratic forms)
-  double eet[3][3][10];
-  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 20; ++j) M_(i, j) = 0.0;
+  for (int i = 0; i < 3; ++i)  // EEt (symmetric, quadratic forms)
     for (int j = i; j < 3; ++j) {
       double acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
       for (int k = 0; k < 3; ++k)
-        for (int a = 0; a < 4; ++a)
-          for (int b = 0; b < 4; ++b) acc[c_ll[a][b]] += lin(i, k, a) * lin(j, k, b);
-      for (int m = 0; m < 10; ++m) eet[i][j][m] = eet[j][i][m] = acc[m];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          const double la = LIN_(i, k, a);
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[c_ll[a][b]] += la * LIN_(j, k, b);
+        }
+#pragma unroll
+      for (int m = 0; m < 10; ++m) EET_(i, j, m) = EET_(j, i, m) = acc[m];
     }
   for (int m = 0; m < 10; ++m) {
-    const double htr = 0.5 * (eet[0][0][m] + eet[1][1][m] + eet[2][2][m]);
-    eet[0][0][m] -= htr, eet[1][1][m] -= htr, eet[2][2][m] -= htr;
+    const double htr = 0.5 * (EET_(0, 0, m) + EET_(1, 1, m) + EET_(2, 2, m));
+    EET_(0, 0, m) -= htr, EET_(1, 1, m) -= htr, EET_(2, 2, m) -= htr;
   }
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) {
-      double* row = M[1 + 3 * i + j];
-      for (int k = 0; k < 3; ++k)
+      double row[20];
+#pragma unroll
+      for (int c = 0; c < 20; ++c) row[c] = 0.0;
+      for (int k = 0; k < 3; ++k) {
+        double lb[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) lb[b] = LIN_(k, j, b);
+#pragma unroll
         for (int m = 0; m < 10; ++m) {
-          const double qv = eet[i][k][m];
-          for (int b = 0; b < 4; ++b) row[c_ql[m][b]] += qv * lin(k, j, b);
+          const double qv = EET_(i, k, m);
+#pragma unroll
+          for (int b = 0; b < 4; ++b) row[c_ql[m][b]] += qv * lb[b];
         }
+      }
+#pragma unroll
+      for (int c = 0; c < 20; ++c) M_(1 + 3 * i + j, c) = row[c];
     }
   {  // det(E): e00 (e11 e22 - e12 e21) - e01 (e10 e22 - e12 e20) + e02 (e10 e21 - e11 e20)
-    const int minors[3][4][2] = {{{1, 1}, {2, 2}, {1, 2}, {2, 1}}, {{1, 0}, {2, 2}, {1, 2}, {2, 0}}, {{1, 0}, {2, 1}, {1, 1}, {2, 0}}};
+    double row[20];
+#pragma unroll
+    for (int c = 0; c < 20; ++c) row[c] = 0.0;
     for (int t = 0; t < 3; ++t) {
+      const int c0 = t == 0 ? 1 : 0, c1 = t == 2 ? 1 : 2;  // the two columns of the minor of e0t
       double mq[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-      for (int a = 0; a < 4; ++a)
-        for (int b = 0; b < 4; ++b)
-          mq[c_ll[a][b]] += lin(minors[t][0][0], minors[t][0][1], a) * lin(minors[t][1][0], minors[t][1][1], b) -
-                            lin(minors[t][2][0], minors[t][2][1], a) * lin(minors[t][3][0], minors[t][3][1], b);
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        const double p = LIN_(1, c0, a), q = LIN_(1, c1, a);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) mq[c_ll[a][b]] += p * LIN_(2, c1, b) - q * LIN_(2, c0, b);
+      }
       const double sgn = t == 1 ? -1.0 : 1.0;
+      double lb[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) lb[b] = sgn * LIN_(0, t, b);
+#pragma unroll
       for (int m = 0; m < 10; ++m)
-        for (int b = 0; b < 4; ++b) M[0][c_ql[m][b]] += sgn * mq[m] * lin(0, t, b);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) row[c_ql[m][b]] += mq[m] * lb[b];
     }
+#pragma unroll
+    for (int c = 0; c < 20; ++c) M_(0, c) = row[c];
   }
   // ---- Gauss-Jordan on the ten leading monomials (partial pivoting)
   for (int c = 0; c < 10; ++c) {
     int br = c;
-    double bv = fabs(M[c][c]);
-    for (int i = c + 1; i < 10; ++i)
-      if (fabs(M[i][c]) > bv) bv = fabs(M[i][c]), br = i;
+    double bv = fabs(M_(c, c));
+    for (int i = c + 1; i < 10; ++i) {
+      const double v = fabs(M_(i, c));
+      if (v > bv) bv = v, br = i;
+    }
     if (bv == 0.0) return 0;
     if (br != c)
       for (int j = c; j < 20; ++j) {
-        const double t = M[c][j];
-        M[c][j] = M[br][j];
-        M[br][j] = t;
+        const double t = M_(c, j);
+        M_(c, j) = M_(br, j);
+        M_(br, j) = t;
       }
-    const double inv = 1.0 / M[c][c];
-    for (int j = c; j < 20; ++j) M[c][j] *= inv;
+    const double inv = 1.0 / M_(c, c);
+    for (int j = c; j < 20; ++j) M_(c, j) *= inv;
     for (int i = 0; i < 10; ++i) {
       if (i == c) continue;
-      const double f = M[i][c];
+      const double f = M_(i, c);
       if (f != 0.0)
-        for (int j = c; j < 20; ++j) M[i][j] -= f * M[c][j];
+        for (int j = c; j < 20; ++j) M_(i, j) -= f * M_(c, j);
     }
   }
   // ---- B(z) [x y 1]^T = 0: row pair (x2z, x2), (y2z, y2), (xyz, xy): upper row - z * lower row.  Tail columns:
   // 10 xz2, 11 xz, 12 x, 13 yz2, 14 yz, 15 y, 16 z3, 17 z2, 18 z, 19 1
   double bx[3][4], by[3][4], b1[3][5];
+#pragma unroll
   for (int r = 0; r < 3; ++r) {
-    const double* e = M[4 + 2 * r] + 10;
-    const double* f = M[5 + 2 * r] + 10;
+    double e[10], f[10];
+#pragma unroll
+    for (int c = 0; c < 10; ++c) e[c] = M_(4 + 2 * r, 10 + c), f[c] = M_(5 + 2 * r, 10 + c);
     bx[r][0] = e[2], bx[r][1] = e[1] - f[2], bx[r][2] = e[0] - f[1], bx[r][3] = -f[0];
     by[r][0] = e[5], by[r][1] = e[4] - f[5], by[r][2] = e[3] - f[4], by[r][3] = -f[3];
     b1[r][0] = e[9], b1[r][1] = e[8] - f[9], b1[r][2] = e[7] - f[8], b1[r][3] = e[6] - f[7], b1[r][4] = -f[6];
   }
   // det B(z) = sum over rows r of b1[r] * cofactor_r, cofactor_r = +-(bx[s] by[t] - bx[t] by[s])
   double det[11];
+#pragma unroll
   for (int i = 0; i < 11; ++i) det[i] = 0.0;
+#pragma unroll
   for (int r = 0; r < 3; ++r) {
     const int s = r == 0 ? 1 : 0, t = r == 2 ? 1 : 2;
     double cof[7] = {0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
     for (int a = 0; a < 4; ++a)
+#pragma unroll
       for (int b = 0; b < 4; ++b) cof[a + b] += bx[s][a] * by[t][b] - bx[t][a] * by[s][b];
     const double sgn = r == 1 ? -1.0 : 1.0;
+#pragma unroll
     for (int a = 0; a < 5; ++a)
+#pragma unroll
       for (int b = 0; b < 7; ++b) det[a + b] += sgn * b1[r][a] * cof[b];
   }
   {
     double mx = 0;
+#pragma unroll
     for (int i = 0; i < 11; ++i) mx = fmax(mx, fabs(det[i]));
     if (!(mx > 0.0) || !isfinite(mx)) return 0;
     const double inv = 1.0 / mx;
+#pragma unroll
     for (int i = 0; i < 11; ++i) det[i] *= inv;
   }
   double roots[10];
-  const int nroots = real_roots(det, 10, roots);
+  const int nroots = real_roots<SS>(det, 10, roots, sm);  // the derivative table reuses M's storage
   int nm = 0;
   for (int k = 0; k < nroots && nm < kPoseMaxModels; ++k) {
     const double z = roots[k];
     double Bz[3][3];
+#pragma unroll
     for (int r = 0; r < 3; ++r) {
       Bz[r][0] = horner(bx[r], 3, z);
       Bz[r][1] = horner(by[r], 3, z);
       Bz[r][2] = horner(b1[r], 4, z);
     }
     double best[3] = {0, 0, 0}, bestw = -1.0;
+#pragma unroll
     for (int a = 0; a < 2; ++a)
+#pragma unroll
       for (int b = a + 1; b < 3; ++b) {
         const double v0 = Bz[a][1] * Bz[b][2] - Bz[a][2] * Bz[b][1];
         const double v1 = Bz[a][2] * Bz[b][0] - Bz[a][0] * Bz[b][2];
@@ -362,16 +430,23 @@ __device__ int five_point_solve(const double (&x1)[5][2], const double (&x2)[5][
     if (!(bestw > 1e-10 * vn)) continue;  // [x y 1] at infinity
     const double x = best[0] / best[2], y = best[1] / best[2];
     double E[9], nn = 0;
+#pragma unroll
     for (int j = 0; j < 9; ++j) {
-      E[j] = x * eb[0][j] + y * eb[1][j] + z * eb[2][j] + eb[3][j];
+      E[j] = x * EB_(0, j) + y * EB_(1, j) + z * EB_(2, j) + EB_(3, j);
       nn += E[j] * E[j];
     }
     if (!(nn > 0.0) || !isfinite(nn)) continue;
     const double inv = 1.0 / sqrt(nn);
+#pragma unroll
     for (int j = 0; j < 9; ++j) models[nm * 9 + j] = E[j] * inv;
     ++nm;
   }
   return nm;
+#undef LIN_
+#undef EB_
+#undef EET_
+#undef M_
+#undef Q_
 }
 
 // ORBX_HOST_TESTABLE_END
@@ -379,6 +454,7 @@ __global__ void __launch_bounds__(32) pose_solve_kernel(const PoseState* __restr
                                                        const double* __restrict__ x1, const double* __restrict__ x2,
                                                        const int* __restrict__ samples, double* __restrict__ models,
                                                        int* __restrict__ nmodels) {
+  extern __shared__ double s_solve[];  // [kSolveScratch][32]
   const int p = blockIdx.y;
   const int it = c_wave[wave] + blockIdx.x * blockDim.x + threadIdx.x;
   if (it >= c_wave[wave + 1] || it >= st[p].niters) return;
@@ -391,7 +467,7 @@ __global__ void __launch_bounds__(32) pose_solve_kernel(const PoseState* __restr
     b[i][0] = x2[2 * j], b[i][1] = x2[2 * j + 1];
   }
   const size_t h = (size_t)p * kPoseMaxIters + it;
-  nmodels[h] = five_point_solve(a, b, models + h * (kPoseMaxModels * 9));
+  nmodels[h] = five_point_solve<32>(a, b, models + h * (kPoseMaxModels * 9), s_solve + threadIdx.x);
 }
 
 // Sampson error of EMEstimatorCallback::computeError, unfused, rounded to fp32
@@ -698,11 +774,13 @@ int run_essential(orbx_pose_estimator* pe, const float* pts1, const float* pts2,
       pts1, pts2, n_dev, n_fixed, pp, pe->x1, pe->x2, pe->state, true);
   ORBX_LAUNCH_CHECK();
   const int wave[kPoseWaves + 1] = {0, 32, 96, 256, kPoseMaxIters};
+  constexpr int kSolveSmem = kSolveScratch * 32 * (int)sizeof(double);
+  ORBX_CUDA(cudaFuncSetAttribute(pose_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
   for (int w = 0; w < kPoseWaves; ++w) {
     const int len = wave[w + 1] - wave[w];
     pose_sample_kernel<<<np, 32, 0, s>>>(pe->state, w, pe->samples);
     ORBX_LAUNCH_CHECK();
-    pose_solve_kernel<<<dim3(div_up(len, 32), np), 32, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->samples, pe->models,
+    pose_solve_kernel<<<dim3(div_up(len, 32), np), 32, kSolveSmem, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->samples, pe->models,
                                                              pe->nmodels);
     ORBX_LAUNCH_CHECK();
     pose_count_kernel<<<dim3(std::min(len, 32), np), 128, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->models, pe->nmodels, pe->counts);

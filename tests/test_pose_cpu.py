@@ -90,8 +90,8 @@ def _host_solver():
            "#define __forceinline__ inline\n#define __restrict__\nconstexpr int kPoseMaxModels = 10;\n" + tables + body +
            "extern \"C\" int solve5(const double* x1, const double* x2, double* m) { double a[5][2], b[5][2];\n"
            "  for (int i = 0; i < 5; ++i) { a[i][0] = x1[2*i]; a[i][1] = x1[2*i+1]; b[i][0] = x2[2*i]; b[i][1] = x2[2*i+1]; }\n"
-           "  return five_point_solve(a, b, m); }\n"
-           "extern \"C\" int roots(const double* c, int deg, double* r) { return real_roots(c, deg, r); }\n")
+           "  double sm[kSolveScratch]; return five_point_solve<1>(a, b, m, sm); }\n"
+           "extern \"C\" int roots(const double* c, int deg, double* r) { double d[121]; return real_roots<1>(c, deg, r, d); }\n")
     d = tempfile.mkdtemp(prefix="orbx_pose_host_")
     open(os.path.join(d, "host.cpp"), "w").write(src)
     subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-o", os.path.join(d, "libhost.so"), os.path.join(d, "host.cpp")])
