@@ -1,6 +1,7 @@
-// Header-only C++ mirror of slamkit-rs `feature::{OrbDetector, FeatureMatcher}` over the C ABI (orbx.h).
-// Same names and argument meaning as /root/reference/src/feature/detector.rs:15-44 and matcher.rs:15-66;
-// errors become std::runtime_error (the reference returns Err(Box<dyn Error>)).
+// Header-only C++ mirror of slamkit-rs `feature::{OrbDetector, FeatureMatcher}`, `odometry::PoseEstimator` and
+// `mapping::Triangulator` over the C ABI (orbx.h).  Same names and argument meaning as
+// /root/reference/src/feature/detector.rs:15-44, matcher.rs:15-66, src/odometry/pose.rs:17-114 and
+// src/mapping/triangulation.rs:52-198; errors become std::runtime_error (the reference returns Err(Box<dyn Error>)).
 #pragma once
 #include <stdexcept>
 #include <string>
@@ -100,6 +101,104 @@ class FeatureMatcher {
 
  private:
   orbx_matcher* h_ = nullptr;
+};
+
+struct CameraIntrinsics {  // odometry::CameraIntrinsics (camera.rs:5-36)
+  double fx, fy, cx, cy;
+  static CameraIntrinsics kitti() { return {718.856, 718.856, 607.1928, 185.2157}; }
+};
+
+struct Pose {  // (R, t), world to camera; R row-major
+  double R[9];
+  double t[3];
+};
+
+// odometry::PoseEstimator (pose.rs:10-114); points are (x, y) pairs as returned by extract_matched_points
+class PoseEstimator {
+ public:
+  explicit PoseEstimator(const CameraIntrinsics& k, int device = 0, int max_points = 1 << 14) {
+    check(orbx_pose_estimator_create(device, max_points, 1, k.fx, k.fy, k.cx, k.cy, &h_));
+  }
+  ~PoseEstimator() { orbx_pose_estimator_destroy(h_); }
+  PoseEstimator(const PoseEstimator&) = delete;
+  PoseEstimator& operator=(const PoseEstimator&) = delete;
+
+  // pose.rs:47-80: E row-major (9 doubles); throws "Insufficient points: n (need 8)" / "Failed to compute essential matrix"
+  std::vector<double> compute_essential_matrix(const std::vector<float>& p1, const std::vector<float>& p2) {
+    std::vector<double> E(9);
+    check(orbx_compute_essential_matrix(h_, p1.data(), (int)(p1.size() / 2), p2.data(), (int)(p2.size() / 2), E.data(),
+                                        nullptr, nullptr, nullptr));
+    return E;
+  }
+  // pose.rs:83-114: throws "Too few inliers: k"
+  Pose recover_pose(const std::vector<double>& E, const std::vector<float>& p1, const std::vector<float>& p2) {
+    Pose out{};
+    check(orbx_recover_pose(h_, E.data(), p1.data(), (int)(p1.size() / 2), p2.data(), (int)(p2.size() / 2), out.R, out.t,
+                            nullptr, nullptr));
+    return out;
+  }
+
+ private:
+  orbx_pose_estimator* h_ = nullptr;
+};
+
+struct MapPoint {  // mapping::MapPoint (triangulation.rs:11-22)
+  double position[3];
+  std::vector<uint8_t> descriptor;  // empty == None
+  size_t observations = 1;
+  size_t id = 0;
+};
+
+// mapping::Triangulator (triangulation.rs:52-198)
+class Triangulator {
+ public:
+  explicit Triangulator(const CameraIntrinsics& k, int device = 0, int max_points = 1 << 16) {
+    check(orbx_triangulator_create(device, max_points, k.fx, k.fy, k.cx, k.cy, &h_));
+  }
+  ~Triangulator() { orbx_triangulator_destroy(h_); }
+  Triangulator(const Triangulator&) = delete;
+  Triangulator& operator=(const Triangulator&) = delete;
+
+  Triangulator& with_min_parallax(double deg) {
+    check(orbx_triangulator_set_thresholds(h_, deg, max_reproj_error()));
+    return *this;
+  }
+  Triangulator& with_max_reproj_error(double e) {
+    check(orbx_triangulator_set_thresholds(h_, min_parallax_deg(), e));
+    return *this;
+  }
+  double min_parallax_deg() const {
+    double a = 0, b = 0;
+    check(orbx_triangulator_get_thresholds(h_, &a, &b));
+    return a;
+  }
+  double max_reproj_error() const {
+    double a = 0, b = 0;
+    check(orbx_triangulator_get_thresholds(h_, &a, &b));
+    return b;
+  }
+  // triangulation.rs:92-158; descriptors: rows x 32 bytes or empty (None); throws on mismatched point arrays
+  std::vector<MapPoint> triangulate(const Pose& pose1, const Pose& pose2, const std::vector<float>& p1,
+                                    const std::vector<float>& p2, const std::vector<uint8_t>& descriptors = {}) {
+    const int n1 = (int)(p1.size() / 2), n2 = (int)(p2.size() / 2), cap = n1 > 0 ? n1 : 1;
+    std::vector<int32_t> ids(cap);
+    std::vector<double> xyz(3 * (size_t)cap);
+    std::vector<uint8_t> desc(32 * (size_t)cap), has(cap);
+    int m = 0;
+    check(orbx_triangulate(h_, pose1.R, pose1.t, pose2.R, pose2.t, p1.data(), n1, p2.data(), n2,
+                           descriptors.empty() ? nullptr : descriptors.data(), (int)(descriptors.size() / 32), ids.data(),
+                           xyz.data(), desc.data(), has.data(), nullptr, cap, &m));
+    std::vector<MapPoint> out(m);
+    for (int k = 0; k < m; ++k) {
+      for (int j = 0; j < 3; ++j) out[k].position[j] = xyz[3 * k + j];
+      out[k].id = (size_t)ids[k];
+      if (has[k]) out[k].descriptor.assign(desc.begin() + 32 * k, desc.begin() + 32 * (k + 1));
+    }
+    return out;
+  }
+
+ private:
+  orbx_triangulator* h_ = nullptr;
 };
 
 }  // namespace orbx

@@ -1,4 +1,4 @@
-//! Safe mirror of slamkit-rs `src/feature/{detector,matcher}.rs` over liborbx.
+//! Safe mirror of slamkit-rs `src/feature/{detector,matcher}.rs`, `odometry::PoseEstimator` and `mapping::Triangulator` over liborbx.
 //! Same method names and error behaviour: working calls take `&mut self`, empty inputs are not errors,
 //! results are freshly allocated.  NOT compiled in this repository's build image (no Rust toolchain).
 use orbx_sys as sys;
@@ -95,3 +95,90 @@ impl FeatureMatcher {
     }
 }
 impl Drop for FeatureMatcher { fn drop(&mut self) { unsafe { sys::orbx_matcher_destroy(self.h) } } }
+
+/// odometry::CameraIntrinsics (src/odometry/camera.rs:5-36)
+#[derive(Clone, Copy, Debug)]
+pub struct CameraIntrinsics { pub fx: f64, pub fy: f64, pub cx: f64, pub cy: f64 }
+impl CameraIntrinsics {
+    pub fn new(fx: f64, fy: f64, cx: f64, cy: f64) -> Self { Self { fx, fy, cx, cy } }
+    pub fn kitti() -> Self { Self { fx: 718.856, fy: 718.856, cx: 607.1928, cy: 185.2157 } }
+}
+
+/// (R row-major, t): world-to-camera pose as the ABI takes it (nalgebra's `Matrix3` is column-major: pass `r.transpose()`).
+pub type Pose = ([f64; 9], [f64; 3]);
+
+/// Mirror of odometry::PoseEstimator (src/odometry/pose.rs:10-114): cv::findEssentialMat(RANSAC, 0.999, 1.0, 1000) and
+/// cv::recoverPose reproduced on the device with OpenCV's own RANSAC draws.
+pub struct PoseEstimator { h: *mut sys::orbx_pose_estimator, matcher: FeatureMatcher }
+
+impl PoseEstimator {
+    /// pose.rs:17-23
+    pub fn new(intrinsics: CameraIntrinsics) -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_pose_estimator_create(0, 1 << 14, 1, intrinsics.fx, intrinsics.fy, intrinsics.cx, intrinsics.cy, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h, matcher: FeatureMatcher::new()? })
+    }
+    /// pose.rs:27-44
+    pub fn extract_matched_points(&self, kp1: &[KeyPoint], kp2: &[KeyPoint], matches: &[DMatch]) -> Result<(Vec<[f32; 2]>, Vec<[f32; 2]>), Box<dyn Error>> {
+        self.matcher.extract_matched_points(kp1, kp2, matches)
+    }
+    /// pose.rs:47-80 — E row-major; `Err("Insufficient points: n (need 8)")` / `Err("Failed to compute essential matrix")`
+    pub fn compute_essential_matrix(&self, points1: &[[f32; 2]], points2: &[[f32; 2]]) -> Result<[f64; 9], Box<dyn Error>> {
+        let mut e = [0f64; 9];
+        let rc = unsafe { sys::orbx_compute_essential_matrix(self.h, points1.as_ptr() as *const f32, points1.len() as i32,
+            points2.as_ptr() as *const f32, points2.len() as i32, e.as_mut_ptr(), ptr::null_mut(), ptr::null_mut(), ptr::null_mut()) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(e)
+    }
+    /// pose.rs:83-114 — `Err("Too few inliers: k")` when fewer than 8 points are in front of both cameras
+    pub fn recover_pose(&self, essential: &[f64; 9], points1: &[[f32; 2]], points2: &[[f32; 2]]) -> Result<Pose, Box<dyn Error>> {
+        let (mut r, mut t) = ([0f64; 9], [0f64; 3]);
+        let rc = unsafe { sys::orbx_recover_pose(self.h, essential.as_ptr(), points1.as_ptr() as *const f32, points1.len() as i32,
+            points2.as_ptr() as *const f32, points2.len() as i32, r.as_mut_ptr(), t.as_mut_ptr(), ptr::null_mut(), ptr::null_mut()) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((r, t))
+    }
+}
+impl Drop for PoseEstimator { fn drop(&mut self) { unsafe { sys::orbx_pose_estimator_destroy(self.h) } } }
+
+/// mapping::MapPoint (src/mapping/triangulation.rs:11-22)
+#[derive(Clone, Debug)]
+pub struct MapPoint { pub position: [f64; 3], pub descriptor: Option<Vec<u8>>, pub observations: usize, pub id: usize }
+
+/// Mirror of mapping::Triangulator (src/mapping/triangulation.rs:52-198)
+pub struct Triangulator { h: *mut sys::orbx_triangulator }
+
+impl Triangulator {
+    /// triangulation.rs:62-68
+    pub fn new(intrinsics: CameraIntrinsics) -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_triangulator_create(0, 1 << 16, intrinsics.fx, intrinsics.fy, intrinsics.cx, intrinsics.cy, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h })
+    }
+    fn thresholds(&self) -> (f64, f64) {
+        let (mut a, mut b) = (0f64, 0f64);
+        unsafe { sys::orbx_triangulator_get_thresholds(self.h, &mut a, &mut b) };
+        (a, b)
+    }
+    /// triangulation.rs:71-74
+    pub fn with_min_parallax(self, deg: f64) -> Self { unsafe { sys::orbx_triangulator_set_thresholds(self.h, deg, self.thresholds().1) }; self }
+    /// triangulation.rs:77-80
+    pub fn with_max_reproj_error(self, error: f64) -> Self { unsafe { sys::orbx_triangulator_set_thresholds(self.h, self.thresholds().0, error) }; self }
+    /// triangulation.rs:92-158 — `descriptors`: rows x 32 bytes (row i goes to the point of correspondence i)
+    pub fn triangulate(&self, pose1: &Pose, pose2: &Pose, points1: &[[f32; 2]], points2: &[[f32; 2]], descriptors: Option<&[u8]>) -> Result<Vec<MapPoint>, Box<dyn Error>> {
+        let cap = points1.len().max(1);
+        let (mut ids, mut xyz) = (vec![0i32; cap], vec![0f64; 3 * cap]);
+        let (mut desc, mut has) = (vec![0u8; 32 * cap], vec![0u8; cap]);
+        let mut m = 0i32;
+        let (dptr, drows) = descriptors.map_or((ptr::null(), 0), |d| (d.as_ptr(), (d.len() / 32) as i32));
+        let rc = unsafe { sys::orbx_triangulate(self.h, pose1.0.as_ptr(), pose1.1.as_ptr(), pose2.0.as_ptr(), pose2.1.as_ptr(),
+            points1.as_ptr() as *const f32, points1.len() as i32, points2.as_ptr() as *const f32, points2.len() as i32, dptr, drows,
+            ids.as_mut_ptr(), xyz.as_mut_ptr(), desc.as_mut_ptr(), has.as_mut_ptr(), ptr::null_mut(), cap as i32, &mut m) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((0..m as usize).map(|k| MapPoint { position: [xyz[3 * k], xyz[3 * k + 1], xyz[3 * k + 2]], id: ids[k] as usize, observations: 1,
+            descriptor: (has[k] != 0).then(|| desc[32 * k..32 * k + 32].to_vec()) }).collect())
+    }
+}
+impl Drop for Triangulator { fn drop(&mut self) { unsafe { sys::orbx_triangulator_destroy(self.h) } } }
