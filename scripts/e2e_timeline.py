@@ -35,7 +35,7 @@ h2d, comp, d2h = [], [], []
 with torch.cuda.stream(fe.copy_stream):
     for a, b in bounds:
         if do_h2d:
-            fe.frames_dev[a:b, :, :W].copy_(pin[a:b], non_blocking=True)
+            fe.frames_dev[a:b].copy_(pin[a:b], non_blocking=True)
         h2d.append(ev(fe.copy_stream))
 for i, (a, b) in enumerate(bounds):
     fe.stream.wait_event(h2d[i]); fe.extract(fe.frames_dev, a, b); fe.match(a, b); comp.append(ev(fe.stream))

@@ -70,6 +70,8 @@ struct ResizeArgs {
 // stage launchers -------------------------------------------------------------------------------
 int launch_bgr_to_gray(const uint8_t* src, size_t spitch, size_t sstride, uint8_t* dst, int dpitch, size_t dstride,
                        int w, int h, int batch, cudaStream_t s);
+int launch_repack_gray(const uint8_t* src, size_t spitch, size_t sstride, uint8_t* dst, int dpitch, size_t dstride, int w,
+                       int h, int batch, cudaStream_t s);
 int launch_resize(const ResizeArgs& a, int batch, cudaStream_t s);
 int launch_fast(const DevGeom& g, cudaStream_t s);
 int launch_harris(const DevGeom& g, cudaStream_t s);

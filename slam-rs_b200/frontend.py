@@ -69,8 +69,9 @@ class SequenceFrontEnd:
             self.pose_good = torch.zeros((T,), dtype=i32, device=self.dev)
             self.pose_status = torch.zeros((T,), dtype=i32, device=self.dev)
             self._pose_chunk = int(min(self.chunk, 256))
-        # staging for the host path
-        self.frames_dev = torch.zeros((T, self.h, self.pitch), dtype=u8, device=self.dev)
+        # staging for the host path: frames land tightly packed (one contiguous DMA per stage); when the width is not a
+        # multiple of 4 liborbx repacks them into its pitched level-0 plane with its own kernel (csrc/ingest.cu)
+        self.frames_dev = torch.zeros((T, self.h, self.w), dtype=u8, device=self.dev)
         self.copy_stream = torch.cuda.Stream(device=self.dev)
         self.d2h_stream = torch.cuda.Stream(device=self.dev)
         # liborbx runs on one explicit (non-default) stream; callers' streams are joined with events
@@ -187,7 +188,7 @@ class SequenceFrontEnd:
         events = []
         with torch.cuda.stream(self.copy_stream):
             for a, b in bounds:
-                self.frames_dev[a:b, :, :self.w].copy_(frames_pinned[a:b], non_blocking=True)
+                self.frames_dev[a:b].copy_(frames_pinned[a:b], non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self.copy_stream)
                 events.append(ev)
