@@ -405,10 +405,14 @@ static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs, bool fused = fal
   const int rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
   if (rows_q <= 0 || npairs <= 0) return ORBX_OK;
   const int qtiles = div_up(rows_q, kQPB);
-  // enough blocks for ~16 warps per SM over two waves, but never split below one tile
-  const long target = (long)m->num_sms * 8;
-  int splits = (int)std::min<long>(std::max<long>(1, target / std::max<long>(1, (long)qtiles * npairs)),
-                                   std::max(1, div_up(rows_t, kTile)));
+  // about four waves of blocks (10 resident per SM) so that the last, partly filled wave costs little, but never
+  // split below one tile
+  const long target = (long)m->num_sms * 40;
+  const long nblk = std::max<long>(1, (long)qtiles * npairs);
+  // (grids that already hold a few hundred long blocks - frame-to-frame batches - gain nothing from splitting: measured)
+  int splits = nblk >= (long)m->num_sms * 4
+                   ? 1
+                   : (int)std::min<long>(std::max<long>(1, (target + nblk - 1) / nblk), std::max(1, div_up(rows_t, kTile)));
   int rps = (int)align_up((size_t)div_up(std::max(rows_t, 1), splits), kTile);
   if (rps > kMaxSplitRows) rps = kMaxSplitRows;
   splits = std::max(1, div_up(std::max(rows_t, 1), rps));
