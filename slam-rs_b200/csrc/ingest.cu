@@ -44,34 +44,38 @@ __global__ void __launch_bounds__(256) bgr_to_gray_kernel(const uint8_t* __restr
 
 // Repack of device-resident 8UC1 frames whose base / pitch / frame stride is not 4-byte aligned (e.g. tightly packed
 // 1241-byte rows, which is how frames arrive from the host with a plain contiguous DMA) into the detector's pitched
-// level-0 plane, so that every later stage takes its aligned path.  Thread = one 32-bit output word: the two aligned
-// source words that cover it, one funnel shift.  Streaming: reads and writes each level-0 byte once.
+// level-0 plane, so that every later stage takes its aligned path.  Thread = 16 output bytes: the five aligned source
+// words that cover them, four funnel shifts, one 128-bit store.  Streaming: reads and writes each level-0 byte once.
 __global__ void __launch_bounds__(256) repack_gray_kernel(const uint8_t* __restrict__ src, size_t spitch, size_t sstride,
                                                           const uint8_t* __restrict__ src_end, uint8_t* __restrict__ dst,
                                                           int dpitch, size_t dstride, int w) {
-  const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (x4 >= w) return;
-  const uint8_t* s = src + (size_t)blockIdx.z * sstride + (size_t)blockIdx.y * spitch + x4;
-  uint8_t* d = dst + (size_t)blockIdx.z * dstride + (size_t)blockIdx.y * dpitch + x4;
+  const int x16 = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (x16 >= w) return;
+  const uint8_t* s = src + (size_t)blockIdx.z * sstride + (size_t)blockIdx.y * spitch + x16;
+  uint8_t* d = dst + (size_t)blockIdx.z * dstride + (size_t)blockIdx.y * dpitch + x16;
   const uintptr_t sa = (uintptr_t)s;
   const unsigned* a = reinterpret_cast<const unsigned*>(sa & ~(uintptr_t)3);
-  unsigned out;
-  if (reinterpret_cast<const uint8_t*>(a + 2) <= src_end) {
-    out = __funnelshift_r(__ldg(a), __ldg(a + 1), 8 * (unsigned)(sa & 3));
+  uint4 out;
+  if (reinterpret_cast<const uint8_t*>(a + 5) <= src_end) {
+    const unsigned sh = 8 * (unsigned)(sa & 3);
+    const unsigned w0 = __ldg(a), w1 = __ldg(a + 1), w2 = __ldg(a + 2), w3 = __ldg(a + 3), w4 = __ldg(a + 4);
+    out = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                     __funnelshift_r(w3, w4, sh));
   } else {  // the last words of the buffer: never read past its end
-    out = 0;
-    for (int k = 0; k < 4 && s + k < src_end; ++k) out |= (unsigned)__ldg(s + k) << (8 * k);
+    unsigned o[4] = {0, 0, 0, 0};
+    for (int k = 0; k < 16 && s + k < src_end; ++k) o[k >> 2] |= (unsigned)__ldg(s + k) << (8 * (k & 3));
+    out = make_uint4(o[0], o[1], o[2], o[3]);
   }
-  // dpitch is a multiple of 128: the whole word belongs to this row even when it runs past w
-  *reinterpret_cast<unsigned*>(d) = out;
+  // dpitch is a multiple of 128 and the plane is 256-byte aligned: the 16 bytes belong to this row even past w
+  *reinterpret_cast<uint4*>(d) = out;
 }
 
 int launch_repack_gray(const uint8_t* src, size_t spitch, size_t sstride, uint8_t* dst, int dpitch, size_t dstride, int w,
                        int h, int batch, cudaStream_t s) {
   if (batch == 0) return ORBX_OK;
   const uint8_t* end = src + (size_t)(batch - 1) * sstride + (size_t)(h - 1) * spitch + w;
-  dim3 grid(div_up(div_up(w, 4), 256), h, batch);
-  repack_gray_kernel<<<grid, 256, 0, s>>>(src, spitch, sstride, end, dst, dpitch, dstride, w);
+  dim3 grid(div_up(div_up(w, 16), 128), h, batch);
+  repack_gray_kernel<<<grid, 128, 0, s>>>(src, spitch, sstride, end, dst, dpitch, dstride, w);
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

@@ -154,6 +154,32 @@ def test_batch_device_pointers_and_pitch(orbx):
             assert np.array_equal(k, host[i][0]) and np.array_equal(desc[i, :nn[i]].cpu().numpy(), host[i][1])
 
 
+def test_unaligned_device_frames_are_repacked(orbx):
+    """Tightly packed odd-width frames at odd byte offsets inside a device buffer, the last one ending exactly at the end
+    of the allocation (csrc/ingest.cu::repack_gray_kernel must not read past it): same bytes out as the host path."""
+    import torch
+    h, w, nf, B = 97, 203, 300, 3
+    imgs = np.stack([synth.frame(h, w, 70 + i) for i in range(B)])
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h, max_batch=B)
+    host = det.detect_and_compute_batch(imgs)
+    cap = 512
+    for lead in (0, 1, 3):
+        flat = torch.zeros(lead + B * h * w, dtype=torch.uint8, device="cuda")
+        flat[lead:] = torch.from_numpy(imgs.reshape(-1)).cuda()
+        buf = flat[lead:].view(B, h, w)
+        kps = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda")
+        desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+        n = torch.zeros((B,), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        det.detect_and_compute_device(buf, kps, desc, n, width=w)
+        det.sync()
+        nn = n.cpu().numpy()
+        for i in range(B):
+            k = kps[i, :nn[i]].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+            assert np.array_equal(k, host[i][0]) and np.array_equal(desc[i, :nn[i]].cpu().numpy(), host[i][1])
+        assert np.array_equal(det.level(0, frame=B - 1), imgs[B - 1])        # level 0 of the last frame, byte for byte
+
+
 def test_capacity_error_reports_needed_size(orbx):
     img = synth.frame(240, 320, 5)
     det = orbx.OrbDetector(300, max_width=320, max_height=240)
