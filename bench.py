@@ -194,7 +194,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -406,7 +406,7 @@ def run_ours(args, rank, world, local_rank):
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(frames[:args.cpu_frames], os.cpu_count() or 1)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -528,7 +528,7 @@ def run_map(args, rank, world, local_rank):
                          "note": "per-rank kernel time; 8 algorithmic POPC per pair, 5 issued (carry-save)"},
             "clocks": clocks,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -551,10 +551,22 @@ def bind_near_gpu(index):
         return None
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
-    # this image's NCCL configuration prints a version banner on stdout next to the JSON line unless told otherwise
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # stdout carries exactly ONE line, the JSON: this image's NCCL prints a version banner on fd 1 from C, so fd 1 is
+    # pointed at stderr for the whole run and the JSON line goes to the saved descriptor (emit)
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
