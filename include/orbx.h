@@ -282,6 +282,15 @@ int orbx_triangulate(orbx_triangulator* t, const double* R1, const double* t1, c
                      const float* pts1, int n1, const float* pts2, int n2, const uint8_t* desc, int desc_rows,
                      int32_t* ids, double* xyz, uint8_t* out_desc, uint8_t* has_desc, float* points4d, int cap,
                      int* n_out);
+/* batched device form (sequence front end: the pairs of a whole sequence, poses straight from
+ * orbx_estimate_pose_batch): problem p triangulates n_dev[p] correspondences at pts1 / pts2 + p*max_rows*2 floats
+ * between the poses (R1 + 9p, t1 + 3p) — NULL = identity / zero for every problem — and (R2 + 9p, t2 + 3p), and writes
+ * the survivors' ids + p*max_rows, xyz + p*max_rows*3 and n_out[p].  Device pointers, asynchronous on the handle's
+ * stream; npairs * max_rows <= max_points. */
+int orbx_triangulate_batch(orbx_triangulator* t, const double* R1, const double* t1, const double* R2, const double* t2,
+                           const float* pts1, const float* pts2, const int* n_dev, int npairs, int max_rows, int32_t* ids,
+                           double* xyz, int* n_out);
+int orbx_triangulator_set_stream(orbx_triangulator* t, void* cuda_stream);
 /* transform_points_to_world (examples/point_cloud.rs:522-544), the step between triangulate and Map::add_points:
  * xyz[i] = R^T * xyz[i] + (-R^T * t), in place (host or device), nalgebra's accumulation order, unfused f64 */
 int orbx_transform_points_to_world(orbx_triangulator* t, const double* R, const double* tv, double* xyz, int n);

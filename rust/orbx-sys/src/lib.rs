@@ -55,6 +55,8 @@ extern "C" {
     pub fn orbx_triangulator_set_thresholds(t: *mut orbx_triangulator, min_parallax_deg: f64, max_reproj_error: f64) -> c_int;
     pub fn orbx_triangulator_get_thresholds(t: *const orbx_triangulator, min_parallax_deg: *mut f64, max_reproj_error: *mut f64) -> c_int;
     pub fn orbx_triangulate(t: *mut orbx_triangulator, r1: *const f64, t1: *const f64, r2: *const f64, t2: *const f64, pts1: *const f32, n1: c_int, pts2: *const f32, n2: c_int, desc: *const u8, desc_rows: c_int, ids: *mut i32, xyz: *mut f64, out_desc: *mut u8, has_desc: *mut u8, points4d: *mut f32, cap: c_int, n_out: *mut c_int) -> c_int;
+    pub fn orbx_triangulate_batch(t: *mut orbx_triangulator, r1: *const f64, t1: *const f64, r2: *const f64, t2: *const f64, pts1: *const f32, pts2: *const f32, n_dev: *const c_int, npairs: c_int, max_rows: c_int, ids: *mut i32, xyz: *mut f64, n_out: *mut c_int) -> c_int;
+    pub fn orbx_triangulator_set_stream(t: *mut orbx_triangulator, stream: *mut c_void) -> c_int;
     pub fn orbx_transform_points_to_world(t: *mut orbx_triangulator, r: *const f64, tv: *const f64, xyz: *mut f64, n: c_int) -> c_int;
     pub fn orbx_last_error() -> *const c_char;
     pub fn orbx_detector_set_stream(d: *mut orbx_detector, stream: *mut c_void) -> c_int;

@@ -85,6 +85,8 @@ def _load():
         "orbx_triangulator_get_thresholds": (i, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "orbx_triangulate": (i, [vp, vp, vp, vp, vp, vp, i, vp, i, vp, i, vp, vp, vp, vp, vp, i, ip]),
         "orbx_transform_points_to_world": (i, [vp, vp, vp, vp, i]),
+        "orbx_triangulate_batch": (i, [vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp, vp, vp]),
+        "orbx_triangulator_set_stream": (i, [vp, vp]),
         "orbx_matcher_create": (i, [i, i, C.POINTER(vp)]),
         "orbx_matcher_destroy": (None, [vp]),
         "orbx_matcher_sync": (i, [vp]),

@@ -22,7 +22,7 @@ struct orbx_triangulator {
   double fx = 0, fy = 0, cx = 0, cy = 0;
   double min_parallax_deg = 1.0;   // stored only, like the reference (triangulation.rs:54-56, 138)
   double max_reproj_error = 4.0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
   float *pts1 = nullptr, *pts2 = nullptr;  // [max_points][2] staging of host inputs
   uint8_t* desc_in = nullptr;              // [max_points][32]
   double* xyz_all = nullptr;               // [max_points][3]
@@ -48,15 +48,11 @@ __device__ __forceinline__ double cam_z(const double* R, const double* t, double
   return __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(R[6], x), __dmul_rn(R[7], y)), __dmul_rn(R[8], z)), t[2]);
 }
 
-__global__ void __launch_bounds__(128) triangulate_kernel(const float* __restrict__ pts1, const float* __restrict__ pts2,
-                                                         int n, TriCams cams, float* __restrict__ p4,
-                                                         double* __restrict__ xyz_all, uint8_t* __restrict__ keep) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+__device__ __forceinline__ void triangulate_point(const TriCams& cams, float2 q1, float2 q2, float* p4_out,
+                                                  double* xyz_out, uint8_t* keep_out) {
   double a[4][4];
   {
-    const double x1 = (double)pts1[2 * i], y1 = (double)pts1[2 * i + 1];
-    const double x2 = (double)pts2[2 * i], y2 = (double)pts2[2 * i + 1];
+    const double x1 = (double)q1.x, y1 = (double)q1.y, x2 = (double)q2.x, y2 = (double)q2.y;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       a[0][k] = __dsub_rn(__dmul_rn(x1, cams.P1[8 + k]), cams.P1[k]);
@@ -68,17 +64,69 @@ __global__ void __launch_bounds__(128) triangulate_kernel(const float* __restric
   double h[4];
   null_vector4(a, h);
   const float fx = (float)h[0], fy = (float)h[1], fz = (float)h[2], fw = (float)h[3];
-  if (p4) reinterpret_cast<float4*>(p4)[i] = make_float4(fx, fy, fz, fw);
+  if (p4_out) *reinterpret_cast<float4*>(p4_out) = make_float4(fx, fy, fz, fw);
 
   // triangulation.rs:121-136 in f64 on the f32 values
   const double w = (double)fw;
   bool ok = !(fabs(w) < 1e-10);
   const double X = __ddiv_rn((double)fx, w), Y = __ddiv_rn((double)fy, w), Z = __ddiv_rn((double)fz, w);
   ok = ok && cam_z(cams.R1, cams.t1, X, Y, Z) > 0.0 && cam_z(cams.R2, cams.t2, X, Y, Z) > 0.0;
-  xyz_all[3 * (size_t)i] = X;
-  xyz_all[3 * (size_t)i + 1] = Y;
-  xyz_all[3 * (size_t)i + 2] = Z;
-  keep[i] = ok ? 1 : 0;
+  xyz_out[0] = X;
+  xyz_out[1] = Y;
+  xyz_out[2] = Z;
+  *keep_out = ok ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(128) triangulate_kernel(const float* __restrict__ pts1, const float* __restrict__ pts2,
+                                                         int n, TriCams cams, float* __restrict__ p4,
+                                                         double* __restrict__ xyz_all, uint8_t* __restrict__ keep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  triangulate_point(cams, reinterpret_cast<const float2*>(pts1)[i], reinterpret_cast<const float2*>(pts2)[i],
+                    p4 ? p4 + 4 * (size_t)i : nullptr, xyz_all + 3 * (size_t)i, keep + i);
+}
+
+// K [R | t] on the device, same unfused arithmetic as build_projection below
+__device__ __forceinline__ void device_projection(double fx, double fy, double cx, double cy, const double* R,
+                                                  const double* t, double* P) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double r0 = j < 3 ? R[j] : t[0], r1 = j < 3 ? R[3 + j] : t[1], r2 = j < 3 ? R[6 + j] : t[2];
+    P[j] = __dadd_rn(__dmul_rn(fx, r0), __dmul_rn(cx, r2));
+    P[4 + j] = __dadd_rn(__dmul_rn(fy, r1), __dmul_rn(cy, r2));
+    P[8 + j] = r2;
+  }
+}
+
+// batched form: problem p = blockIdx.y with poses read from device memory (NULL first pose = identity / zero);
+// rows at p * max_rows
+__global__ void __launch_bounds__(128) triangulate_batch_kernel(const float* __restrict__ pts1, const float* __restrict__ pts2,
+                                                               const int* __restrict__ n_dev, int max_rows,
+                                                               const double* __restrict__ R1, const double* __restrict__ t1,
+                                                               const double* __restrict__ R2, const double* __restrict__ t2,
+                                                               double fx, double fy, double cx, double cy,
+                                                               double* __restrict__ xyz_all, uint8_t* __restrict__ keep) {
+  __shared__ TriCams cams;
+  const int p = blockIdx.y;
+  const int n = min(n_dev[p], max_rows);
+  if (blockIdx.x * blockDim.x >= n) return;
+  if (threadIdx.x < 9) {
+    cams.R1[threadIdx.x] = R1 ? R1[9 * p + threadIdx.x] : (threadIdx.x % 4 == 0 ? 1.0 : 0.0);
+    cams.R2[threadIdx.x] = R2[9 * p + threadIdx.x];
+  }
+  if (threadIdx.x < 3) {
+    cams.t1[threadIdx.x] = t1 ? t1[3 * p + threadIdx.x] : 0.0;
+    cams.t2[threadIdx.x] = t2[3 * p + threadIdx.x];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) device_projection(fx, fy, cx, cy, cams.R1, cams.t1, cams.P1);
+  if (threadIdx.x == 32) device_projection(fx, fy, cx, cy, cams.R2, cams.t2, cams.P2);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const size_t at = (size_t)p * max_rows + i;
+  triangulate_point(cams, reinterpret_cast<const float2*>(pts1)[at], reinterpret_cast<const float2*>(pts2)[at], nullptr,
+                    xyz_all + 3 * at, keep + at);
 }
 
 // ordered compaction (one block): survivors keep their input order, id = input index (triangulation.rs:140)
@@ -87,9 +135,18 @@ __global__ void __launch_bounds__(1024) triangulate_compact_kernel(const double*
                                                                   const uint8_t* __restrict__ desc_in, int desc_rows,
                                                                   int32_t* __restrict__ ids, double* __restrict__ xyz,
                                                                   uint8_t* __restrict__ desc_out,
-                                                                  uint8_t* __restrict__ has_desc, int* __restrict__ count) {
+                                                                  uint8_t* __restrict__ has_desc, int* __restrict__ count,
+                                                                  const int* __restrict__ n_dev, int max_rows) {
   __shared__ int s_warp[32];
   __shared__ int s_base;
+  // batched form: problem blockIdx.x owns rows [blockIdx.x * max_rows, +n_dev[blockIdx.x]) of every array
+  if (n_dev) {
+    const size_t off = (size_t)blockIdx.x * max_rows;
+    n = min(n_dev[blockIdx.x], max_rows);
+    xyz_all += 3 * off, keep += off, ids += off, xyz += 3 * off, count += blockIdx.x;
+    if (desc_out) desc_out += 32 * off;
+    if (has_desc) has_desc += off;
+  }
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) s_base = 0;
   __syncthreads();
@@ -200,7 +257,8 @@ int orbx_triangulator_create(int device, int max_points, double fx, double fy, d
   t->fx = fx, t->fy = fy, t->cx = cx, t->cy = cy;
   const size_t n = (size_t)max_points;
   int rc = ORBX_OK;
-  if (cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking) != cudaSuccess) rc = ORBX_E_CUDA;
+  if (cudaStreamCreateWithFlags(&t->own_stream, cudaStreamNonBlocking) != cudaSuccess) rc = ORBX_E_CUDA;
+  t->stream = t->own_stream;
   if (!rc) rc = tri_alloc(&t->pts1, n * 2);
   if (!rc) rc = tri_alloc(&t->pts2, n * 2);
   if (!rc) rc = tri_alloc(&t->desc_in, n * 32);
@@ -228,7 +286,7 @@ void orbx_triangulator_destroy(orbx_triangulator* t) {
   cudaFree(t->keep), cudaFree(t->ids), cudaFree(t->xyz), cudaFree(t->desc_out), cudaFree(t->has_desc);
   cudaFree(t->count);
   if (t->count_host) cudaFreeHost(t->count_host);
-  if (t->stream) cudaStreamDestroy(t->stream);
+  if (t->own_stream) cudaStreamDestroy(t->own_stream);
   delete t;
 }
 
@@ -308,7 +366,8 @@ int orbx_triangulate(orbx_triangulator* t, const double* R1, const double* t1, c
   triangulate_compact_kernel<<<1, 1024, 0, t->stream>>>(t->xyz_all, t->keep, n, drows > 0 ? dd : nullptr, drows,
                                                        ids_dev ? ids : t->ids, xyz_dev ? xyz : t->xyz,
                                                        out_desc ? (od_dev ? out_desc : t->desc_out) : nullptr,
-                                                       has_desc ? (hd_dev ? has_desc : t->has_desc) : nullptr, t->count);
+                                                       has_desc ? (hd_dev ? has_desc : t->has_desc) : nullptr, t->count,
+                                                       nullptr, 0);
   ORBX_LAUNCH_CHECK();
   ORBX_CUDA(cudaMemcpyAsync(t->count_host, t->count, sizeof(int), cudaMemcpyDeviceToHost, t->stream));
   if (points4d)
@@ -327,6 +386,40 @@ int orbx_triangulate(orbx_triangulator* t, const double* R1, const double* t1, c
   if (has_desc && !hd_dev)
     ORBX_CUDA(cudaMemcpyAsync(has_desc, t->has_desc, (size_t)m, cudaMemcpyDeviceToHost, t->stream));
   ORBX_CUDA(cudaStreamSynchronize(t->stream));
+  return ORBX_OK;
+}
+
+int orbx_triangulator_set_stream(orbx_triangulator* t, void* stream) {
+  if (!t) return ORBX_E_BADARG;
+  t->stream = stream ? (cudaStream_t)stream : t->own_stream;
+  return ORBX_OK;
+}
+
+int orbx_triangulate_batch(orbx_triangulator* t, const double* R1, const double* t1, const double* R2, const double* t2,
+                           const float* pts1, const float* pts2, const int* n_dev, int npairs, int max_rows, int32_t* ids,
+                           double* xyz, int* n_out) {
+  if (!t || npairs < 0 || max_rows < 0) {
+    set_error("orbx_triangulate_batch: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (npairs == 0 || max_rows == 0) return ORBX_OK;
+  if ((R1 && !is_device_ptr(R1)) || (t1 && !is_device_ptr(t1)) || !is_device_ptr(R2) || !is_device_ptr(t2) ||
+      !is_device_ptr(pts1) || !is_device_ptr(pts2) || !is_device_ptr(n_dev) || !is_device_ptr(ids) || !is_device_ptr(xyz) ||
+      !is_device_ptr(n_out)) {
+    set_error("orbx_triangulate_batch: device pointers required");
+    return ORBX_E_BADARG;
+  }
+  if ((size_t)npairs * max_rows > (size_t)t->max_points) {
+    set_error("orbx_triangulate_batch: %d x %d rows exceed max_points %d", npairs, max_rows, t->max_points);
+    return ORBX_E_CAPACITY;
+  }
+  ORBX_CUDA(cudaSetDevice(t->device));
+  triangulate_batch_kernel<<<dim3(div_up(max_rows, 128), npairs), 128, 0, t->stream>>>(
+      pts1, pts2, n_dev, max_rows, R1, t1, R2, t2, t->fx, t->fy, t->cx, t->cy, t->xyz_all, t->keep);
+  ORBX_LAUNCH_CHECK();
+  triangulate_compact_kernel<<<npairs, 1024, 0, t->stream>>>(t->xyz_all, t->keep, 0, nullptr, 0, ids, xyz, nullptr, nullptr,
+                                                             n_out, n_dev, max_rows);
+  ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }
 

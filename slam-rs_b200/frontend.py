@@ -20,7 +20,7 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
                  ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None,
-                 dual=False, points=False, pose=None):
+                 dual=False, points=False, pose=None, triangulate=False):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
@@ -69,6 +69,13 @@ class SequenceFrontEnd:
             self.pose_good = torch.zeros((T,), dtype=i32, device=self.dev)
             self.pose_status = torch.zeros((T,), dtype=i32, device=self.dev)
             self._pose_chunk = int(min(self.chunk, 256))
+        # triangulate=True (needs pose): Triangulator::triangulate (triangulation.rs:92-158) of every pair between the
+        # identity pose and the recovered (R, t): 3-D points in the camera frame of frame t-1, still on the device
+        self.triangulate = bool(triangulate) and pose is not None
+        if self.triangulate:
+            self.tri_ids = torch.zeros((T, cap), dtype=i32, device=self.dev)
+            self.tri_xyz = torch.zeros((T, cap, 3), dtype=torch.float64, device=self.dev)
+            self.tri_n = torch.zeros((T,), dtype=i32, device=self.dev)
         # staging for the host path: frames land tightly packed (one contiguous DMA per stage); when the width is not a
         # multiple of 4 liborbx repacks them into its pitched level-0 plane with its own kernel (csrc/ingest.cu)
         self.frames_dev = torch.zeros((T, self.h, self.w), dtype=u8, device=self.dev)
@@ -103,6 +110,13 @@ class SequenceFrontEnd:
                 self.pose_est2 = PoseEstimator(pose, device=device, matcher=self.matcher2, max_points=cap,
                                                max_problems=self._pose_chunk)
                 self.pose_est2.set_stream(self.stream2.cuda_stream)
+            if self.triangulate:
+                from .mapping import Triangulator
+                self.tri = Triangulator(pose, max_points=self._pose_chunk * cap, device=device)
+                self.tri.set_stream(self.mstream.cuda_stream)
+                if self.dual:
+                    self.tri2 = Triangulator(pose, max_points=self._pose_chunk * cap, device=device)
+                    self.tri2.set_stream(self.stream2.cuda_stream)
 
     # ------------------------------------------------------------------ stages
     def extract(self, frames_dev, t0, t1, det=None, step=None):
@@ -138,6 +152,11 @@ class SequenceFrontEnd:
                 pe.estimate_pose_batch_device(self.pts1[t0_], self.pts2[t0_], self.n_good[t0_:], nb, cap,
                                               self.pose_E[t0_], self.pose_R[t0_], self.pose_t[t0_],
                                               self.pose_inliers[t0_:], self.pose_good[t0_:], self.pose_status[t0_:])
+                if self.triangulate:
+                    tri = self.tri2 if (self.dual and m is self.matcher2) else self.tri
+                    tri.triangulate_batch_device(self.pose_R[t0_], self.pose_t[t0_], self.pts1[t0_], self.pts2[t0_],
+                                                 self.n_good[t0_:], nb, cap, self.tri_ids[t0_], self.tri_xyz[t0_],
+                                                 self.tri_n[t0_:])
         if self.reference_filter:
             m.match_batch_device(self.desc[a - 1], stride, self.n[a - 1:], self.desc[a], stride, self.n[a:], npairs,
                                  cap, self.m1[a], self.n_m1[a:])
@@ -267,6 +286,11 @@ class SequenceFrontEnd:
         """(E, R, t, ransac_inliers, points_in_front, status) of pair (t-1, t) (synchronises); status = ORBX_POSE_*."""
         return (self.pose_E[t].cpu().numpy(), self.pose_R[t].cpu().numpy(), self.pose_t[t].cpu().numpy(),
                 int(self.pose_inliers[t].item()), int(self.pose_good[t].item()), int(self.pose_status[t].item()))
+
+    def pair_map_points(self, t):
+        """(ids, positions float64 [m, 3]) triangulated from pair (t-1, t) (synchronises)."""
+        m = int(self.tri_n[t].item())
+        return self.tri_ids[t, :m].cpu().numpy(), self.tri_xyz[t, :m].cpu().numpy()
 
     def pair_knn(self, t):
         nq = min(int(self.n[t - 1].item()), self.cap)

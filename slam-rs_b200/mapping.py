@@ -190,6 +190,15 @@ class Triangulator:
         out = (ids[:k], xyz[:k], od[:k], hd[:k] != 0)
         return out + (p4[:n1],) if return_points4d else out
 
+    def set_stream(self, cuda_stream_ptr):
+        check(lib.orbx_triangulator_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def triangulate_batch_device(self, R2, t2, pts1, pts2, n, npairs, max_rows, ids, xyz, n_out, R1=None, t1=None):
+        """``triangulate`` for ``npairs`` problems, all CUDA tensors, asynchronous (``orbx_triangulate_batch``);
+        first pose = identity unless ``R1`` / ``t1`` are given."""
+        check(lib.orbx_triangulate_batch(self._h, _ptr(R1), _ptr(t1), _ptr(R2), _ptr(t2), _ptr(pts1), _ptr(pts2), _ptr(n),
+                                         int(npairs), int(max_rows), _ptr(ids), _ptr(xyz), _ptr(n_out)))
+
     def transform_points_to_world(self, positions, pose):
         """examples/point_cloud.rs:522-544 — camera-frame points of ``triangulate`` to the world frame."""
         r, t = Map._pose(pose)

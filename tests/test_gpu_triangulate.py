@@ -176,3 +176,33 @@ def test_large_batch_properties(orbx):
         uv = c[:, :2] / c[:, 2:] * [KITTI[0], KITTI[1]] + [KITTI[2], KITTI[3]]
         err = np.linalg.norm(uv - p[ids], axis=1)
         assert np.median(err) < 1e-2
+
+
+def test_sequence_front_end_triangulates_every_pair(orbx):
+    """SequenceFrontEnd(pose=..., triangulate=True): the batched device form (orbx_triangulate_batch, poses read from the
+    pose stage's device output) returns, for every pair, exactly what the single call returns for the same inputs."""
+    import torch
+    from oracle import synth
+    from slam_rs_b200.frontend import SequenceFrontEnd
+    T, h, w, nf = 7, 376, 1241, 800
+    seq = synth.sequence(h, w, T, canvas_seed=41, shift=24)
+    cam = orbx.CameraIntrinsics.kitti()
+    single = orbx.Triangulator(cam, max_points=4096)
+    for kwargs in ({"chunk": T}, {"chunk": T, "host_chunk": 3, "dual": True}):
+        fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, pose=cam, triangulate=True, **kwargs)
+        if "dual" in kwargs:
+            fe.run_host(torch.from_numpy(seq).pin_memory(), fe.alloc_host_outputs())
+        else:
+            dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
+            dev[:, :, :w] = torch.from_numpy(seq).cuda()
+            fe.run_device(dev)
+        torch.cuda.synchronize()
+        total = 0
+        for t in range(1, T):
+            p1, p2 = fe.pair_points(t)
+            _, Rm, tv, _, _, _ = fe.pair_pose(t)
+            ids, xyz = fe.pair_map_points(t)
+            wi, wx, _, _ = single.triangulate((np.eye(3), np.zeros(3)), (Rm, tv), p1, p2)
+            assert np.array_equal(ids, wi) and np.array_equal(xyz, wx)
+            total += len(ids)
+        assert total > 0
