@@ -180,6 +180,29 @@ def test_unaligned_device_frames_are_repacked(orbx):
         assert np.array_equal(det.level(0, frame=B - 1), imgs[B - 1])        # level 0 of the last frame, byte for byte
 
 
+@pytest.mark.parametrize("w", [204, 208, 332])
+def test_tight_aligned_pitch_device_frames_in_place(orbx, w):
+    """Device frames whose pitch equals a width that is a multiple of 4 but not of 128 are read in place (no repack,
+    no pitch padding behind the rows): same bytes out as the host path."""
+    import torch
+    h, nf, B = 101, 300, 4
+    imgs = np.stack([synth.frame(h, w, 90 + i) for i in range(B)])
+    det = orbx.OrbDetector(nf, max_width=w, max_height=h, max_batch=B)
+    host = det.detect_and_compute_batch(imgs)
+    cap = 512
+    buf = torch.from_numpy(imgs).cuda()
+    kps = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda")
+    desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    n = torch.zeros((B,), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    det.detect_and_compute_device(buf, kps, desc, n, width=w)
+    det.sync()
+    nn = n.cpu().numpy()
+    for i in range(B):
+        k = kps[i, :nn[i]].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+        assert np.array_equal(k, host[i][0]) and np.array_equal(desc[i, :nn[i]].cpu().numpy(), host[i][1])
+
+
 def test_capacity_error_reports_needed_size(orbx):
     img = synth.frame(240, 320, 5)
     det = orbx.OrbDetector(300, max_width=320, max_height=240)
