@@ -221,23 +221,28 @@ class SequenceFrontEnd:
                 self.extract(self.frames_dev, a, b, det=det, step=self.host_chunk)
                 ex = torch.cuda.Event()
                 ex.record(st)
-                if prev_extracted is not None:
-                    st.wait_event(prev_extracted)  # descriptors of frame a-1 come from the other stream
-                prev_extracted = ex
-                self.match(a, b, matcher=m)
-                last = st
             else:
+                st, m = self.mstream, self.matcher
                 self.stream.wait_event(events[i])
                 self.extract(self.frames_dev, a, b)
-                self.mstream.wait_stream(self.stream)
-                self.match(a, b)
-                last = self.mstream
-            # results of this chunk go back on the D2H stream while the next chunk computes
-            self.d2h_stream.wait_stream(last)
+                ex = torch.cuda.Event()
+                ex.record(self.stream)
+            # keypoints and descriptors of this chunk go back while it is being matched ...
+            self.d2h_stream.wait_event(ex)
             with torch.cuda.stream(self.d2h_stream):
                 out["n"][a:b].copy_(self.n[a:b], non_blocking=True)
                 out["kps"][a:b].copy_(self.kps[a:b], non_blocking=True)
                 out["desc"][a:b].copy_(self.desc[a:b], non_blocking=True)
+            if self.dual:
+                if prev_extracted is not None:
+                    st.wait_event(prev_extracted)  # descriptors of frame a-1 come from the other stream
+                prev_extracted = ex
+            else:
+                self.mstream.wait_stream(self.stream)
+            self.match(a, b, matcher=m)
+            # ... and its matches while the next chunk computes
+            self.d2h_stream.wait_stream(st)
+            with torch.cuda.stream(self.d2h_stream):
                 out["good"][a:b].copy_(self.good[a:b], non_blocking=True)
                 out["n_good"][a:b].copy_(self.n_good[a:b], non_blocking=True)
         cur.wait_stream(self.stream)
