@@ -189,11 +189,12 @@ class SequenceFrontEnd:
         self.mstream.wait_stream(cur)
         self.copy_stream.wait_stream(cur)
         self.d2h_stream.wait_stream(cur)
-        # chunk schedule: a short first chunk so that compute starts early, full chunks in the middle, a short
+        # chunk schedule: three short, doubling first chunks so that compute starts early (measured: 16.60 -> 16.43 ms
+        # against two; a fourth, or a tapered end, loses again), full chunks in the middle, a short
         # last chunk so that little is left to copy back after the last kernel
         c = self.host_chunk
         bounds, a = [], 0
-        for size in (max(c // 4, 1), max(c // 2, 1)):
+        for size in (max(c // 8, 1), max(c // 4, 1), max(c // 2, 1)):
             if T - a > c:
                 bounds.append((a, a + size))
                 a += size
