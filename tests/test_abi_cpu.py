@@ -52,6 +52,14 @@ def test_no_cpu_fallback():
     assert e.value.code == -3 and "no CPU fallback" in str(e.value)
     with pytest.raises(s.OrbxError):
         s.FeatureMatcher()
+    cam = s.CameraIntrinsics.kitti()
+    for make in (lambda: s.Map(cam, capacity=16), lambda: s.Triangulator(cam, max_points=16)):
+        with pytest.raises(s.OrbxError) as e:
+            make()
+        assert e.value.code == -3
+    h = ctypes.c_void_p()                      # (the PoseEstimator mirror creates a FeatureMatcher first: go to the ABI)
+    assert s.lib.orbx_pose_estimator_create(0, 64, 1, cam.fx, cam.fy, cam.cx, cam.cy, ctypes.byref(h)) == -3
+    assert b"no CPU fallback" in s.lib.orbx_last_error()
 
 
 def test_bad_arguments_are_errors_not_crashes():
@@ -116,3 +124,23 @@ def test_query_sharding_world2_gloo(tmp_path):
     outs = [p.communicate(timeout=300)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "OK" in outs[0]
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """bench.py --impl reference (the reference's OpenCV path on the host cores): stdout is ONE JSON line with the
+    contract's keys; nothing else may reach stdout (the NCCL banner once did)."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--ref-frames", "3"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "frames/s" and d["higher_is_better"] is True and d["value"] > 0
+    assert d["n_gpus"] == 1 and d["steps"] == 1 and d["vs_baseline"] is None and d["dtype"] == "u8"
+    assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert "workload" in d["config"]
