@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from oracle import pose_restated as PR
-from tests.test_pose_cpu import two_view_scene, K, KITTI
+from tests.test_pose_cpu import two_view_scene, golden_pose_cases, K, KITTI
 
 pytestmark = pytest.mark.gpu
 cv2 = pytest.importorskip("cv2")
@@ -52,6 +52,19 @@ def test_recover_pose_vs_cv2(orbx, seed):
     assert np.abs(R - Rcv).max() < 1e-6 and np.abs(t - tcv.ravel()).max() < 1e-6
     assert pe.last_good == good and np.array_equal(pe.last_pose_mask, mcv.ravel() != 0)
     assert np.abs(R - Rt).max() < 0.02 and abs(np.linalg.det(R) - 1.0) < 1e-9
+
+
+def test_committed_golden(orbx):
+    """tests/golden/pose_kitti.npz: OpenCV's outputs committed as a fixture (tests/golden/make_golden_pose.py)."""
+    pe = orbx.PoseEstimator(orbx.CameraIntrinsics.kitti(), max_points=1024)
+    for c in golden_pose_cases():
+        n = len(c["p1"])
+        E = pe.compute_essential_matrix(c["p1"], c["p2"])
+        assert e_diff(E, c["E"]) < 1e-6
+        assert (pe.last_mask != (c["mask"] != 0)).sum() <= max(1, n // 500)
+        R, t = pe.recover_pose(c["E"], c["p1"], c["p2"])
+        assert np.abs(R - c["R"]).max() < 1e-6 and np.abs(t - c["t"]).max() < 1e-6
+        assert pe.last_good == int(c["good"]) and np.array_equal(pe.last_pose_mask, c["pose_mask"] != 0)
 
 
 def test_full_chain_like_visual_odometry(orbx):

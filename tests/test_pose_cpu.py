@@ -75,6 +75,28 @@ def test_recover_pose_vs_cv2(seed):
     assert np.abs(R - Rt).max() < 0.02                                         # and it is the true motion
 
 
+def golden_pose_cases():
+    """tests/golden/pose_kitti.npz (made by tests/golden/make_golden_pose.py with cv2 4.13.0): yields dicts of one case."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pose_kitti.npz"))
+    for i in range(len(g["cases"])):
+        yield {k[:-len(f"_{i}")]: g[k] for k in g.files if k.endswith(f"_{i}")}
+
+
+def test_oracle_vs_committed_golden():
+    """The restatement against the committed OpenCV outputs (no cv2 call here): same winner, mask, pose."""
+    n = 0
+    for c in golden_pose_cases():
+        E, m, iters = PR.find_essential_mat(c["p1"], c["p2"], KITTI)
+        assert min(np.abs(E - c["E"]).max(), np.abs(E + c["E"]).max()) < 1e-6
+        assert np.array_equal(m, c["mask"] != 0) and 0 < iters <= 1000
+        R, t, pm, good = PR.recover_pose(c["E"], c["p1"], c["p2"], KITTI)
+        assert good == int(c["good"]) and np.array_equal(pm, c["pose_mask"] != 0)
+        assert np.abs(R - c["R"]).max() < 1e-9 and np.abs(t - c["t"]).max() < 1e-9
+        n += 1
+    assert n == 3
+
+
 def _host_solver():
     """The five-point solver and root finder of csrc/pose.cu (the section between the ORBX_HOST_TESTABLE markers is
     plain C++) compiled for the host — a test harness for the device code's arithmetic, not a product path."""
