@@ -246,6 +246,8 @@ class SequenceFrontEnd:
             with torch.cuda.stream(self.d2h_stream):
                 out["good"][a:b].copy_(self.good[a:b], non_blocking=True)
                 out["n_good"][a:b].copy_(self.n_good[a:b], non_blocking=True)
+                for key in self._extra_outputs():
+                    out[key][a:b].copy_(getattr(self, key)[a:b], non_blocking=True)
         cur.wait_stream(self.stream)
         cur.wait_stream(self.mstream)
         if self.dual:
@@ -253,10 +255,21 @@ class SequenceFrontEnd:
         cur.wait_stream(self.d2h_stream)
         return T
 
+    def _extra_outputs(self):
+        """Names of the per-pair results of the optional stages (pose, triangulation) that run_host also returns."""
+        keys = []
+        if self.pose_intrinsics is not None:
+            keys += ["pose_E", "pose_R", "pose_t", "pose_inliers", "pose_good", "pose_status"]
+        if self.triangulate:
+            keys += ["tri_ids", "tri_xyz", "tri_n"]
+        return keys
+
     def alloc_host_outputs(self):
         T, cap = self.max_frames, self.cap
         pin = dict(pin_memory=True)
+        extra = {k: torch.zeros(getattr(self, k).shape, dtype=getattr(self, k).dtype, **pin) for k in self._extra_outputs()}
         return {
+            **extra,
             "n": torch.zeros((T,), dtype=torch.int32, **pin),
             "kps": torch.zeros((T, cap, 28), dtype=torch.uint8, **pin),
             "desc": torch.zeros((T, cap, 32), dtype=torch.uint8, **pin),
@@ -268,7 +281,8 @@ class SequenceFrontEnd:
         return T * self.h * self.w
 
     def d2h_bytes(self, T):
-        return T * (4 + self.cap * (28 + 32 + 16) + 4)
+        extra = sum(getattr(self, k)[0].numel() * getattr(self, k).element_size() for k in self._extra_outputs())
+        return T * (4 + self.cap * (28 + 32 + 16) + 4 + extra)
 
     # ------------------------------------------------------------------ host views
     def frame_result(self, t):

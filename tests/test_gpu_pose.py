@@ -160,6 +160,10 @@ def test_sequence_front_end_pose(orbx):
             dev[:, :, :w] = torch.from_numpy(seq).cuda()
             fe.run_device(dev)
         torch.cuda.synchronize()
+        if "dual" in kwargs:                                                   # run_host also brings the poses back
+            for key in ("pose_E", "pose_R", "pose_t", "pose_inliers", "pose_good", "pose_status"):
+                assert np.array_equal(out[key][1:].numpy(), getattr(fe, key)[1:].cpu().numpy()), key
+            assert fe.d2h_bytes(T) == sum(v.numel() * v.element_size() for v in out.values())
         for t in range(1, T):
             p1, p2 = fe.pair_points(t)
             E, R, tv, ninl, good, status = fe.pair_pose(t)

@@ -190,8 +190,10 @@ def test_sequence_front_end_triangulates_every_pair(orbx):
     single = orbx.Triangulator(cam, max_points=4096)
     for kwargs in ({"chunk": T}, {"chunk": T, "host_chunk": 3, "dual": True}):
         fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, pose=cam, triangulate=True, **kwargs)
+        out = None
         if "dual" in kwargs:
-            fe.run_host(torch.from_numpy(seq).pin_memory(), fe.alloc_host_outputs())
+            out = fe.alloc_host_outputs()
+            fe.run_host(torch.from_numpy(seq).pin_memory(), out)
         else:
             dev = torch.zeros((T, h, fe.pitch), dtype=torch.uint8, device="cuda")
             dev[:, :, :w] = torch.from_numpy(seq).cuda()
@@ -204,5 +206,9 @@ def test_sequence_front_end_triangulates_every_pair(orbx):
             ids, xyz = fe.pair_map_points(t)
             wi, wx, _, _ = single.triangulate((np.eye(3), np.zeros(3)), (Rm, tv), p1, p2)
             assert np.array_equal(ids, wi) and np.array_equal(xyz, wx)
+            if out is not None:                                                # the host copies run_host made
+                m = int(out["tri_n"][t])
+                assert m == len(ids) and np.array_equal(out["tri_ids"][t, :m].numpy(), ids)
+                assert np.array_equal(out["tri_xyz"][t, :m].numpy(), xyz)
             total += len(ids)
         assert total > 0
