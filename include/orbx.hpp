@@ -6,6 +6,7 @@
 #include <stdexcept>
 #include <string>
 #include <utility>
+#include <array>
 #include <vector>
 
 #include "orbx.h"
@@ -103,9 +104,11 @@ class FeatureMatcher {
   orbx_matcher* h_ = nullptr;
 };
 
-struct CameraIntrinsics {  // odometry::CameraIntrinsics (camera.rs:5-36)
+struct CameraIntrinsics {  // odometry::CameraIntrinsics (camera.rs:5-55)
   double fx, fy, cx, cy;
   static CameraIntrinsics kitti() { return {718.856, 718.856, 607.1928, 185.2157}; }
+  static CameraIntrinsics webcam_vga() { return {500.0, 500.0, 320.0, 240.0}; }                   // camera.rs:29-36
+  std::array<double, 9> to_matrix() const { return {fx, 0.0, cx, 0.0, fy, cy, 0.0, 0.0, 1.0}; }  // camera.rs:39-54, row-major
 };
 
 struct Pose {  // (R, t), world to camera; R row-major

@@ -102,6 +102,10 @@ pub struct CameraIntrinsics { pub fx: f64, pub fy: f64, pub cx: f64, pub cy: f64
 impl CameraIntrinsics {
     pub fn new(fx: f64, fy: f64, cx: f64, cy: f64) -> Self { Self { fx, fy, cx, cy } }
     pub fn kitti() -> Self { Self { fx: 718.856, fy: 718.856, cx: 607.1928, cy: 185.2157 } }
+    /// camera.rs:29-36
+    pub fn webcam_vga() -> Self { Self { fx: 500.0, fy: 500.0, cx: 320.0, cy: 240.0 } }
+    /// camera.rs:39-54 (row-major 3x3; behind the `opencv-types` feature this becomes a CV_64F `Mat`)
+    pub fn to_matrix(&self) -> [f64; 9] { [self.fx, 0.0, self.cx, 0.0, self.fy, self.cy, 0.0, 0.0, 1.0] }
 }
 
 /// (R row-major, t): world-to-camera pose as the ABI takes it (nalgebra's `Matrix3` is column-major: pass `r.transpose()`).

@@ -15,7 +15,7 @@ from .feature import _ptr, FeatureMatcher
 
 
 class CameraIntrinsics:
-    """odometry::CameraIntrinsics (src/odometry/camera.rs:14-26): fx, fy, cx, cy; ``kitti()`` preset."""
+    """odometry::CameraIntrinsics (src/odometry/camera.rs:5-55): fx, fy, cx, cy; presets; ``to_matrix()``."""
 
     def __init__(self, fx, fy, cx, cy):
         self.fx, self.fy, self.cx, self.cy = float(fx), float(fy), float(cx), float(cy)
@@ -23,6 +23,16 @@ class CameraIntrinsics:
     @staticmethod
     def kitti():
         return CameraIntrinsics(718.856, 718.856, 607.1928, 185.2157)
+
+    @staticmethod
+    def webcam_vga():
+        """camera.rs:29-36"""
+        return CameraIntrinsics(500.0, 500.0, 320.0, 240.0)
+
+    def to_matrix(self):
+        """camera.rs:39-54: the 3x3 float64 camera matrix K."""
+        import numpy as np
+        return np.array([[self.fx, 0.0, self.cx], [0.0, self.fy, self.cy], [0.0, 0.0, 1.0]])
 
 
 class Map:

@@ -1,4 +1,4 @@
-// The reference's hot-path unit tests (detector.rs:51-80, matcher.rs:73-86, triangulation.rs:243-354, pose.rs:52-59)
+// The reference's hot-path unit tests (detector.rs:51-80, matcher.rs:73-86, camera.rs:58-85, triangulation.rs:243-354, pose.rs:52-59)
 // against the C++ mirror.
 // Built and run by tests/test_gpu_hostmirror.py on the GPU box.
 #include <cassert>
@@ -29,6 +29,13 @@ int main() {
     std::vector<uint8_t> e;
     assert(m.match_descriptors(e, e).size() == 0);
     assert(m.filter_good_matches({}, 2.0f).size() == 0);
+  }
+  {  // camera.rs:58-85 test_camera_creation / test_kitti_preset / test_to_matrix
+    orbx::CameraIntrinsics cam{500.0, 500.0, 320.0, 240.0};
+    assert(cam.fx == 500.0 && cam.fy == 500.0 && cam.cx == 320.0 && cam.cy == 240.0);
+    assert(orbx::CameraIntrinsics::kitti().fx > 700.0 && orbx::CameraIntrinsics::kitti().fy > 700.0);
+    auto k = orbx::CameraIntrinsics{100.0, 200.0, 50.0, 75.0}.to_matrix();
+    assert(k.size() == 9 && k[0] == 100.0 && k[2] == 50.0 && k[4] == 200.0 && k[5] == 75.0 && k[8] == 1.0 && k[1] == 0.0);
   }
   {  // triangulation.rs:243-258 test_triangulator_creation / _builder
     orbx::Triangulator t(orbx::CameraIntrinsics::kitti(), 0, 64);

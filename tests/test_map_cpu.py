@@ -52,3 +52,17 @@ def test_extract_matched_points_restatement():
         R.extract_matched_points(kp1, kp2, np.array([[5, 0]]))
     with pytest.raises(IndexError):
         R.extract_matched_points(kp1, kp2, np.array([[0, -1]]))
+
+
+def test_camera_intrinsics_mirror():
+    """camera.rs:58-85 (test_camera_creation, test_kitti_preset, test_to_matrix) over the Python mirror."""
+    from slam_rs_b200.mapping import CameraIntrinsics
+    cam = CameraIntrinsics(500.0, 500.0, 320.0, 240.0)
+    assert (cam.fx, cam.fy, cam.cx, cam.cy) == (500.0, 500.0, 320.0, 240.0)
+    k = CameraIntrinsics.kitti()
+    assert k.fx > 700.0 and k.fy > 700.0
+    v = CameraIntrinsics.webcam_vga()
+    assert (v.fx, v.cx, v.cy) == (500.0, 320.0, 240.0)
+    m = CameraIntrinsics(100.0, 200.0, 50.0, 75.0).to_matrix()
+    assert m.shape == (3, 3) and m.dtype == np.float64
+    assert np.array_equal(m, [[100.0, 0, 50.0], [0, 200.0, 75.0], [0, 0, 1.0]])
