@@ -24,8 +24,11 @@ namespace orbx {
 
 constexpr int kPoseMaxIters = 1000;
 constexpr int kPoseMaxModels = 10;
-constexpr int kPoseWaves = 4;
-__constant__ int c_wave[kPoseWaves + 1] = {0, 32, 96, 256, kPoseMaxIters};
+// Hypotheses are solved speculatively in waves (the iteration budget shrinks as soon as a good model is counted).  The
+// solve kernel holds 87 threads per SM (2.6 KB of shared scratch each), so a wave of len x pairs solves costs
+// ceil(len x pairs / 12.9 k) solve latencies: the first wave is short (the budget is ~5 at 95 % inliers).
+constexpr int kPoseWaves = 5;
+__constant__ int c_wave[kPoseWaves + 1] = {0, 8, 32, 96, 256, kPoseMaxIters};
 
 struct PoseState {
   unsigned long long rng;
@@ -450,14 +453,18 @@ __device__ int five_point_solve(const double (&x1)[5][2], const double (&x2)[5][
 }
 
 // ORBX_HOST_TESTABLE_END
-__global__ void __launch_bounds__(32) pose_solve_kernel(const PoseState* __restrict__ st, int wave, PoseParams pp,
+__global__ void __launch_bounds__(32) pose_solve_kernel(const PoseState* __restrict__ st, int nproblems, int wave, PoseParams pp,
                                                        const double* __restrict__ x1, const double* __restrict__ x2,
                                                        const int* __restrict__ samples, double* __restrict__ models,
                                                        int* __restrict__ nmodels) {
   extern __shared__ double s_solve[];  // [kSolveScratch][32]
-  const int p = blockIdx.y;
-  const int it = c_wave[wave] + blockIdx.x * blockDim.x + threadIdx.x;
-  if (it >= c_wave[wave + 1] || it >= st[p].niters) return;
+  // threads are laid over (pair, hypothesis of this wave): a warp holds 32 / len pairs in the short first wave
+  const int len = c_wave[wave + 1] - c_wave[wave];
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = g / len;
+  if (p >= nproblems) return;
+  const int it = c_wave[wave] + g % len;
+  if (it >= st[p].niters) return;
   const int* idx = samples + ((size_t)p * kPoseMaxIters + it) * 5;
   const size_t base = (size_t)p * pp.max_rows;
   double a[5][2], b[5][2];
@@ -773,15 +780,15 @@ int run_essential(orbx_pose_estimator* pe, const float* pts1, const float* pts2,
   pose_prepare_kernel<<<dim3(std::max(1, std::min(div_up(pp.max_rows, 256), 64)), np), 256, 0, s>>>(
       pts1, pts2, n_dev, n_fixed, pp, pe->x1, pe->x2, pe->state, true);
   ORBX_LAUNCH_CHECK();
-  const int wave[kPoseWaves + 1] = {0, 32, 96, 256, kPoseMaxIters};
+  const int wave[kPoseWaves + 1] = {0, 8, 32, 96, 256, kPoseMaxIters};
   constexpr int kSolveSmem = kSolveScratch * 32 * (int)sizeof(double);
   ORBX_CUDA(cudaFuncSetAttribute(pose_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSolveSmem));
   for (int w = 0; w < kPoseWaves; ++w) {
     const int len = wave[w + 1] - wave[w];
     pose_sample_kernel<<<np, 32, 0, s>>>(pe->state, w, pe->samples);
     ORBX_LAUNCH_CHECK();
-    pose_solve_kernel<<<dim3(div_up(len, 32), np), 32, kSolveSmem, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->samples, pe->models,
-                                                             pe->nmodels);
+    pose_solve_kernel<<<div_up(len * np, 32), 32, kSolveSmem, s>>>(pe->state, np, w, pp, pe->x1, pe->x2, pe->samples, pe->models,
+                                                                   pe->nmodels);
     ORBX_LAUNCH_CHECK();
     pose_count_kernel<<<dim3(std::min(len, 32), np), 128, 0, s>>>(pe->state, w, pp, pe->x1, pe->x2, pe->models, pe->nmodels, pe->counts);
     ORBX_LAUNCH_CHECK();

@@ -20,7 +20,7 @@ from .feature import OrbDetector, FeatureMatcher, KEYPOINT_DTYPE, DMATCH_DTYPE
 class SequenceFrontEnd:
     def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=250, device=0, cap=None,
                  ratio=0.75, cross_check=True, reference_filter=False, overlap=False, host_chunk=None,
-                 dual=False, points=False, pose=None, triangulate=False):
+                 dual=False, points=False, pose=None, triangulate=False, pose_chunk=1024):
         self.w, self.h = int(width), int(height)
         self.device = int(device)
         self.dev = torch.device("cuda", self.device)
@@ -68,7 +68,9 @@ class SequenceFrontEnd:
             self.pose_inliers = torch.zeros((T,), dtype=i32, device=self.dev)
             self.pose_good = torch.zeros((T,), dtype=i32, device=self.dev)
             self.pose_status = torch.zeros((T,), dtype=i32, device=self.dev)
-            self._pose_chunk = int(min(self.chunk, 256))
+            # pairs per pose launch set: the solve kernel's time is one solve's latency whatever the pair count (until the
+            # warp slots fill), so the whole chunk goes in one set (scratch: 0.8 MB per pair)
+            self._pose_chunk = int(min(self.chunk, pose_chunk))
         # triangulate=True (needs pose): Triangulator::triangulate (triangulation.rs:92-158) of every pair between the
         # identity pose and the recovered (R, t): 3-D points in the camera frame of frame t-1, still on the device
         self.triangulate = bool(triangulate) and pose is not None
@@ -102,21 +104,25 @@ class SequenceFrontEnd:
             self.matcher2.set_stream(self.stream2.cuda_stream)
         if pose is not None:
             from .odometry import PoseEstimator
-            # one estimator (scratch + stream) per pipeline stream
+            # One estimator (scratch + stream) per pipeline stream.  The pose stage runs on a stream of its own, ordered
+            # after the matched-points kernel by an event: its five-point solve is latency-bound (one warp per pair,
+            # 2.6 % of the warp slots - profiles/r01_ncu_full_pose_v9.csv), so it overlaps the next chunk's extraction.
+            self.pstream = torch.cuda.Stream(device=self.dev)
             self.pose_est = PoseEstimator(pose, device=device, matcher=self.matcher, max_points=cap,
                                           max_problems=self._pose_chunk)
-            self.pose_est.set_stream(self.mstream.cuda_stream)
+            self.pose_est.set_stream(self.pstream.cuda_stream)
             if self.dual:
+                self.pstream2 = torch.cuda.Stream(device=self.dev)
                 self.pose_est2 = PoseEstimator(pose, device=device, matcher=self.matcher2, max_points=cap,
                                                max_problems=self._pose_chunk)
-                self.pose_est2.set_stream(self.stream2.cuda_stream)
+                self.pose_est2.set_stream(self.pstream2.cuda_stream)
             if self.triangulate:
                 from .mapping import Triangulator
                 self.tri = Triangulator(pose, max_points=self._pose_chunk * cap, device=device)
-                self.tri.set_stream(self.mstream.cuda_stream)
+                self.tri.set_stream(self.pstream.cuda_stream)
                 if self.dual:
                     self.tri2 = Triangulator(pose, max_points=self._pose_chunk * cap, device=device)
-                    self.tri2.set_stream(self.stream2.cuda_stream)
+                    self.tri2.set_stream(self.pstream2.cuda_stream)
 
     # ------------------------------------------------------------------ stages
     def extract(self, frames_dev, t0, t1, det=None, step=None):
@@ -145,7 +151,10 @@ class SequenceFrontEnd:
                                                   self.good[a], self.n_good[a:], npairs, cap, self.pts1[a],
                                                   self.pts2[a], self.bad_index)
         if self.pose_intrinsics is not None:
-            pe = self.pose_est2 if (self.dual and m is self.matcher2) else self.pose_est
+            second = self.dual and m is self.matcher2
+            pe = self.pose_est2 if second else self.pose_est
+            ps = self.pstream2 if second else self.pstream
+            ps.wait_stream(self.stream2 if second else self.mstream)   # matched points of these pairs are written
             for b0 in range(0, npairs, self._pose_chunk):
                 nb = min(self._pose_chunk, npairs - b0)
                 t0_ = a + b0
@@ -153,7 +162,7 @@ class SequenceFrontEnd:
                                               self.pose_E[t0_], self.pose_R[t0_], self.pose_t[t0_],
                                               self.pose_inliers[t0_:], self.pose_good[t0_:], self.pose_status[t0_:])
                 if self.triangulate:
-                    tri = self.tri2 if (self.dual and m is self.matcher2) else self.tri
+                    tri = self.tri2 if second else self.tri
                     tri.triangulate_batch_device(self.pose_R[t0_], self.pose_t[t0_], self.pts1[t0_], self.pts2[t0_],
                                                  self.n_good[t0_:], nb, cap, self.tri_ids[t0_], self.tri_xyz[t0_],
                                                  self.tri_n[t0_:])
@@ -170,6 +179,8 @@ class SequenceFrontEnd:
         cur = torch.cuda.current_stream(self.dev)
         self.stream.wait_stream(cur)
         self.mstream.wait_stream(cur)
+        for ps in self._pose_streams():
+            ps.wait_stream(cur)
         for a in range(0, T, self.chunk):
             b = min(a + self.chunk, T)
             self.extract(frames_dev, a, b)
@@ -177,7 +188,14 @@ class SequenceFrontEnd:
             self.match(a, b)
         cur.wait_stream(self.stream)
         cur.wait_stream(self.mstream)
+        for ps in self._pose_streams():
+            cur.wait_stream(ps)
         return T
+
+    def _pose_streams(self):
+        if self.pose_intrinsics is None:
+            return []
+        return [self.pstream, self.pstream2] if self.dual else [self.pstream]
 
     def run_host(self, frames_pinned, out):
         """End-to-end pass over HOST frames (pinned uint8 [T, h, w]) into the pinned host buffers of
@@ -189,6 +207,8 @@ class SequenceFrontEnd:
         self.mstream.wait_stream(cur)
         self.copy_stream.wait_stream(cur)
         self.d2h_stream.wait_stream(cur)
+        for ps in self._pose_streams():
+            ps.wait_stream(cur)
         # chunk schedule: three short, doubling first chunks so that compute starts early (measured: 16.60 -> 16.43 ms
         # against two; a fourth, or a tapered end, loses again), full chunks in the middle, a short
         # last chunk so that little is left to copy back after the last kernel
@@ -246,12 +266,18 @@ class SequenceFrontEnd:
             with torch.cuda.stream(self.d2h_stream):
                 out["good"][a:b].copy_(self.good[a:b], non_blocking=True)
                 out["n_good"][a:b].copy_(self.n_good[a:b], non_blocking=True)
-                for key in self._extra_outputs():
-                    out[key][a:b].copy_(getattr(self, key)[a:b], non_blocking=True)
+            if self.pose_intrinsics is not None:
+                # pose / triangulation results follow on their own stream (see __init__): copied when they are ready
+                self.d2h_stream.wait_stream(self.pstream2 if (self.dual and (i & 1)) else self.pstream)
+                with torch.cuda.stream(self.d2h_stream):
+                    for key in self._extra_outputs():
+                        out[key][a:b].copy_(getattr(self, key)[a:b], non_blocking=True)
         cur.wait_stream(self.stream)
         cur.wait_stream(self.mstream)
         if self.dual:
             cur.wait_stream(self.stream2)
+        for ps in self._pose_streams():
+            cur.wait_stream(ps)
         cur.wait_stream(self.d2h_stream)
         return T
 
