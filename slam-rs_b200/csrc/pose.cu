@@ -658,13 +658,16 @@ __global__ void __launch_bounds__(128) pose_cheirality_kernel(PoseState* __restr
   if (i < s.n) {
     const double ax = x1[2 * (base + i)], ay = x1[2 * (base + i) + 1];
     const double bx = x2[2 * (base + i)], by = x2[2 * (base + i) + 1];
-    for (int c = 0; c < 4; ++c) {
-      const double* R = (c & 1) ? s.R2 : s.R1;
-      const double sg = c >= 2 ? -1.0 : 1.0;
+    // Candidates c and c + 2 share R and differ in the sign of t: their DLT systems differ by the sign of column 3,
+    // every step of the Jacobi iteration is sign-symmetric in IEEE arithmetic, so the null vector of the second is
+    // (q0, q1, q2, -q3) bit for bit - the point and its depth in the second view are the exact negatives.  Two SVDs
+    // per point instead of four, same results.
+    for (int c = 0; c < 2; ++c) {
+      const double* R = c ? s.R2 : s.R1;
       double P[3][4];
       for (int r = 0; r < 3; ++r) {
         P[r][0] = R[3 * r], P[r][1] = R[3 * r + 1], P[r][2] = R[3 * r + 2];
-        P[r][3] = sg * s.t[r];
+        P[r][3] = s.t[r];
       }
       double a[4][4];
       // first view: P0 = [I | 0]
@@ -676,12 +679,12 @@ __global__ void __launch_bounds__(128) pose_cheirality_kernel(PoseState* __restr
       }
       double q[4];
       null_vector4(a, q);
-      bool ok = q[2] * q[3] > 0.0;
+      const double w = q[2] * q[3];
       const double X = q[0] / q[3], Y = q[1] / q[3], Z = q[2] / q[3];
-      ok = ok && Z < 50.0;
       const double z2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(P[2][0], X), __dmul_rn(P[2][1], Y)), __dmul_rn(P[2][2], Z)), P[2][3]);
-      ok = ok && z2 > 0.0 && z2 < 50.0;
-      keep |= ok ? 1u << c : 0u;
+      const bool ok_pos = w > 0.0 && Z < 50.0 && z2 > 0.0 && z2 < 50.0;          // (R, t)
+      const bool ok_neg = w < 0.0 && -Z < 50.0 && -z2 > 0.0 && -z2 < 50.0;       // (R, -t)
+      keep |= (ok_pos ? 1u << c : 0u) | (ok_neg ? 1u << (c + 2) : 0u);
     }
     bits[base + i] = (uint8_t)keep;
   }
