@@ -150,7 +150,8 @@ def test_sequence_front_end_pose(orbx):
     seq = synth.sequence(h, w, T, canvas_seed=31, shift=24)
     cam = orbx.CameraIntrinsics.kitti()
     same = pairs = 0
-    for kwargs in ({"chunk": T}, {"chunk": T, "host_chunk": 3, "dual": True}):
+    # pose_chunk=3: the pairs of a chunk go through the pose stage in several launch sets (the default takes them in one)
+    for kwargs in ({"chunk": T, "pose_chunk": 3}, {"chunk": T, "host_chunk": 3, "dual": True}):
         fe = SequenceFrontEnd(w, h, nfeatures=nf, max_frames=T, pose=cam, **kwargs)
         if "dual" in kwargs:
             out = fe.alloc_host_outputs()
