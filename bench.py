@@ -371,6 +371,13 @@ def run_ours(args, rank, world, local_rank):
                     "avg_launch_ms": match_ms / max(match_launches, 1),
                     "note": "integer XOR+POPC work: neither HBM nor tensor bound (north_star stage 5); achieved = "
                             "algorithmic 8 POPC x (forward + reverse) pairs, the kernel issues 5 POPC per pair once"}
+            # the HBM view of the same kernel, for the record: every descriptor row is read once (32 B) and every query
+            # row writes its two DMatch records, its count and one reverse-best word (44 B): far below the HBM roofline
+            ham_bytes = float(np.sum(n_dev)) * (32 + 44) * args.steps
+            ham_gbs = ham_bytes / (match_ms * 1e-3) / 1e9
+            roof["hbm"] = {"bound": "hbm", "achieved": ham_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ham_gbs / hbm_peak,
+                           "algorithmic_bytes_per_launch": ham_bytes / max(match_launches, 1), "traffic": tr,
+                           "peak_source": "MEASURED_PEAKS.json hbm_gbs (%s)" % peak_kind}
         else:
             key = {"blur": "blur+brief", "brief": "blur+brief"}.get(dom, dom)
             s = stages.get(key, {})
