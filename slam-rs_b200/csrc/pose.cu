@@ -144,6 +144,13 @@ __device__ __forceinline__ double horner(const double* c, int deg, double z) { r
 // real roots of a polynomial of degree <= 10 (ascending coefficients): between consecutive real roots of p' the
 // polynomial is monotonic, so the roots of p^(k) bracket those of p^(k-1); every bracket with a sign change is
 // bisected.  d: scratch for the derivative table (11 x 11, strided).  Returns the number of roots (ascending).
+//
+// The kernel is latency-bound (one solve per thread, dependent DFMA chains: profiles/r01_ncu_full_pose_v9.csv has 70 %
+// of its stall samples in the Horner loop of the bisection), so each level is evaluated in independent chains: all
+// bracket ends in one multi-point Horner pass, then the brackets with a sign change bisected four at a time.  Every
+// bracket sees exactly the arithmetic of a one-at-a-time bisection; only the interleaving differs.
+constexpr int kRootLanes = 4;
+
 template <int SS>
 __device__ int real_roots(const double* coef, int deg, double* roots, double* d) {
   while (deg > 0 && coef[deg] == 0.0) --deg;
@@ -153,6 +160,8 @@ __device__ int real_roots(const double* coef, int deg, double* roots, double* d)
   for (int k = 1; k < deg; ++k)
     for (int i = 0; i <= deg - k; ++i) D_(k, i) = D_(k - 1, i + 1) * (double)(i + 1);
   double prev[10], cur[10];
+  double ba[10], bb[10], bfa[10];  // brackets to bisect at this level: ends, value at the low end
+  int bpos[10];                    // and where their root goes in cur
   int nprev = 1;
   prev[0] = -D_(deg - 1, 0) / D_(deg - 1, 1);  // the linear one
   for (int k = deg - 2; k >= 0; --k) {
@@ -161,53 +170,106 @@ __device__ int real_roots(const double* coef, int deg, double* roots, double* d)
     double mx = 0;  // Cauchy bound of this polynomial
     for (int i = 0; i < dg; ++i) mx = fmax(mx, fabs(c[i * SS] / c[dg * SS]));
     const double B = 1.0 + mx;
-    int ncur = 0;
-    double lo = -B, flo = horner_s<SS>(c, dg, lo);
-    for (int j = 0; j <= nprev; ++j) {
-      const double hi = j < nprev ? fmin(fmax(prev[j], -B), B) : B;
-      const double fhi = horner_s<SS>(c, dg, hi);
-      if (flo == 0.0) {
-        if (ncur == 0 || cur[ncur - 1] != lo) cur[ncur++] = lo;
-      } else if ((flo < 0.0) != (fhi < 0.0) && fhi != 0.0) {
-        // 34 bisection steps (2^-34 of the bracket is plenty for the critical points, which only serve as brackets of
-        // the next level), then - for the polynomial itself - Newton steps inside the bracket down to rounding
-        double a = lo, b = hi, fa = flo;
-        for (int itr = 0; itr < 34; ++itr) {
-          const double m = 0.5 * (a + b);
-          if (m == a || m == b) break;
-          const double fm = horner_s<SS>(c, dg, m);
-          if (fm == 0.0) {
-            a = b = m;
-            break;
-          }
-          if ((fm < 0.0) == (fa < 0.0))
-            a = m, fa = fm;
-          else
-            b = m;
-        }
-        if (k == 0 && a != b) {
-          double x = 0.5 * (a + b);
-          for (int itr = 0; itr < 6; ++itr) {
-            double f = c[dg * SS], df = 0.0;
-            for (int i = dg - 1; i >= 0; --i) {
-              df = df * x + f;
-              f = f * x + c[i * SS];
-            }
-            const double xn = x - f / df;
-            if (!(xn >= a && xn <= b)) break;  // also catches df == 0
-            const bool done = fabs(xn - x) <= 4.5e-16 * fabs(xn);
-            x = xn;
-            if (done) break;
-          }
-          a = b = x;
-        }
-        cur[ncur++] = 0.5 * (a + b);
-      }
-      lo = hi;
-      flo = fhi;
-      if (ncur >= dg) break;
+    // the polynomial at the bracket ends x_0 = -B, x_j = critical point j - 1 (clamped), x_(nprev + 1) = B
+    double xs[12], fs[12];
+    xs[0] = -B, xs[11] = B;
+#pragma unroll
+    for (int j = 1; j <= 10; ++j) {
+      xs[j] = B;  // unused slots repeat the upper bound
+      if (j <= nprev) xs[j] = fmin(fmax(prev[j - 1], -B), B);
     }
-    if (flo == 0.0 && ncur < dg && (ncur == 0 || cur[ncur - 1] != lo)) cur[ncur++] = lo;
+#pragma unroll
+    for (int j = 0; j < 12; ++j) fs[j] = c[dg * SS];
+    for (int i = dg - 1; i >= 0; --i) {
+      const double ci = c[i * SS];
+#pragma unroll
+      for (int j = 0; j < 12; ++j) fs[j] = fs[j] * xs[j] + ci;
+    }
+    // scan the brackets in order: exact zeros at bracket ends are roots, sign changes are queued for bisection
+    int ncur = 0, nb = 0;
+    bool stop = false;
+    double lo_last = xs[0], flo_last = fs[0];
+#pragma unroll
+    for (int j = 0; j < 11; ++j) {
+      if (!stop && j <= nprev) {
+        const double lo = xs[j], flo = fs[j], hi = xs[j + 1], fhi = fs[j + 1];
+        if (flo == 0.0) {
+          if (ncur == 0 || cur[ncur - 1] != lo) cur[ncur++] = lo;
+        } else if ((flo < 0.0) != (fhi < 0.0) && fhi != 0.0) {
+          ba[nb] = lo, bb[nb] = hi, bfa[nb] = flo, bpos[nb] = ncur;
+          ++nb;
+          cur[ncur++] = nan("");  // filled below; a bisected root never equals a later bracket end with value zero
+        }
+        lo_last = hi, flo_last = fhi;
+        if (ncur >= dg) stop = true;
+      }
+    }
+    if (flo_last == 0.0 && ncur < dg && (ncur == 0 || cur[ncur - 1] != lo_last)) cur[ncur++] = lo_last;
+    // 34 bisection steps per bracket (2^-34 of the bracket is plenty for the critical points, which only serve as
+    // brackets of the next level), kRootLanes brackets in flight
+    for (int g = 0; g < nb; g += kRootLanes) {
+      double a[kRootLanes], b[kRootLanes], fa[kRootLanes];
+      bool live[kRootLanes];
+#pragma unroll
+      for (int u = 0; u < kRootLanes; ++u) {
+        const int q = g + u < nb ? g + u : g;
+        a[u] = ba[q], b[u] = bb[q], fa[u] = bfa[q];
+        live[u] = g + u < nb;
+      }
+      for (int itr = 0; itr < 34; ++itr) {
+        double m[kRootLanes], fm[kRootLanes];
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < kRootLanes; ++u) {
+          m[u] = 0.5 * (a[u] + b[u]);
+          if (m[u] == a[u] || m[u] == b[u]) live[u] = false;
+          any |= live[u];
+          fm[u] = c[dg * SS];
+        }
+        if (!any) break;
+        for (int i = dg - 1; i >= 0; --i) {
+          const double ci = c[i * SS];
+#pragma unroll
+          for (int u = 0; u < kRootLanes; ++u) fm[u] = fm[u] * m[u] + ci;
+        }
+#pragma unroll
+        for (int u = 0; u < kRootLanes; ++u) {
+          if (!live[u]) continue;
+          if (fm[u] == 0.0) {
+            a[u] = b[u] = m[u];
+            live[u] = false;
+          } else if ((fm[u] < 0.0) == (fa[u] < 0.0)) {
+            a[u] = m[u], fa[u] = fm[u];
+          } else {
+            b[u] = m[u];
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kRootLanes; ++u)
+        if (g + u < nb) ba[g + u] = a[u], bb[g + u] = b[u];
+    }
+    // the roots of the polynomial itself (k == 0) are polished by Newton steps inside the bracket down to rounding
+    for (int q = 0; q < nb; ++q) {
+      double a = ba[q], b = bb[q];
+      if (k == 0 && a != b) {
+        double x = 0.5 * (a + b);
+        for (int itr = 0; itr < 6; ++itr) {
+          double f = c[dg * SS], df = 0.0;
+          for (int i = dg - 1; i >= 0; --i) {
+            df = df * x + f;
+            f = f * x + c[i * SS];
+          }
+          const double xn = x - f / df;
+          if (!(xn >= a && xn <= b)) break;  // also catches df == 0
+          const bool done = fabs(xn - x) <= 4.5e-16 * fabs(xn);
+          x = xn;
+          if (done) break;
+        }
+        a = b = x;
+      }
+      cur[bpos[q]] = 0.5 * (a + b);
+    }
     nprev = ncur;
     for (int j = 0; j < ncur; ++j) prev[j] = cur[j];
   }
