@@ -149,7 +149,10 @@ __device__ __forceinline__ double horner(const double* c, int deg, double z) { r
 // of its stall samples in the Horner loop of the bisection), so each level is evaluated in independent chains: all
 // bracket ends in one multi-point Horner pass, then the brackets with a sign change bisected four at a time.  Every
 // bracket sees exactly the arithmetic of a one-at-a-time bisection; only the interleaving differs.
-constexpr int kRootLanes = 4;
+#ifndef ORBX_ROOT_LANES
+#define ORBX_ROOT_LANES 4  // tests/test_pose_cpu.py builds the host harness with 1 as well and compares bit for bit
+#endif
+constexpr int kRootLanes = ORBX_ROOT_LANES;
 
 template <int SS>
 __device__ int real_roots(const double* coef, int deg, double* roots, double* d) {

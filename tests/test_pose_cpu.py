@@ -97,7 +97,7 @@ def test_oracle_vs_committed_golden():
     assert n == 3
 
 
-def _host_solver():
+def _host_solver(extra_flags=()):
     """The five-point solver and root finder of csrc/pose.cu (the section between the ORBX_HOST_TESTABLE markers is
     plain C++) compiled for the host — a test harness for the device code's arithmetic, not a product path."""
     import ctypes as C
@@ -116,7 +116,8 @@ def _host_solver():
            "extern \"C\" int roots(const double* c, int deg, double* r) { double d[121]; return real_roots<1>(c, deg, r, d); }\n")
     d = tempfile.mkdtemp(prefix="orbx_pose_host_")
     open(os.path.join(d, "host.cpp"), "w").write(src)
-    subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-o", os.path.join(d, "libhost.so"), os.path.join(d, "host.cpp")])
+    subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", *extra_flags, "-o", os.path.join(d, "libhost.so"),
+                           os.path.join(d, "host.cpp")])
     return C.CDLL(os.path.join(d, "libhost.so"))
 
 
@@ -143,3 +144,27 @@ def test_device_solver_arithmetic_on_host():
         E, m, _ = PR.find_essential_mat(p1, p2, KITTI, solver=solve)
         assert min(np.abs(E - Ecv).max(), np.abs(E + Ecv).max()) < 1e-6
         assert np.array_equal(m, mcv.ravel().astype(bool))
+
+
+def test_interleaved_bisection_is_bit_identical_to_serial():
+    """The root finder bisects four brackets of a level at a time (ORBX_ROOT_LANES = 4, for instruction-level parallelism
+    on the device); with one lane it is the plain one-bracket-at-a-time bisection.  Same roots and same essential
+    matrices, bit for bit - incl. polynomials with exact zeros at bracket ends and multiple roots."""
+    import ctypes as C
+    par, ser = _host_solver(), _host_solver(("-DORBX_ROOT_LANES=1",))
+    rng = np.random.default_rng(5)
+    for t in range(4000):
+        deg = int(rng.integers(2, 11))
+        c = np.zeros(11)
+        c[:deg + 1] = np.poly(rng.integers(-3, 4, deg))[::-1] if t % 5 == 0 else rng.normal(0, 1, deg + 1)
+        r1, r2 = np.zeros(10), np.zeros(10)
+        n1 = ser.roots(C.c_void_p(c.ctypes.data), 10, C.c_void_p(r1.ctypes.data))
+        n2 = par.roots(C.c_void_p(c.ctypes.data), 10, C.c_void_p(r2.ctypes.data))
+        assert n1 == n2 and np.array_equal(r1[:n1].view(np.int64), r2[:n2].view(np.int64)), c
+    for _ in range(500):
+        x1 = rng.normal(0, 0.3, (5, 2))
+        x2 = x1 + rng.normal(0, 0.05, (5, 2))
+        m1, m2 = np.zeros((10, 9)), np.zeros((10, 9))
+        n1 = ser.solve5(C.c_void_p(x1.ctypes.data), C.c_void_p(x2.ctypes.data), C.c_void_p(m1.ctypes.data))
+        n2 = par.solve5(C.c_void_p(x1.ctypes.data), C.c_void_p(x2.ctypes.data), C.c_void_p(m2.ctypes.data))
+        assert n1 == n2 and np.array_equal(m1[:n1].view(np.int64), m2[:n2].view(np.int64))
