@@ -168,3 +168,46 @@ def test_interleaved_bisection_is_bit_identical_to_serial():
         n1 = ser.solve5(C.c_void_p(x1.ctypes.data), C.c_void_p(x2.ctypes.data), C.c_void_p(m1.ctypes.data))
         n2 = par.solve5(C.c_void_p(x1.ctypes.data), C.c_void_p(x2.ctypes.data), C.c_void_p(m2.ctypes.data))
         assert n1 == n2 and np.array_equal(m1[:n1].view(np.int64), m2[:n2].view(np.int64))
+
+
+def test_cheirality_sign_symmetry_of_the_jacobi_null_vector():
+    """pose_cheirality_kernel runs one SVD for the candidates (R, t) and (R, -t): their DLT systems differ by the sign
+    of column 3, and csrc/jacobi.cuh's iteration is sign-symmetric in IEEE arithmetic, so the null vector of the second
+    is (q0, q1, q2, -q3) or its negative BIT FOR BIT.  Checked on the host build of jacobi.cuh, with and without FMA
+    contraction (the device contracts)."""
+    import ctypes as C
+    import os
+    import subprocess
+    import tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = ("#include <math.h>\n#define __device__\n#define __forceinline__ inline\n"
+           "#include \"%s\"\n"
+           "extern \"C\" void nullvec(const double* a, double* q) { double m[4][4], h[4];\n"
+           "  for (int i = 0; i < 16; ++i) m[i / 4][i %% 4] = a[i];\n"
+           "  orbx::null_vector4(m, h); for (int i = 0; i < 4; ++i) q[i] = h[i]; }\n"
+           % os.path.join(root, "slam-rs_b200", "csrc", "jacobi.cuh"))
+    d = tempfile.mkdtemp(prefix="orbx_jacobi_host_")
+    open(os.path.join(d, "j.cpp"), "w").write(src)
+    rng = np.random.default_rng(9)
+    for flags in ((), ("-mfma", "-ffp-contract=fast")):
+        so = os.path.join(d, "libj%d.so" % len(flags))
+        subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", *flags, "-o", so, os.path.join(d, "j.cpp")])
+        lib = C.CDLL(so)
+        for t in range(2000):
+            if t % 2:                                                          # the DLT system of the kernel: [I | 0] and [R | t]
+                ax, ay, bx, by = rng.normal(0, 0.4, 4)
+                P = np.hstack([np.linalg.qr(rng.normal(0, 1, (3, 3)))[0], rng.normal(0, 1, (3, 1))])
+                A = np.array([[-1, 0, ax, 0], [0, -1, ay, 0], bx * P[2] - P[0], by * P[2] - P[1]], np.float64)
+            else:
+                A = rng.normal(0, 1, (4, 4))
+            A2 = A * np.array([1.0, 1.0, 1.0, -1.0])
+            q, q2 = np.zeros(4), np.zeros(4)
+            lib.nullvec(C.c_void_p(np.ascontiguousarray(A).ctypes.data), C.c_void_p(q.ctypes.data))
+            lib.nullvec(C.c_void_p(np.ascontiguousarray(A2).ctypes.data), C.c_void_p(q2.ctypes.data))
+            want = q * np.array([1.0, 1.0, 1.0, -1.0])
+            assert (np.array_equal(q2.view(np.int64), want.view(np.int64))
+                    or np.array_equal(q2.view(np.int64), (-want).view(np.int64))), (A, q, q2)
+            sv = np.linalg.svd(A)
+            if sv[1][2] - sv[1][3] > 1e-3 * sv[1][0]:                          # and it is LAPACK's smallest right singular vector
+                v = sv[2][3]
+                assert min(np.abs(q - v).max(), np.abs(q + v).max()) < 1e-9
