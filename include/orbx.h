@@ -295,6 +295,30 @@ int orbx_triangulator_set_stream(orbx_triangulator* t, void* cuda_stream);
  * xyz[i] = R^T * xyz[i] + (-R^T * t), in place (host or device), nalgebra's accumulation order, unfused f64 */
 int orbx_transform_points_to_world(orbx_triangulator* t, const double* R, const double* tv, double* xyz, int n);
 
+/* ------------------------------------------------------------------ sequence front end
+ * The per-frame loop of examples/visual_odometry.rs:84-218 (detect_and_compute :102, match_descriptors :106, match
+ * filter :107) over a whole sequence, scheduled natively (csrc/sequence.cu): frames -> T x (keypoints, descriptors) ->
+ * T-1 frame-to-frame problems, BFMatcher k=2 (+ cross-check) + Lowe ratio.  Row capacity per frame is
+ * orbx_sequence_capacity() (>= nfeatures: OpenCV keeps ties).  Result row t of `good` / `n_good` describes the pair
+ * (t-1, t); row 0 is unused.  All run calls are asynchronous: orbx_sequence_sync() before reading results. */
+typedef struct orbx_sequence orbx_sequence;
+/* chunk: frames per launch set of orbx_sequence_run_device; host_chunk: pipeline granularity of orbx_sequence_run_host */
+int orbx_sequence_create(int device, int width, int height, int nfeatures, int max_frames, int chunk, int host_chunk,
+                         float ratio, int cross_check, orbx_sequence** out);
+void orbx_sequence_destroy(orbx_sequence* s);
+int orbx_sequence_capacity(const orbx_sequence* s);
+/* device-resident frames (8UC1, `pitch` bytes per row, frame t at frames_dev + t*frame_stride); results stay in HBM */
+int orbx_sequence_run_device(orbx_sequence* s, const uint8_t* frames_dev, size_t pitch, size_t frame_stride, int T);
+/* HOST frames, tightly packed [T][height][width] (pinned memory for copy / compute overlap), results to host arrays
+ * (pinned likewise; any may be NULL): kps T x cap, desc T x cap x 32, n T, good T x cap, n_good T.  Upload, kernels
+ * and download of consecutive chunks overlap on four streams. */
+int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_keypoint* kps, uint8_t* desc, int* n,
+                           orbx_dmatch* good, int* n_good);
+/* device pointers of the last pass's results (layout as above; valid until destroy) */
+int orbx_sequence_results(orbx_sequence* s, orbx_keypoint** kps, uint8_t** desc, int** n, orbx_dmatch** good,
+                          int** n_good);
+int orbx_sequence_sync(orbx_sequence* s);
+
 /* ------------------------------------------------------------------ misc */
 const char* orbx_last_error(void);
 const char* orbx_version(void);

@@ -204,4 +204,41 @@ class Triangulator {
   orbx_triangulator* h_ = nullptr;
 };
 
+// The per-frame loop of examples/visual_odometry.rs:84-218 over a whole sequence (csrc/sequence.cu): host frames in,
+// keypoints / descriptors of every frame and the good matches of every consecutive pair out.
+class Sequence {
+ public:
+  struct Result {  // row t of good / n_good describes the pair (t-1, t); rows hold capacity() entries, n[t] / n_good[t] valid
+    std::vector<orbx_keypoint> kps;
+    std::vector<uint8_t> desc;
+    std::vector<int> n;
+    std::vector<orbx_dmatch> good;
+    std::vector<int> n_good;
+  };
+  Sequence(int width, int height, int nfeatures, int max_frames, int device = 0, int chunk = 1000, int host_chunk = 167,
+           float ratio = 0.75f, bool cross_check = true)
+      : max_frames_(max_frames) {
+    check(orbx_sequence_create(device, width, height, nfeatures, max_frames, chunk, host_chunk, ratio, cross_check ? 1 : 0,
+                               &h_));
+  }
+  ~Sequence() { orbx_sequence_destroy(h_); }
+  Sequence(const Sequence&) = delete;
+  Sequence& operator=(const Sequence&) = delete;
+
+  int capacity() const { return orbx_sequence_capacity(h_); }
+  // frames: T tightly packed 8-bit images (pinned memory lets the upload overlap the kernels); blocks until done
+  Result run(const uint8_t* frames, int T) {
+    const size_t cap = (size_t)capacity(), n = (size_t)T;
+    Result r;
+    r.kps.resize(n * cap), r.desc.resize(n * cap * 32), r.n.resize(n), r.good.resize(n * cap), r.n_good.resize(n);
+    check(orbx_sequence_run_host(h_, frames, T, r.kps.data(), r.desc.data(), r.n.data(), r.good.data(), r.n_good.data()));
+    check(orbx_sequence_sync(h_));
+    return r;
+  }
+
+ private:
+  orbx_sequence* h_ = nullptr;
+  int max_frames_;
+};
+
 }  // namespace orbx

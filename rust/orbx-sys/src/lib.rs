@@ -14,6 +14,7 @@ pub enum orbx_matcher {}
 pub enum orbx_map {}
 pub enum orbx_triangulator {}
 pub enum orbx_pose_estimator {}
+pub enum orbx_sequence {}
 pub const ORBX_E_DATA: c_int = -5;
 pub const ORBX_OK: c_int = 0;
 pub const ORBX_E_CAPACITY: c_int = -2;
@@ -58,6 +59,16 @@ extern "C" {
     pub fn orbx_triangulate_batch(t: *mut orbx_triangulator, r1: *const f64, t1: *const f64, r2: *const f64, t2: *const f64, pts1: *const f32, pts2: *const f32, n_dev: *const c_int, npairs: c_int, max_rows: c_int, ids: *mut i32, xyz: *mut f64, n_out: *mut c_int) -> c_int;
     pub fn orbx_triangulator_set_stream(t: *mut orbx_triangulator, stream: *mut c_void) -> c_int;
     pub fn orbx_transform_points_to_world(t: *mut orbx_triangulator, r: *const f64, tv: *const f64, xyz: *mut f64, n: c_int) -> c_int;
+    pub fn orbx_sequence_create(device: c_int, width: c_int, height: c_int, nfeatures: c_int, max_frames: c_int, chunk: c_int,
+        host_chunk: c_int, ratio: f32, cross_check: c_int, out: *mut *mut orbx_sequence) -> c_int;
+    pub fn orbx_sequence_destroy(s: *mut orbx_sequence);
+    pub fn orbx_sequence_capacity(s: *const orbx_sequence) -> c_int;
+    pub fn orbx_sequence_run_device(s: *mut orbx_sequence, frames_dev: *const u8, pitch: usize, frame_stride: usize, t: c_int) -> c_int;
+    pub fn orbx_sequence_run_host(s: *mut orbx_sequence, frames: *const u8, t: c_int, kps: *mut orbx_keypoint, desc: *mut u8,
+        n: *mut c_int, good: *mut orbx_dmatch, n_good: *mut c_int) -> c_int;
+    pub fn orbx_sequence_results(s: *mut orbx_sequence, kps: *mut *mut orbx_keypoint, desc: *mut *mut u8, n: *mut *mut c_int,
+        good: *mut *mut orbx_dmatch, n_good: *mut *mut c_int) -> c_int;
+    pub fn orbx_sequence_sync(s: *mut orbx_sequence) -> c_int;
     pub fn orbx_last_error() -> *const c_char;
     pub fn orbx_detector_set_stream(d: *mut orbx_detector, stream: *mut c_void) -> c_int;
 }

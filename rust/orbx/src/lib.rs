@@ -186,3 +186,40 @@ impl Triangulator {
     }
 }
 impl Drop for Triangulator { fn drop(&mut self) { unsafe { sys::orbx_triangulator_destroy(self.h) } } }
+
+/// One frame's features and (for t >= 1) the good matches of the pair (t-1, t), as `Sequence::run` returns them.
+pub struct FrameResult { pub keypoints: Vec<KeyPoint>, pub descriptors: Vec<u8>, pub good_matches: Vec<DMatch> }
+
+/// The loop of examples/visual_odometry.rs:84-218 (detect_and_compute :102, match_descriptors :106, filter :107) over a
+/// whole sequence in one call: liborbx schedules the frames through its batched kernels (csrc/sequence.cu), upload,
+/// kernels and download of consecutive chunks overlapping.  Matching is BFMatcher k=2 + cross-check + Lowe ratio.
+pub struct Sequence { h: *mut sys::orbx_sequence, width: usize, height: usize }
+
+impl Sequence {
+    pub fn new(width: usize, height: usize, max_features: i32, max_frames: usize) -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_sequence_create(0, width as i32, height as i32, max_features, max_frames as i32, 1000, 167, 0.75, 1, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h, width, height })
+    }
+    /// `frames`: T tightly packed 8-bit gray images (T * height * width bytes)
+    pub fn run(&mut self, frames: &[u8]) -> Result<Vec<FrameResult>, Box<dyn Error>> {
+        let t = frames.len() / (self.width * self.height);
+        let cap = unsafe { sys::orbx_sequence_capacity(self.h) } as usize;
+        let mut kps = vec![KeyPoint::default(); t * cap];
+        let mut desc = vec![0u8; t * cap * 32];
+        let mut good = vec![DMatch::default(); t * cap];
+        let (mut n, mut n_good) = (vec![0i32; t], vec![0i32; t]);
+        let rc = unsafe { sys::orbx_sequence_run_host(self.h, frames.as_ptr(), t as i32, kps.as_mut_ptr(), desc.as_mut_ptr(),
+            n.as_mut_ptr(), good.as_mut_ptr(), n_good.as_mut_ptr()) };
+        if rc != 0 { return Err(err(rc)); }
+        let rc = unsafe { sys::orbx_sequence_sync(self.h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((0..t).map(|i| {
+            let (k, g) = (n[i] as usize, if i > 0 { n_good[i] as usize } else { 0 });
+            FrameResult { keypoints: kps[i * cap..i * cap + k].to_vec(), descriptors: desc[i * cap * 32..(i * cap + k) * 32].to_vec(),
+                          good_matches: good[i * cap..i * cap + g].to_vec() }
+        }).collect())
+    }
+}
+impl Drop for Sequence { fn drop(&mut self) { unsafe { sys::orbx_sequence_destroy(self.h) } } }

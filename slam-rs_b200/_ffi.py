@@ -103,6 +103,13 @@ def _load():
         "orbx_extract_matched_points_batch": (i, [vp, vp, vp, vp, vp, C.c_size_t, vp, vp, i, i, vp, vp, vp]),
         "orbx_matcher_set_timing": (i, [vp, i]),
         "orbx_matcher_timing": (i, [vp, C.POINTER(f), ip, i]),
+        "orbx_sequence_create": (i, [i, i, i, i, i, i, i, f, i, C.POINTER(vp)]),
+        "orbx_sequence_destroy": (None, [vp]),
+        "orbx_sequence_capacity": (i, [vp]),
+        "orbx_sequence_run_device": (i, [vp, vp, sz, sz, i]),
+        "orbx_sequence_run_host": (i, [vp, vp, i, vp, vp, vp, vp, vp]),
+        "orbx_sequence_results": (i, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+        "orbx_sequence_sync": (i, [vp]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
         "orbx_launch_count": (C.c_uint64, []),

@@ -1,0 +1,314 @@
+// liborbx — the sequence front end as a native entry of the C ABI.
+//
+// /root/reference/examples/visual_odometry.rs:84-218 runs, per frame, detect_and_compute (:102), match_descriptors
+// (:106) and a match filter (:107).  Over a whole sequence the extractions are independent and so are the T-1
+// frame-to-frame matching problems; this file runs them as batched launches of the detector / matcher handles with the
+// pipeline that slam-rs_b200/frontend.py::SequenceFrontEnd measured best on B200: frames go up in chunks on a copy
+// stream, two detector + matcher pairs on two streams alternate over the chunks (the tail wave of every kernel of one
+// chunk overlaps the next chunk's kernels), results go back on a fourth stream while the next chunk computes.
+// No kernels of its own: host-side scheduling only (streams, events, the chunk schedule).
+#include <vector>
+
+#include "common.cuh"
+
+struct orbx_sequence {
+  int device = 0, w = 0, h = 0, nfeatures = 0, max_frames = 0, chunk = 0, host_chunk = 0, cap = 0;
+  float ratio = 0.75f;
+  orbx_detector* det[2] = {nullptr, nullptr};
+  orbx_matcher* mat[2] = {nullptr, nullptr};
+  cudaStream_t st[2] = {nullptr, nullptr}, copy = nullptr, d2h = nullptr;
+  // device-resident results of one pass (row t of knn / good / n_good describes the pair (t-1, t))
+  uint8_t* frames = nullptr;  // [T][h][w] staging of run_host, tightly packed
+  orbx_keypoint* kps = nullptr;
+  uint8_t* desc = nullptr;
+  int* n = nullptr;
+  orbx_dmatch* knn = nullptr;
+  int* n_per_q = nullptr;
+  orbx_dmatch* good = nullptr;
+  int* n_good = nullptr;
+  std::vector<cudaEvent_t> events;  // pool, reused by every pass
+  size_t next_event = 0;
+};
+
+namespace {
+
+using orbx::set_error;
+
+int take_event(orbx_sequence* s, cudaEvent_t* e) {
+  if (s->next_event == s->events.size()) {
+    cudaEvent_t ev;
+    ORBX_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    s->events.push_back(ev);
+  }
+  *e = s->events[s->next_event++];
+  return ORBX_OK;
+}
+
+// `waiter` continues after everything queued on `on` so far
+int wait_stream(orbx_sequence* s, cudaStream_t waiter, cudaStream_t on) {
+  cudaEvent_t e;
+  if (int rc = take_event(s, &e)) return rc;
+  ORBX_CUDA(cudaEventRecord(e, on));
+  ORBX_CUDA(cudaStreamWaitEvent(waiter, e, 0));
+  return ORBX_OK;
+}
+
+// a pass starts after everything the previous pass queued on any of the four streams
+int join_all(orbx_sequence* s) {
+  s->next_event = 0;
+  cudaStream_t all[4] = {s->st[0], s->st[1], s->copy, s->d2h};
+  cudaEvent_t e[4];
+  for (int i = 0; i < 4; ++i) {
+    if (int rc = take_event(s, &e[i])) return rc;
+    ORBX_CUDA(cudaEventRecord(e[i], all[i]));
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j)
+      if (i != j) ORBX_CUDA(cudaStreamWaitEvent(all[i], e[j], 0));
+  return ORBX_OK;
+}
+
+// frames a..b-1 through detector `k` in launch sets of at most `step` frames
+int extract(orbx_sequence* s, int k, const uint8_t* frames, size_t pitch, size_t stride, int a, int b, int step) {
+  for (int f = a; f < b; f += step) {
+    const int nb = std::min(step, b - f);
+    const int rc = orbx_detect_and_compute_batch(s->det[k], frames + (size_t)f * stride, s->w, s->h, pitch, stride, nb,
+                                                 s->kps + (size_t)f * s->cap, s->desc + (size_t)f * s->cap * 32, s->cap,
+                                                 s->n + f);
+    if (rc) return rc;
+  }
+  return ORBX_OK;
+}
+
+// pairs (t-1, t) for t in [max(a, 1), b): BFMatcher k=2 (+ cross-check) and Lowe's ratio test, batched
+int match(orbx_sequence* s, int k, int a, int b) {
+  a = std::max(a, 1);
+  if (b <= a) return ORBX_OK;
+  const int npairs = b - a;
+  const size_t cap = (size_t)s->cap, stride = cap * 32;
+  int rc = orbx_knn_match2_batch(s->mat[k], s->desc + (size_t)(a - 1) * stride, stride, s->n + (a - 1),
+                                 s->desc + (size_t)a * stride, stride, s->n + a, npairs, s->cap, s->knn + (size_t)a * cap * 2,
+                                 s->n_per_q + (size_t)a * cap);
+  if (rc) return rc;
+  return orbx_ratio_test_batch(s->mat[k], s->knn + (size_t)a * cap * 2, s->n_per_q + (size_t)a * cap, s->n + (a - 1), npairs,
+                               s->cap, s->ratio, s->good + (size_t)a * cap, s->n_good + a);
+}
+
+template <typename T>
+int dev_alloc(T** p, size_t count) {
+  cudaError_t e = cudaMalloc((void**)p, count * sizeof(T));
+  if (e != cudaSuccess) {
+    set_error("cudaMalloc(%zu) failed: %s", count * sizeof(T), cudaGetErrorString(e));
+    return ORBX_E_NOMEM;
+  }
+  e = cudaMemset(*p, 0, count * sizeof(T));
+  if (e != cudaSuccess) {
+    set_error("cudaMemset failed: %s", cudaGetErrorString(e));
+    return ORBX_E_CUDA;
+  }
+  return ORBX_OK;
+}
+
+// The chunk schedule of run_host (measured in frontend.py): three short, doubling first chunks so that compute starts
+// early, full chunks in the middle, a short last chunk so that little is left to copy back after the last kernel.
+std::vector<std::pair<int, int>> chunk_schedule(int T, int c) {
+  std::vector<std::pair<int, int>> bounds;
+  int a = 0;
+  const int first[3] = {std::max(c / 8, 1), std::max(c / 4, 1), std::max(c / 2, 1)};
+  for (int size : first)
+    if (T - a > c) {
+      bounds.push_back({a, a + size});
+      a += size;
+    }
+  while (T - a > c + c / 2) {
+    bounds.push_back({a, a + c});
+    a += c;
+  }
+  if (T - a > c) {
+    bounds.push_back({a, T - c / 2});
+    a = T - c / 2;
+  }
+  bounds.push_back({a, T});
+  return bounds;
+}
+
+}  // namespace
+
+extern "C" {
+
+void orbx_sequence_destroy(orbx_sequence* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  cudaDeviceSynchronize();
+  for (int k = 0; k < 2; ++k) {
+    if (s->det[k]) orbx_detector_destroy(s->det[k]);
+    if (s->mat[k]) orbx_matcher_destroy(s->mat[k]);
+    if (s->st[k]) cudaStreamDestroy(s->st[k]);
+  }
+  if (s->copy) cudaStreamDestroy(s->copy);
+  if (s->d2h) cudaStreamDestroy(s->d2h);
+  for (cudaEvent_t e : s->events) cudaEventDestroy(e);
+  cudaFree(s->frames);
+  cudaFree(s->kps);
+  cudaFree(s->desc);
+  cudaFree(s->n);
+  cudaFree(s->knn);
+  cudaFree(s->n_per_q);
+  cudaFree(s->good);
+  cudaFree(s->n_good);
+  delete s;
+}
+
+int orbx_sequence_create(int device, int width, int height, int nfeatures, int max_frames, int chunk, int host_chunk,
+                         float ratio, int cross_check, orbx_sequence** out) {
+  if (!out || width < 16 || height < 16 || nfeatures < 1 || max_frames < 1 || chunk < 1 || host_chunk < 1) {
+    set_error("orbx_sequence_create: bad argument");
+    return ORBX_E_BADARG;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    set_error("orbx_sequence_create: no CUDA device %d (there is no CPU fallback)", device);
+    return ORBX_E_CUDA;
+  }
+  ORBX_CUDA(cudaSetDevice(device));
+  auto* s = new orbx_sequence();
+  s->device = device, s->w = width, s->h = height, s->nfeatures = nfeatures, s->max_frames = max_frames;
+  s->chunk = std::min(chunk, max_frames);
+  s->host_chunk = std::min(host_chunk, s->chunk);
+  s->ratio = ratio;
+  // OpenCV keeps ties at the selection threshold, so a frame can return a little more than nfeatures (orbx.h)
+  s->cap = (nfeatures + nfeatures / 8 + 64 + 31) / 32 * 32;
+  orbx_params p;
+  orbx_default_params(&p);
+  p.nfeatures = nfeatures;
+  int rc = ORBX_OK;
+  for (int k = 0; k < 2 && !rc; ++k) {
+    if (cudaStreamCreateWithFlags(&s->st[k], cudaStreamNonBlocking) != cudaSuccess) rc = ORBX_E_CUDA;
+    // handle 0 also serves run_device, whose launch sets are `chunk` frames
+    if (!rc) rc = orbx_detector_create(&p, device, width, height, k == 0 ? s->chunk : s->host_chunk, &s->det[k]);
+    if (!rc) rc = orbx_matcher_create(device, cross_check, &s->mat[k]);
+    if (!rc) rc = orbx_detector_set_stream(s->det[k], s->st[k]);
+    if (!rc) rc = orbx_matcher_set_stream(s->mat[k], s->st[k]);
+  }
+  if (!rc && cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking) != cudaSuccess) rc = ORBX_E_CUDA;
+  if (!rc && cudaStreamCreateWithFlags(&s->d2h, cudaStreamNonBlocking) != cudaSuccess) rc = ORBX_E_CUDA;
+  const size_t T = (size_t)max_frames, cap = (size_t)s->cap;
+  if (!rc) rc = dev_alloc(&s->frames, T * height * width);
+  if (!rc) rc = dev_alloc(&s->kps, T * cap);
+  if (!rc) rc = dev_alloc(&s->desc, T * cap * 32);
+  if (!rc) rc = dev_alloc(&s->n, T);
+  if (!rc) rc = dev_alloc(&s->knn, T * cap * 2);
+  if (!rc) rc = dev_alloc(&s->n_per_q, T * cap);
+  if (!rc) rc = dev_alloc(&s->good, T * cap);
+  if (!rc) rc = dev_alloc(&s->n_good, T);
+  if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = ORBX_E_CUDA;  // the memsets ran on the legacy stream
+  if (rc) {
+    if (rc == ORBX_E_CUDA) set_error("orbx_sequence_create: CUDA error %s", cudaGetErrorString(cudaGetLastError()));
+    orbx_sequence_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return ORBX_OK;
+}
+
+int orbx_sequence_capacity(const orbx_sequence* s) { return s ? s->cap : 0; }
+
+int orbx_sequence_sync(orbx_sequence* s) {
+  if (!s) {
+    set_error("orbx_sequence_sync: null handle");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(s->device));
+  ORBX_CUDA(cudaStreamSynchronize(s->copy));
+  ORBX_CUDA(cudaStreamSynchronize(s->st[0]));
+  ORBX_CUDA(cudaStreamSynchronize(s->st[1]));
+  ORBX_CUDA(cudaStreamSynchronize(s->d2h));
+  return ORBX_OK;
+}
+
+int orbx_sequence_results(orbx_sequence* s, orbx_keypoint** kps, uint8_t** desc, int** n, orbx_dmatch** good,
+                          int** n_good) {
+  if (!s) {
+    set_error("orbx_sequence_results: null handle");
+    return ORBX_E_BADARG;
+  }
+  if (kps) *kps = s->kps;
+  if (desc) *desc = s->desc;
+  if (n) *n = s->n;
+  if (good) *good = s->good;
+  if (n_good) *n_good = s->n_good;
+  return ORBX_OK;
+}
+
+int orbx_sequence_run_device(orbx_sequence* s, const uint8_t* frames_dev, size_t pitch, size_t frame_stride, int T) {
+  if (!s || !frames_dev || T < 1 || T > s->max_frames || pitch < (size_t)s->w || frame_stride < pitch * s->h) {
+    set_error("orbx_sequence_run_device: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (!orbx::is_device_ptr(frames_dev)) {
+    set_error("orbx_sequence_run_device: frames must be device memory (orbx_sequence_run_host takes host frames)");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(s->device));
+  if (int rc = join_all(s)) return rc;
+  for (int a = 0; a < T; a += s->chunk) {
+    const int b = std::min(a + s->chunk, T);
+    if (int rc = extract(s, 0, frames_dev, pitch, frame_stride, a, b, s->chunk)) return rc;
+    if (int rc = match(s, 0, a, b)) return rc;
+  }
+  return ORBX_OK;
+}
+
+int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_keypoint* kps, uint8_t* desc, int* n,
+                           orbx_dmatch* good, int* n_good) {
+  if (!s || !frames || T < 1 || T > s->max_frames) {
+    set_error("orbx_sequence_run_host: bad argument");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(s->device));
+  if (int rc = join_all(s)) return rc;
+  const size_t fb = (size_t)s->h * s->w, cap = (size_t)s->cap;
+  const auto bounds = chunk_schedule(T, s->host_chunk);
+  std::vector<cudaEvent_t> uploaded(bounds.size());
+  for (size_t i = 0; i < bounds.size(); ++i) {
+    const int a = bounds[i].first, b = bounds[i].second;
+    ORBX_CUDA(cudaMemcpyAsync(s->frames + a * fb, frames + a * fb, (size_t)(b - a) * fb, cudaMemcpyHostToDevice, s->copy));
+    if (int rc = take_event(s, &uploaded[i])) return rc;
+    ORBX_CUDA(cudaEventRecord(uploaded[i], s->copy));
+  }
+  cudaEvent_t prev_extracted = nullptr;
+  for (size_t i = 0; i < bounds.size(); ++i) {
+    const int a = bounds[i].first, b = bounds[i].second, k = (int)(i & 1);
+    cudaStream_t st = s->st[k];
+    ORBX_CUDA(cudaStreamWaitEvent(st, uploaded[i], 0));
+    if (int rc = extract(s, k, s->frames, (size_t)s->w, fb, a, b, s->host_chunk)) return rc;
+    cudaEvent_t extracted;
+    if (int rc = take_event(s, &extracted)) return rc;
+    ORBX_CUDA(cudaEventRecord(extracted, st));
+    // keypoints and descriptors of this chunk go back while it is being matched ...
+    ORBX_CUDA(cudaStreamWaitEvent(s->d2h, extracted, 0));
+    if (n) ORBX_CUDA(cudaMemcpyAsync(n + a, s->n + a, (size_t)(b - a) * sizeof(int), cudaMemcpyDeviceToHost, s->d2h));
+    if (kps)
+      ORBX_CUDA(cudaMemcpyAsync(kps + a * cap, s->kps + a * cap, (size_t)(b - a) * cap * sizeof(orbx_keypoint),
+                                cudaMemcpyDeviceToHost, s->d2h));
+    if (desc)
+      ORBX_CUDA(cudaMemcpyAsync(desc + a * cap * 32, s->desc + a * cap * 32, (size_t)(b - a) * cap * 32,
+                                cudaMemcpyDeviceToHost, s->d2h));
+    // descriptors of frame a-1 come from the other stream
+    if (prev_extracted) ORBX_CUDA(cudaStreamWaitEvent(st, prev_extracted, 0));
+    prev_extracted = extracted;
+    if (int rc = match(s, k, a, b)) return rc;
+    // ... and its matches while the next chunk computes
+    if (int rc = wait_stream(s, s->d2h, st)) return rc;
+    if (good)
+      ORBX_CUDA(cudaMemcpyAsync(good + a * cap, s->good + a * cap, (size_t)(b - a) * cap * sizeof(orbx_dmatch),
+                                cudaMemcpyDeviceToHost, s->d2h));
+    if (n_good)
+      ORBX_CUDA(cudaMemcpyAsync(n_good + a, s->n_good + a, (size_t)(b - a) * sizeof(int), cudaMemcpyDeviceToHost, s->d2h));
+  }
+  return ORBX_OK;
+}
+
+}  // extern "C"

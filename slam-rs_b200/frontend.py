@@ -342,3 +342,76 @@ class SequenceFrontEnd:
         nq = min(int(self.n[t - 1].item()), self.cap)
         k = self.knn[t, :nq].cpu().numpy().view(DMATCH_DTYPE).reshape(nq, 2)
         return k, self.n_per_q[t, :nq].cpu().numpy()
+
+
+class NativeSequence:
+    """The same pipeline scheduled by liborbx itself (csrc/sequence.cu, ``orbx_sequence_*``): what a compiled-language
+    host (include/orbx.hpp, rust/orbx) calls.  Frames and results are numpy / torch CPU arrays (pinned for overlap) or
+    CUDA tensors; no torch stream is involved - the library owns its four streams."""
+
+    def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=1000, host_chunk=167, device=0, ratio=0.75,
+                 cross_check=True):
+        import ctypes as C
+        from ._ffi import lib, check
+        self._lib, self._check, self._C = lib, check, C
+        self._h = C.c_void_p()
+        self.w, self.h, self.max_frames = int(width), int(height), int(max_frames)
+        check(lib.orbx_sequence_create(int(device), self.w, self.h, int(nfeatures), self.max_frames, int(chunk),
+                                       int(host_chunk), float(ratio), 1 if cross_check else 0, C.byref(self._h)))
+        self.cap = int(lib.orbx_sequence_capacity(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.orbx_sequence_destroy(self._h)
+            self._h = self._C.c_void_p()
+
+    __del__ = close
+
+    def alloc_host_outputs(self):
+        T, cap = self.max_frames, self.cap
+        pin = dict(pin_memory=True)
+        return {"n": torch.zeros((T,), dtype=torch.int32, **pin),
+                "kps": torch.zeros((T, cap, 28), dtype=torch.uint8, **pin),
+                "desc": torch.zeros((T, cap, 32), dtype=torch.uint8, **pin),
+                "good": torch.zeros((T, cap, 16), dtype=torch.uint8, **pin),
+                "n_good": torch.zeros((T,), dtype=torch.int32, **pin)}
+
+    def run_host(self, frames, out):
+        """frames: uint8 CPU tensor [T, h, w] (contiguous; pinned for overlap); out: alloc_host_outputs().  Asynchronous."""
+        assert frames.dtype == torch.uint8 and frames.is_contiguous() and tuple(frames.shape[1:]) == (self.h, self.w)
+        vp = self._C.c_void_p
+        self._check(self._lib.orbx_sequence_run_host(self._h, vp(frames.data_ptr()), int(frames.shape[0]),
+                                                     vp(out["kps"].data_ptr()), vp(out["desc"].data_ptr()),
+                                                     vp(out["n"].data_ptr()), vp(out["good"].data_ptr()),
+                                                     vp(out["n_good"].data_ptr())))
+        return int(frames.shape[0])
+
+    def run_device(self, frames_dev):
+        """frames_dev: uint8 CUDA tensor [T, h, pitch >= w]; results stay on the device (``results()``).  Asynchronous."""
+        assert frames_dev.is_cuda and frames_dev.dtype == torch.uint8 and frames_dev.stride(2) == 1
+        self._check(self._lib.orbx_sequence_run_device(self._h, self._C.c_void_p(frames_dev.data_ptr()),
+                                                       int(frames_dev.stride(1)), int(frames_dev.stride(0)),
+                                                       int(frames_dev.shape[0])))
+        return int(frames_dev.shape[0])
+
+    def sync(self):
+        self._check(self._lib.orbx_sequence_sync(self._h))
+
+    def results_to_host(self, T):
+        """Device results of the last pass copied to numpy (synchronises): dict like alloc_host_outputs()."""
+        C = self._C
+        ptrs = [C.c_void_p() for _ in range(5)]
+        self._check(self._lib.orbx_sequence_results(self._h, *[C.byref(p) for p in ptrs]))
+        self.sync()
+        from cuda.bindings import runtime as rt  # cuda-python, for a plain cudaMemcpy of raw device pointers
+        cap = self.cap
+        shapes = {"kps": ((T, cap, 28), np.uint8), "desc": ((T, cap, 32), np.uint8), "n": ((T,), np.int32),
+                  "good": ((T, cap, 16), np.uint8), "n_good": ((T,), np.int32)}
+        out = {}
+        for (key, (shape, dt)), p in zip(shapes.items(), ptrs):
+            a = np.zeros(shape, dt)
+            err, = rt.cudaMemcpy(a.ctypes.data, p.value, a.nbytes, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+            if int(err) != 0:
+                raise RuntimeError("cudaMemcpy failed: %s" % err)
+            out[key] = a
+        return out

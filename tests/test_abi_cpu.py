@@ -57,6 +57,10 @@ def test_no_cpu_fallback():
         with pytest.raises(s.OrbxError) as e:
             make()
         assert e.value.code == -3
+    from slam_rs_b200.frontend import NativeSequence
+    with pytest.raises(s.OrbxError) as e:
+        NativeSequence(640, 480, max_frames=4)
+    assert e.value.code == -3
     h = ctypes.c_void_p()                      # (the PoseEstimator mirror creates a FeatureMatcher first: go to the ABI)
     assert s.lib.orbx_pose_estimator_create(0, 64, 1, cam.fx, cam.fy, cam.cx, cam.cy, ctypes.byref(h)) == -3
     assert b"no CPU fallback" in s.lib.orbx_last_error()
