@@ -2,17 +2,11 @@
 (slam-rs_b200/frontend.py::SequenceFrontEnd, itself checked against the per-frame API and the oracle in
 tests/test_gpu_matcher.py): same kernels, same launch sets, so every output must be identical bit for bit.
 
-NOT YET RUN ON A GPU: written after round 1's GPU budget was spent.  The test is therefore opt-in
-(ORBX_TEST_UNVALIDATED=1) until it has passed once on a B200; DESIGN.md §6 lists it as the first item of the next round.
 """
-import os
-
 import numpy as np
 import pytest
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("ORBX_TEST_UNVALIDATED") != "1",
-                                 reason="native sequence entry not yet validated on a GPU (set ORBX_TEST_UNVALIDATED=1)")]
+pytestmark = pytest.mark.gpu
 
 
 def _valid_rows_equal(a, b, counts, what):
