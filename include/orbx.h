@@ -98,6 +98,8 @@ int orbx_detect_and_compute_batch(orbx_detector* d, const uint8_t* imgs, int w, 
 int orbx_detect_and_compute_batch_bgr(orbx_detector* d, const uint8_t* imgs, int w, int h, size_t pitch,
                                       size_t frame_stride, int batch, orbx_keypoint* kps, uint8_t* desc,
                                       int cap_per_frame, int* n_per_frame);
+/* waits for the handle's stream; returns ORBX_E_CAPACITY (once) if an asynchronous call since the last sync had to
+ * truncate a frame to cap rows (n is clamped to cap on that path) or exhausted the tie arena */
 int orbx_detector_sync(orbx_detector* d);
 /* run on a caller-owned CUDA stream (cudaStream_t as void*); NULL restores the handle's own stream */
 int orbx_detector_set_stream(orbx_detector* d, void* stream);
@@ -298,15 +300,22 @@ int orbx_transform_points_to_world(orbx_triangulator* t, const double* R, const 
 /* ------------------------------------------------------------------ sequence front end
  * The per-frame loop of examples/visual_odometry.rs:84-218 (detect_and_compute :102, match_descriptors :106, match
  * filter :107) over a whole sequence, scheduled natively (csrc/sequence.cu): frames -> T x (keypoints, descriptors) ->
- * T-1 frame-to-frame problems, BFMatcher k=2 (+ cross-check) + Lowe ratio.  Row capacity per frame is
- * orbx_sequence_capacity() (>= nfeatures: OpenCV keeps ties).  Result row t of `good` / `n_good` describes the pair
- * (t-1, t); row 0 is unused.  All run calls are asynchronous: orbx_sequence_sync() before reading results. */
+ * T-1 frame-to-frame problems, BFMatcher k=2 (+ cross-check) + Lowe ratio (north_star stage 5) or, after
+ * orbx_sequence_set_reference_filter(), the reference's own k=1 + filter_good_matches.  Row capacity per frame is
+ * orbx_sequence_capacity() (>= nfeatures: OpenCV keeps ties; a frame with more keypoints than that - a tie flood -
+ * is truncated to the capacity and orbx_sequence_sync() returns ORBX_E_CAPACITY).  Result row t of `good` / `n_good`
+ * describes the pair (t-1, t); row 0 is unused.  All run calls are asynchronous: orbx_sequence_sync() before reading
+ * results. */
 typedef struct orbx_sequence orbx_sequence;
 /* chunk: frames per launch set of orbx_sequence_run_device; host_chunk: pipeline granularity of orbx_sequence_run_host */
 int orbx_sequence_create(int device, int width, int height, int nfeatures, int max_frames, int chunk, int host_chunk,
                          float ratio, int cross_check, orbx_sequence** out);
 void orbx_sequence_destroy(orbx_sequence* s);
 int orbx_sequence_capacity(const orbx_sequence* s);
+/* enable=1: the pairs are matched exactly as the reference's loop does - match_descriptors (k=1, no cross-check,
+ * visual_odometry.rs:106) then filter_good_matches(matches, ratio) (:107, ratio 2.0 there) - instead of the
+ * north_star's k=2 + cross-check + Lowe composition; `good` / `n_good` then hold that filter's survivors. */
+int orbx_sequence_set_reference_filter(orbx_sequence* s, int enable, float ratio);
 /* device-resident frames (8UC1, `pitch` bytes per row, frame t at frames_dev + t*frame_stride); results stay in HBM */
 int orbx_sequence_run_device(orbx_sequence* s, const uint8_t* frames_dev, size_t pitch, size_t frame_stride, int T);
 /* HOST frames, tightly packed [T][height][width] (pinned memory for copy / compute overlap), results to host arrays
@@ -318,6 +327,40 @@ int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_
 int orbx_sequence_results(orbx_sequence* s, orbx_keypoint** kps, uint8_t** desc, int** n, orbx_dmatch** good,
                           int** n_good);
 int orbx_sequence_sync(orbx_sequence* s);
+/* Device-side timing of whole passes: with enable=1, CUDA events bracket everything the run calls queue on the handle's
+ * four streams.  orbx_sequence_elapsed() waits for the last pass and returns the milliseconds from the start of the
+ * first pass since the last reset to the end of the last one (consecutive passes run back to back: each pass starts
+ * after everything the previous one queued), and how many passes that covers. */
+int orbx_sequence_set_timing(orbx_sequence* s, int enable);
+int orbx_sequence_elapsed(orbx_sequence* s, float* ms, int* passes, int reset);
+
+/* ------------------------------------------------------------------ multi-GPU: query-sharded map-to-frame matching
+ * (BASELINE configs[3]; the call it serves is match_descriptors at src/mapping/map.rs:107 over a map
+ * too large for one GPU's time budget).  One process drives `ndev` GPUs of one box: the train set is resident on every
+ * GPU (orbx_comm_set_train: one ncclBroadcast over NVLink per map update), the query rows are cut into contiguous
+ * slices, and every GPU's kernel stores its DMatch records straight into device `devices[0]`'s result buffer through
+ * peer-mapped pointers - there is no gather collective.  Results are identical to orbx_match / orbx_knn_match2 on one
+ * GPU (query_idx is the global row).  Listing the same device more than once makes "virtual ranks" on one GPU (no NCCL;
+ * for tests). */
+typedef struct orbx_comm orbx_comm;
+/* devices: ndev CUDA device indices (NULL = 0..ndev-1); needs peer access from every device to devices[0] */
+int orbx_comm_create(const int* devices, int ndev, orbx_comm** out);
+void orbx_comm_destroy(orbx_comm* c);
+int orbx_comm_size(const orbx_comm* c);
+/* train: nt x 32 bytes, host memory or device memory of devices[0]; copied, so the caller may reuse it after
+ * orbx_comm_sync().  Asynchronous. */
+int orbx_comm_set_train(orbx_comm* c, const uint8_t* train, int nt);
+/* BFMatcher.knnMatch(k=2) of nq query rows (host memory or device memory of devices[0]) against the resident train
+ * set: out nq x 2, n_per_q nq (host, or device memory of devices[0]).  Host outputs: returns when they are ready;
+ * device outputs: asynchronous on the handle's streams (orbx_comm_sync). */
+int orbx_comm_knn_match2(orbx_comm* c, const uint8_t* q, int nq, orbx_dmatch* out, int* n_per_q);
+/* k = 1 (match_descriptors, matcher.rs:24-37): out nq, *n = nq (0 when either side is empty) */
+int orbx_comm_match(orbx_comm* c, const uint8_t* q, int nq, orbx_dmatch* out, int* n);
+int orbx_comm_sync(orbx_comm* c);
+/* device time of the calls (CUDA events on devices[0]'s stream, from "queries staged" to "every rank's records have
+ * landed"); with timing on, every call synchronises.  kernel_ms_rank0: accumulated Hamming-kernel time of rank 0. */
+int orbx_comm_set_timing(orbx_comm* c, int enable);
+int orbx_comm_timing(orbx_comm* c, float* ms, int* calls, float* kernel_ms_rank0, int reset);
 
 /* ------------------------------------------------------------------ misc */
 const char* orbx_last_error(void);

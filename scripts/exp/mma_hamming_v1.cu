@@ -1,0 +1,553 @@
+// Experiment: brute-force Hamming k=2 + reverse best-1 as an exact integer contraction on the
+// 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM), measured against the POPC kernel.
+//
+//   d(q, t) = popcount(q ^ t) over 256 bits.  With bits encoded as +-a (query) and +-b (train):
+//   sum_k A[q][k] * B[t][k] = a*b*(256 - 2 d).   a = 8, b = 16  ->  256 * (128 - d)
+//   One more K-slice of 32 int8 carries the column index and a validity flag, so the accumulator IS the packed
+//   search key:   acc = 256 * (128 - d) + (255 - (t mod 256))      (max acc <=> min d, ties -> lowest t)
+//   invalid train rows (t >= nt) get -260096 from the flag bytes and never win.
+//
+// Build:  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o mma_hamming mma_hamming.cu
+// Run:    ./mma_hamming [npairs] [rows]      (self-checks against a CPU loop, then times)
+#include <cuda_runtime.h>
+#include <limits.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#define CK(x)                                                                              \
+  do {                                                                                     \
+    cudaError_t e_ = (x);                                                                  \
+    if (e_ != cudaSuccess) {                                                               \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__);      \
+      exit(1);                                                                             \
+    }                                                                                      \
+  } while (0)
+
+constexpr int kKBytes = 288;                 // 256 data + 32 aux int8 per row
+constexpr int kChunks = kKBytes / 16;        // 18 chunks of 16 bytes
+constexpr int kGroupBytes = kChunks * 128;   // 8 rows x 288 bytes, core-matrix major: [chunk][row & 7][16]
+constexpr int kTileM = 128, kTileN = 256;
+constexpr int kABytes = kTileM / 8 * kGroupBytes;  // 36864
+constexpr int kBBytes = kTileN / 8 * kGroupBytes;  // 73728
+constexpr int kStages = 2;
+constexpr int kSmemBytes = kABytes + kStages * kBBytes + 4 * 256 * 4 * 2 + 2048;  // + s_col[2 groups][4][256] + barriers
+constexpr int kThreads = 320;                // warp 0 producer, warp 1 MMA, warps 2-9 epilogue (two groups of four)
+constexpr int kInvalid = -40000;             // anything below is "no valid column"
+
+// ------------------------------------------------------------------------------------------------ expansion
+// E layout per descriptor set: 8-row groups of kGroupBytes; row r, K-byte k at (r / 8) * kGroupBytes + (k / 16) * 128 +
+// (r & 7) * 16 + (k & 15) - the canonical K-major no-swizzle UMMA layout (core matrix = 8 rows x 16 bytes), so a tile
+// of any 8-aligned row range is one contiguous block: loaded with one cp.async.bulk, no tensor map.
+// side 0 = query (A: +-8, aux = 16 x 1, 16 x 127), side 1 = train (B: +-16, aux = index bytes, 16 x flag).
+__global__ void expand_kernel(const uint8_t* __restrict__ desc, size_t desc_stride, const int* __restrict__ n_dev,
+                              int rows_padded, uint8_t* __restrict__ out, size_t out_stride, int side) {
+  const int set = blockIdx.y;
+  const int n = n_dev[set];
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;  // (row, chunk)
+  if (idx >= rows_padded * kChunks) return;
+  const int row = idx / kChunks, c = idx - row * kChunks;
+  uint4 o;
+  if (c < 16) {
+    unsigned bits = 0;
+    if (row < n) bits = *reinterpret_cast<const unsigned short*>(desc + set * desc_stride + (size_t)row * 32 + 2 * c);
+    const unsigned lo = side ? 0xF0F0F0F0u : 0xF8F8F8F8u;  // -16 / -8
+    const unsigned fl = side ? 0xE0u : 0xF0u;              // (-v) ^ (+v)
+    unsigned w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const unsigned nib = (bits >> (4 * i)) & 0xFu;
+      const unsigned x = (nib * 0x00204081u) & 0x01010101u;  // bit j -> byte j
+      w[i] = lo ^ (x * fl);
+    }
+    o = make_uint4(w[0], w[1], w[2], w[3]);
+    if (row >= n) o = make_uint4(0, 0, 0, 0);
+  } else if (side == 0) {
+    o = c == 16 ? make_uint4(0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u)
+                : make_uint4(0x7F7F7F7Fu, 0x7F7F7F7Fu, 0x7F7F7F7Fu, 0x7F7F7F7Fu);
+  } else if (c == 16) {
+    const int v = 255 - (row & 255);
+    const int b0 = min(v, 127), b1 = min(v - b0, 127), b2 = v - b0 - b1;
+    o = make_uint4((unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16), 0, 0, 0);
+  } else {
+    const unsigned f = row < n ? 0u : 0x80808080u;  // -128 x 16 on invalid rows
+    o = make_uint4(f, f, f, f);
+  }
+  uint8_t* dst = out + set * out_stride + (size_t)(row >> 3) * kGroupBytes + c * 128 + (row & 7) * 16;
+  *reinterpret_cast<uint4*>(dst) = o;
+}
+
+// ------------------------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ int g_lbo = 128, g_sbo = kGroupBytes;
+__device__ __forceinline__ uint64_t make_desc_rt(uint32_t saddr, int lbo, int sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+  // K-major, SWIZZLE_NONE: LBO = 128 B (next 16-byte K chunk), SBO = kGroupBytes (next 8-row group), version 1 (sm_100)
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((128 >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((kGroupBytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// kind::i8: D s32 (c_format 2), A / B signed int8 (format 1), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, int* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+
+struct MmaArgs {
+  const uint8_t* ea;  // expanded query sets  [problem][rows_padded / 8][kGroupBytes]
+  const uint8_t* eb;  // expanded train sets
+  size_t ea_stride, eb_stride;
+  const int* nq_dev;
+  const int* nt_dev;
+  int max_rows, npairs, mtiles;
+  unsigned* best;               // [problem][max_rows][2] packed min-order keys (dist << 16 | train), ~0 = none
+  unsigned long long* rev;      // [problem][max_rows] reverse best-1 (dist << 32 | query), preset ~0; may be null
+  int* dump;                    // diagnostic: raw accumulators of the first tile of unit 0 [128][256]
+  int lbo, sbo, kstep, nk;      // diagnostic: descriptor strides, start-address step per MMA, MMAs per tile
+};
+
+// One CTA per SM, persistent over work units (problem, 128-query tile).  Per unit the A tile is loaded once and the
+// train set streams through a two-stage B ring; accumulators alternate between two 256-column TMEM buffers, buffer b
+// is drained by epilogue group b while the MMA of the next tile runs.
+__global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kABytes;
+  int* s_col = reinterpret_cast<int*>(smem + kABytes + kStages * kBBytes);  // [2][4][256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_col + 2 * 4 * 256);
+  uint64_t* a_full = bars + 0;
+  uint64_t* a_empty = bars + 1;
+  uint64_t* b_full = bars + 2;   // [2]
+  uint64_t* b_empty = bars + 4;  // [2]
+  uint64_t* t_full = bars + 6;   // [2]
+  uint64_t* t_empty = bars + 8;  // [2]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 10);
+  unsigned* s_merge = reinterpret_cast<unsigned*>(bars + 12);  // [128][2] group 1 -> group 0 at unit end (after barriers)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(b_full + i, 1);
+      mbar_init(b_empty + i, 1);
+      mbar_init(t_full + i, 1);
+      mbar_init(t_empty + i, 4);  // one arrival per epilogue warp of the group
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+
+  const int nunits = a.npairs * a.mtiles;
+  if (warp == 0) {
+    // ===== producer: bulk copies global -> shared, completion on the full barriers
+    if (lane == 0) {
+      uint32_t ua = 0, ub = 0;  // units / B tiles issued so far
+      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int p = u / a.mtiles, mt = u - p * a.mtiles;
+        const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+        if (mt * kTileM >= nq || nt <= 0) continue;
+        mbar_wait(a_empty, (ua & 1) ^ 1);
+        mbar_expect_tx(a_full, kABytes);
+        bulk_g2s(sA, a.ea + p * a.ea_stride + (size_t)mt * kABytes, kABytes, a_full);
+        ++ua;
+        const int ntiles = (nt + kTileN - 1) / kTileN;
+        for (int n = 0; n < ntiles; ++n, ++ub) {
+          const int s = ub & 1;
+          mbar_wait(b_empty + s, ((ub >> 1) & 1) ^ 1);
+          mbar_expect_tx(b_full + s, kBBytes);
+          bulk_g2s(sB + s * kBBytes, a.eb + p * a.eb_stride + (size_t)n * kBBytes, kBBytes, b_full + s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one elected thread
+    if (lane == 0) {
+      uint32_t ua = 0, ub = 0;
+      uint32_t tcount[2] = {0, 0};  // tiles issued into each TMEM buffer
+      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int p = u / a.mtiles, mt = u - p * a.mtiles;
+        const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+        if (mt * kTileM >= nq || nt <= 0) continue;
+        mbar_wait(a_full, ua & 1);
+        ++ua;
+        const int ntiles = (nt + kTileN - 1) / kTileN;
+        for (int n = 0; n < ntiles; ++n, ++ub) {
+          const int s = ub & 1, buf = n & 1;
+          mbar_wait(t_empty + buf, (tcount[buf] & 1) ^ 1);
+          ++tcount[buf];
+          mbar_wait(b_full + s, (ub >> 1) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBBytes);
+#pragma unroll
+          for (int k = 0; k < kKBytes / 32; ++k)
+            if (a.dump) {
+              if (k < a.nk)
+                mma_i8(tmem + buf * kTileN, make_desc_rt(sa + k * a.kstep, a.lbo, a.sbo),
+                       make_desc_rt(sb + k * a.kstep, a.lbo, a.sbo), k > 0);
+            } else
+              mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256), k > 0);
+          mma_commit(b_empty + s);
+          mma_commit(t_full + buf);
+        }
+        mma_commit(a_empty);
+      }
+    }
+  } else {
+    // ===== epilogue: group g drains TMEM buffer g (tiles n with n & 1 == g)
+    const int g = (warp - 2) >> 2, q = warp & 3;  // TMEM lanes 32q .. 32q+31 belong to warps with warp % 4 == q
+    const int row = 32 * q + lane;                // row of the A tile
+    int* col = s_col + g * 4 * 256;
+    uint32_t tc = 0;  // tiles drained by this group
+    for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+      const int p = u / a.mtiles, mt = u - p * a.mtiles;
+      const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+      if (mt * kTileM >= nq || nt <= 0) continue;
+      const int qi = mt * kTileM + row;
+      const bool active = qi < nq;
+      const int rowbias = active ? 127 - row : -(1 << 30);
+      unsigned b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // running global best-2, min order (dist << 16 | train)
+      const int ntiles = (nt + kTileN - 1) / kTileN;
+      for (int n = g; n < ntiles; n += 2, ++tc) {
+        mbar_wait(t_full + g, tc & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        int m1 = INT_MIN, m2 = INT_MIN;
+        const uint32_t tbase = tmem + g * kTileN + ((uint32_t)(32 * q) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < kTileN; c0 += 32) {
+          int v[32];
+          tmem_ld32(tbase + c0, v);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+          if (a.dump && u == 0 && n == 0)
+            for (int j = 0; j < 32; ++j) a.dump[row * 256 + c0 + j] = v[j];
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const int x = v[j], y = v[j + 1];
+            const int hi = max(x, y), lo = min(x, y);
+            const int t = min(m1, hi);
+            m1 = max(m1, hi);
+            m2 = max3(m2, t, lo);
+            if (a.rev) {
+              const int rx = __reduce_max_sync(0xFFFFFFFFu, x * 128 + rowbias);
+              const int ry = __reduce_max_sync(0xFFFFFFFFu, y * 128 + rowbias);
+              if (lane == 0) {
+                col[q * 256 + c0 + j] = rx;
+                col[q * 256 + c0 + j + 1] = ry;
+              }
+            }
+          }
+        }
+        // TMEM buffer g is free for the MMA of tile n + 2
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(t_empty + g);
+        // tile-local keys -> global min-order keys
+        const int n0 = n * kTileN;
+        if (m1 > kInvalid) {
+          const unsigned k1 = ((unsigned)(128 - (m1 >> 8)) << 16) | (unsigned)(n0 + 255 - (m1 & 255));
+          unsigned hi = max(b1, k1);
+          b1 = min(b1, k1);
+          b2 = min(b2, hi);
+        }
+        if (m2 > kInvalid) {
+          const unsigned k2 = ((unsigned)(128 - (m2 >> 8)) << 16) | (unsigned)(n0 + 255 - (m2 & 255));
+          unsigned hi = max(b1, k2);
+          b1 = min(b1, k2);
+          b2 = min(b2, hi);
+        }
+        if (a.rev) {
+          // column maxima of the 128 rows: four quarter results per column -> one RED.MIN per (unit, column)
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+          const int t128 = (warp - 2 - 4 * g) * 32 + lane;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int c = t128 + 128 * h;
+            const int m = max(max(col[c], col[256 + c]), max(col[512 + c], col[768 + c]));
+            if (n0 + c < nt && m > kInvalid * 128) {
+              const unsigned d = (unsigned)(128 - (m >> 15));
+              const unsigned r = (unsigned)(127 - (m & 127));
+              atomicMin(a.rev + (size_t)p * a.max_rows + n0 + c,
+                        ((unsigned long long)d << 32) | (unsigned long long)(mt * kTileM + r));
+            }
+          }
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+        }
+      }
+      // merge the two groups' running best-2 (group 1 -> shared -> group 0), then write
+      if (g == 1) {
+        s_merge[2 * row] = b1;
+        s_merge[2 * row + 1] = b2;
+      }
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+      if (g == 0) {
+        const unsigned o1 = s_merge[2 * row], o2 = s_merge[2 * row + 1];
+        unsigned hi = max(b1, o1);
+        b1 = min(b1, o1);
+        b2 = min(min(b2, o2), hi);
+        if (active) {
+          unsigned* o = a.best + ((size_t)p * a.max_rows + qi) * 2;
+          o[0] = b1;
+          o[1] = b2;
+        }
+      }
+      asm volatile("bar.sync 3, 256;" ::: "memory");
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+// ------------------------------------------------------------------------------------------------ host
+static unsigned popc256(const uint8_t* a, const uint8_t* b) {
+  unsigned d = 0;
+  for (int i = 0; i < 32; ++i) d += __builtin_popcount((unsigned)(a[i] ^ b[i]));
+  return d;
+}
+
+// Layout probe: A one-hot per row, B coded bytes; prints which (row, k) of B every accumulator actually saw.
+static int diag() {
+  const int rowsA = 128, rowsB = 256;
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+  CK(cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  struct Var { const char* name; int lbo, sbo, kstep, nk; int layout; };
+  // layout 0: [group][chunk][8][16] (lbo 128, sbo 2304); layout 1: same bytes, descriptor strides swapped
+  const Var vars[] = {{"doc: lbo=128 sbo=2304", 128, kGroupBytes, 256, 9, 0},
+                      {"swapped: lbo=2304 sbo=128", kGroupBytes, 128, 256, 9, 0},
+                      {"one MMA only (k=0)", 128, kGroupBytes, 256, 1, 0}};
+  std::vector<int8_t> A(kABytes, 0), B(kBBytes, 0);
+  auto at = [](int row, int k) { return (size_t)(row >> 3) * kGroupBytes + (k >> 4) * 128 + (row & 7) * 16 + (k & 15); };
+  auto bcode = [](int j, int k) { return (int)((j * 31 + k * 7) % 251) - 125; };
+  for (int i = 0; i < rowsA; ++i) A[at(i, (i * 5 + 3) % kKBytes)] = 1;
+  for (int j = 0; j < rowsB; ++j)
+    for (int k = 0; k < kKBytes; ++k) B[at(j, k)] = (int8_t)bcode(j, k);
+  uint8_t *d_a, *d_b;
+  int *d_n, *d_dump;
+  unsigned* d_best;
+  CK(cudaMalloc(&d_a, kABytes));
+  CK(cudaMalloc(&d_b, kBBytes));
+  CK(cudaMalloc(&d_n, 8));
+  CK(cudaMalloc(&d_dump, 128 * 256 * 4));
+  CK(cudaMalloc(&d_best, 256 * 2 * 4));
+  CK(cudaMemcpy(d_a, A.data(), kABytes, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_b, B.data(), kBBytes, cudaMemcpyHostToDevice));
+  const int nn[2] = {128, 256};
+  CK(cudaMemcpy(d_n, nn, 8, cudaMemcpyHostToDevice));
+  for (const Var& v : vars) {
+    MmaArgs a{};
+    a.ea = d_a, a.eb = d_b, a.nq_dev = d_n, a.nt_dev = d_n + 1, a.max_rows = 256, a.npairs = 1, a.mtiles = 1;
+    a.best = d_best, a.rev = nullptr, a.dump = d_dump, a.lbo = v.lbo, a.sbo = v.sbo, a.kstep = v.kstep, a.nk = v.nk;
+    CK(cudaMemset(d_dump, 0, 128 * 256 * 4));
+    hamming_mma_kernel<<<1, kThreads, kSmemBytes>>>(a);
+    CK(cudaDeviceSynchronize());
+    std::vector<int> D(128 * 256);
+    CK(cudaMemcpy(D.data(), d_dump, D.size() * 4, cudaMemcpyDeviceToHost));
+    long ok = 0;
+    for (int i = 0; i < 128; ++i)
+      for (int j = 0; j < 256; ++j) ok += D[i * 256 + j] == bcode(j, (i * 5 + 3) % kKBytes);
+    printf("== %s: %ld / %d accumulators as documented\n", v.name, ok, 128 * 256);
+    // decode: for row i, which k' explains D[i][j] = bcode(j', k') with j' = j for all j?  else try (j', k') search on j = 0..3
+    for (int i = 0; i < 128; i += (i < 20 ? 1 : 9)) {
+      const int ki = (i * 5 + 3) % kKBytes;
+      int found = -1;
+      for (int k = 0; k < kKBytes && found < 0; ++k) {
+        bool all = true;
+        for (int j = 0; j < 256 && all; ++j) all = D[i * 256 + j] == bcode(j, k);
+        if (all) found = k;
+      }
+      printf("  row %3d onehot k=%3d -> D[i][0..5] = %5d %5d %5d %5d %5d %5d  explained by k'=%d (want B: %d %d %d)\n", i, ki,
+             D[i * 256], D[i * 256 + 1], D[i * 256 + 2], D[i * 256 + 3], D[i * 256 + 4], D[i * 256 + 5], found,
+             bcode(0, ki), bcode(1, ki), bcode(2, ki));
+    }
+  }
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  if (argc > 1 && !strcmp(argv[1], "diag")) return diag();
+  const int npairs = argc > 1 ? atoi(argv[1]) : 999;
+  const int rows = argc > 2 ? atoi(argv[2]) : 2000;
+  const int cap = (rows + rows / 8 + 64 + 31) / 32 * 32;
+  const int rows_padded = (cap + 255) / 256 * 256;
+  const int nsets = npairs + 1;
+  printf("npairs %d rows %d cap %d rows_padded %d smem %d\n", npairs, rows, cap, rows_padded, kSmemBytes);
+  // descriptor sets: random, set s+1 holds noisy copies of half of set s (real matches), and a few exact duplicates
+  std::vector<uint8_t> desc((size_t)nsets * cap * 32);
+  std::vector<int> n(nsets);
+  srand(1);
+  for (int s = 0; s < nsets; ++s) {
+    n[s] = rows - (s % 7) * 13;
+    if (s == 3) n[s] = 257;
+    if (s == 5) n[s] = 1;
+    for (size_t i = 0; i < (size_t)cap * 32; ++i) desc[(size_t)s * cap * 32 + i] = (uint8_t)(rand() >> 7);
+    if (s > 0)
+      for (int r = 0; r < n[s] / 2 && r < n[s - 1]; ++r) {
+        uint8_t* d = &desc[((size_t)s * cap + r) * 32];
+        memcpy(d, &desc[((size_t)(s - 1) * cap + (r * 7) % n[s - 1]) * 32], 32);
+        if (r % 5) d[rand() % 32] ^= (uint8_t)(1 << (rand() % 8));  // r % 5 == 0: exact duplicate (distance 0)
+        if (r % 11 == 0 && r + 1 < n[s]) memcpy(d + 32, d, 32);      // tie between two train rows
+      }
+  }
+  uint8_t *d_desc, *d_ea, *d_eb;
+  int* d_n;
+  unsigned* d_best;
+  unsigned long long* d_rev;
+  const size_t estride = (size_t)rows_padded / 8 * kGroupBytes;
+  CK(cudaMalloc(&d_desc, desc.size()));
+  CK(cudaMalloc(&d_ea, estride * nsets + kBBytes));
+  CK(cudaMalloc(&d_eb, estride * nsets + kBBytes));
+  CK(cudaMalloc(&d_n, nsets * sizeof(int)));
+  CK(cudaMalloc(&d_best, (size_t)npairs * cap * 2 * sizeof(unsigned)));
+  CK(cudaMalloc(&d_rev, (size_t)npairs * cap * sizeof(unsigned long long)));
+  CK(cudaMemcpy(d_desc, desc.data(), desc.size(), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d_n, n.data(), nsets * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemset(d_best, 0xFF, (size_t)npairs * cap * 2 * sizeof(unsigned)));
+  CK(cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+
+  MmaArgs a{};
+  a.ea = d_ea;                      // pair p: query = set p, train = set p + 1
+  a.eb = d_eb + estride;
+  a.ea_stride = a.eb_stride = estride;
+  a.nq_dev = d_n;
+  a.nt_dev = d_n + 1;
+  a.max_rows = cap;
+  a.npairs = npairs;
+  a.mtiles = (cap + kTileM - 1) / kTileM;
+  a.best = d_best;
+  a.rev = d_rev;
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0), cudaEventCreate(&e1), cudaEventCreate(&e2);
+  for (int rep = 0; rep < 4; ++rep) {
+    CK(cudaMemset(d_rev, 0xFF, (size_t)npairs * cap * sizeof(unsigned long long)));
+    cudaEventRecord(e0);
+    dim3 ge((rows_padded * kChunks + 255) / 256, nsets);
+    expand_kernel<<<ge, 256>>>(d_desc, (size_t)cap * 32, d_n, rows_padded, d_ea, estride, 0);
+    expand_kernel<<<ge, 256>>>(d_desc, (size_t)cap * 32, d_n, rows_padded, d_eb, estride, 1);
+    cudaEventRecord(e1);
+    hamming_mma_kernel<<<sms, kThreads, kSmemBytes>>>(a);
+    cudaEventRecord(e2);
+    CK(cudaDeviceSynchronize());
+    float ms_e, ms_k;
+    cudaEventElapsedTime(&ms_e, e0, e1);
+    cudaEventElapsedTime(&ms_k, e1, e2);
+    double pairs = 0;
+    for (int p = 0; p < npairs; ++p) pairs += (double)n[p] * n[p + 1];
+    printf("rep %d: expand %.3f ms, mma kernel %.3f ms, %.1f G pairs/s (kernel), %.1f G pairs/s (both)\n", rep, ms_e, ms_k,
+           pairs / ms_k * 1e-6, pairs / (ms_k + ms_e) * 1e-6);
+  }
+  // check a few pairs against the CPU loop
+  std::vector<unsigned> best((size_t)npairs * cap * 2);
+  std::vector<unsigned long long> rev((size_t)npairs * cap);
+  CK(cudaMemcpy(best.data(), d_best, best.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(rev.data(), d_rev, rev.size() * 8, cudaMemcpyDeviceToHost));
+  long bad = 0, checked = 0;
+  const int check_pairs[] = {0, 1, 2, 3, 4, 5, npairs / 2, npairs - 1};
+  for (int p : check_pairs) {
+    if (p < 0 || p >= npairs) continue;
+    const int nq = n[p], nt = n[p + 1];
+    std::vector<unsigned long long> r(nt, ~0ull);
+    for (int i = 0; i < nq; ++i) {
+      unsigned b1 = ~0u, b2 = ~0u;
+      for (int j = 0; j < nt; ++j) {
+        const unsigned d = popc256(&desc[((size_t)p * cap + i) * 32], &desc[((size_t)(p + 1) * cap + j) * 32]);
+        const unsigned key = (d << 16) | (unsigned)j;
+        const unsigned hi = std::max(b1, key);
+        b1 = std::min(b1, key);
+        b2 = std::min(b2, hi);
+        const unsigned long long rk = ((unsigned long long)d << 32) | (unsigned long long)i;
+        r[j] = std::min(r[j], rk);
+      }
+      const unsigned* o = &best[((size_t)p * cap + i) * 2];
+      ++checked;
+      if (o[0] != b1 || o[1] != b2) {
+        if (bad < 10) printf("pair %d query %d: got %08x %08x want %08x %08x\n", p, i, o[0], o[1], b1, b2);
+        ++bad;
+      }
+    }
+    for (int j = 0; j < nt; ++j) {
+      ++checked;
+      if (rev[(size_t)p * cap + j] != r[j]) {
+        if (bad < 20) printf("pair %d train %d: rev got %016llx want %016llx\n", p, j, rev[(size_t)p * cap + j], r[j]);
+        ++bad;
+      }
+    }
+  }
+  printf("checked %ld results, %ld mismatches -> %s\n", checked, bad, bad ? "FAIL" : "OK (bit-exact)");
+  return bad ? 1 : 0;
+}

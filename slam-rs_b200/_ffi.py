@@ -110,6 +110,18 @@ def _load():
         "orbx_sequence_run_host": (i, [vp, vp, i, vp, vp, vp, vp, vp]),
         "orbx_sequence_results": (i, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
         "orbx_sequence_sync": (i, [vp]),
+        "orbx_sequence_set_reference_filter": (i, [vp, i, f]),
+        "orbx_sequence_set_timing": (i, [vp, i]),
+        "orbx_sequence_elapsed": (i, [vp, C.POINTER(f), ip, i]),
+        "orbx_comm_create": (i, [ip, i, C.POINTER(vp)]),
+        "orbx_comm_destroy": (None, [vp]),
+        "orbx_comm_size": (i, [vp]),
+        "orbx_comm_set_train": (i, [vp, vp, i]),
+        "orbx_comm_knn_match2": (i, [vp, vp, i, vp, vp]),
+        "orbx_comm_match": (i, [vp, vp, i, vp, vp]),
+        "orbx_comm_sync": (i, [vp]),
+        "orbx_comm_set_timing": (i, [vp, i]),
+        "orbx_comm_timing": (i, [vp, C.POINTER(f), ip, C.POINTER(f), i]),
         "orbx_last_error": (C.c_char_p, []),
         "orbx_version": (C.c_char_p, []),
         "orbx_launch_count": (C.c_uint64, []),

@@ -62,6 +62,11 @@ inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 
 constexpr int kMaxLevels = 8;
 
+// internal entry points shared between translation units
+int match_slice(orbx_matcher* m, int K, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* counts,
+                int index_base);
+cudaStream_t matcher_stream(orbx_matcher* m);
+
 // CUDA-event stage timer: events are recorded on the launching stream around each stage and only
 // read back (with a synchronise) when the caller asks for the totals.
 struct EventTimer {

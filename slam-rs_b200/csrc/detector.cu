@@ -12,6 +12,8 @@
 //   cand, key : per level [B][cand_cap_l] u32 — FAST candidates and their Harris keys; cand_cap_l is the
 //               NMS worst case (one survivor per 2x2 block of the culled interior), so it cannot overflow
 //   sel       : per level [B][sel_cap_l] u64 — sorted survivors of retainBest(N_l)
+//   spill     : u64 arena for tie floods (a level whose retainBest keeps more than sel_cap_l / the shared-memory sort
+//               holds): one frame's worst case + 8192 entries per further frame of the batch
 //   counters  : cand_count[B][8], hist[B][8][256], flags — zeroed with one memset per batch
 #include <math.h>
 #include <string.h>
@@ -30,7 +32,10 @@ struct orbx_detector {
   // allocations
   uint8_t *pyr = nullptr, *blr = nullptr;
   uint32_t *cand = nullptr, *key = nullptr, *counters = nullptr, *tables = nullptr, *kp_lvl = nullptr;
-  unsigned long long* sel = nullptr;
+  unsigned long long *sel = nullptr, *spill = nullptr;
+  size_t spill_cap = 0;   // entries of the tie-flood arena
+  int* sticky = nullptr;  // [2] device words that survive the per-batch reset (DevGeom::sticky)
+  size_t out_rows = 0;    // rows of out_kps / out_desc / kp_lvl (grown on demand: B x cap of the largest call)
   orbx_keypoint* out_kps = nullptr;
   uint8_t* out_desc = nullptr;
   int* out_n = nullptr;  // [max_batch] counts + [1] flags
@@ -191,13 +196,20 @@ int orbx_detector_create(const orbx_params* params, int device, int max_w, int m
     max_sel = std::max(max_sel, d->sel_cap[l]);
   }
   d->sort_cap = std::min(next_pow2(max_sel), 16384);
-  d->counter_words = B * kMaxLevels * (1 + 256 + 1) + 16;
+  d->counter_words = B * kMaxLevels * (1 + 256 + 1 + 1) + 16;
+  size_t worst = 0;  // every level of one frame flooded (sorted in power-of-two regions)
+  for (int l = 0; l < n; ++l) worst += (size_t)next_pow2(d->cand_cap[l]);
+  d->spill_cap = std::min<size_t>(worst + (B - 1) * std::min<size_t>(worst, 8192), 0x7FFFFFFFu);
+  d->out_rows = B * d->out_cap;
   int rc = ORBX_OK;
   if (!rc) rc = dev_alloc(&d->pyr, d->pyr_bytes + 256);
   if (!rc) rc = dev_alloc(&d->blr, d->pyr_bytes + 256);
   if (!rc) rc = dev_alloc(&d->cand, d->cand_words * 4);
   if (!rc) rc = dev_alloc(&d->key, d->cand_words * 4);
   if (!rc) rc = dev_alloc(&d->sel, d->sel_words * 8);
+  if (!rc) rc = dev_alloc(&d->spill, d->spill_cap * 8);
+  if (!rc) rc = dev_alloc(&d->sticky, 2 * sizeof(int));
+  if (!rc && cudaMemset(d->sticky, 0, 2 * sizeof(int)) != cudaSuccess) rc = ORBX_E_CUDA;
   if (!rc) rc = dev_alloc(&d->counters, d->counter_words * 4);
   if (!rc) rc = dev_alloc(&d->tables, d->table_words * 4);
   if (!rc) rc = dev_alloc(&d->kp_lvl, B * d->out_cap * 4);
@@ -232,6 +244,8 @@ void orbx_detector_destroy(orbx_detector* d) {
   cudaFree(d->cand);
   cudaFree(d->key);
   cudaFree(d->sel);
+  cudaFree(d->spill);
+  cudaFree(d->sticky);
   cudaFree(d->counters);
   cudaFree(d->tables);
   cudaFree(d->kp_lvl);
@@ -248,7 +262,21 @@ int orbx_detector_max_features(const orbx_detector* d) { return d ? d->p.nfeatur
 int orbx_detector_sync(orbx_detector* d) {
   if (!d) return ORBX_E_BADARG;
   ORBX_CUDA(cudaSetDevice(d->device));
+  // overflow of asynchronous calls since the last sync (kernels cannot return an error code): read and clear
+  int st[2] = {0, 0};
+  ORBX_CUDA(cudaMemcpyAsync(st, d->sticky, sizeof(st), cudaMemcpyDeviceToHost, d->stream));
   ORBX_CUDA(cudaStreamSynchronize(d->stream));
+  if (st[0] || st[1]) {
+    ORBX_CUDA(cudaMemsetAsync(d->sticky, 0, sizeof(st), d->stream));
+    ORBX_CUDA(cudaStreamSynchronize(d->stream));
+    if (st[0])
+      set_error("orbx detect: %d tied keypoints on one level exhausted the handle's tie arena (smaller batches hold more)",
+                st[0]);
+    else
+      set_error("orbx detect: a frame produced %d keypoints, more than the row capacity of the asynchronous call "
+                "(rows were truncated to cap; re-run with cap >= %d)", st[1], st[1]);
+    return ORBX_E_CAPACITY;
+  }
   return ORBX_OK;
 }
 

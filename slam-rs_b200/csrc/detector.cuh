@@ -45,8 +45,14 @@ struct DevGeom {
   uint32_t* cand_count;  // [B][8]
   uint32_t* hist;        // [B][8][256]
   uint32_t* sel_count;   // [B][8]
-  int* flags;            // [0] != 0: a per-level selection overflowed sel_cap
+  uint32_t* sel_off;     // [B][8] offset of the level's sorted selection inside `spill`, or kSelInline
+  int* flags;            // [0] != 0: the spill arena is exhausted (entries needed); [1] = spill cursor
+  unsigned long long* spill;  // tie floods: selections larger than sel_cap / the shared-memory sort live here
+  uint32_t spill_cap;    // entries
+  int* sticky;           // survives the per-batch reset: [0] arena exhausted, [1] largest per-frame count that did not
+                         // fit the caller's cap on the asynchronous path (read and cleared by orbx_detector_sync)
 };
+constexpr uint32_t kSelInline = 0xFFFFFFFFu;
 
 struct OutArgs {
   orbx_keypoint* kps;  // [B][cap]
@@ -54,6 +60,7 @@ struct OutArgs {
   uint32_t* kp_lvl;    // [B][lvl_cap]  level << 24 | y << 12 | x
   int* n;              // [B]
   int cap, lvl_cap;
+  int clamp_n;         // asynchronous path: n[frame] = min(total, cap), the overflow goes to DevGeom::sticky[1]
 };
 
 struct ResizeArgs {

@@ -95,6 +95,7 @@ struct MatchArgs {
   int* n_out;                // optional per problem count (K=1 batch): nq or 0
   unsigned long long* rev;   // FUSED only: [problem][max_rows_t] reverse best-1 (dist << 32 | query_idx), preset ~0
   int rev_rows;              // row pitch of rev (max train rows per problem)
+  int q_index_base;          // added to query_idx in the records (query-sharded matching: this launch owns a slice)
 };
 
 __device__ __forceinline__ unsigned lop3_xor3(unsigned a, unsigned b, unsigned c) {
@@ -236,11 +237,11 @@ __global__ void __launch_bounds__(kQPB) hamming_knn_kernel(MatchArgs a) {
     orbx_dmatch* o = a.out + ((size_t)prob * a.max_rows + qi) * K;
     int cnt = 0;
     if (b1 != 0xFFFFFFFFu) {
-      o[0] = orbx_dmatch{qi, (int)(b1 & 0xFFFF), 0, (float)(b1 >> 16)};
+      o[0] = orbx_dmatch{qi + a.q_index_base, (int)(b1 & 0xFFFF), 0, (float)(b1 >> 16)};
       cnt = 1;
     }
     if (K == 2 && b2 != 0xFFFFFFFFu) {
-      o[1] = orbx_dmatch{qi, (int)(b2 & 0xFFFF), 0, (float)(b2 >> 16)};
+      o[1] = orbx_dmatch{qi + a.q_index_base, (int)(b2 & 0xFFFF), 0, (float)(b2 >> 16)};
       cnt = 2;
     }
     if (a.n_per_q) a.n_per_q[(size_t)prob * a.max_rows + qi] = cnt;
@@ -279,11 +280,11 @@ __global__ void merge_splits_kernel(MatchArgs a) {
   orbx_dmatch* o = a.out + ((size_t)prob * a.max_rows + qi) * K;
   int cnt = 0;
   if (b1 != ~0ull) {
-    o[0] = orbx_dmatch{qi, (int)(b1 & 0xFFFFFFFFu), 0, (float)(unsigned)(b1 >> 32)};
+    o[0] = orbx_dmatch{qi + a.q_index_base, (int)(b1 & 0xFFFFFFFFu), 0, (float)(unsigned)(b1 >> 32)};
     cnt = 1;
   }
   if (K == 2 && b2 != ~0ull) {
-    o[1] = orbx_dmatch{qi, (int)(b2 & 0xFFFFFFFFu), 0, (float)(unsigned)(b2 >> 32)};
+    o[1] = orbx_dmatch{qi + a.q_index_base, (int)(b2 & 0xFFFFFFFFu), 0, (float)(unsigned)(b2 >> 32)};
     cnt = 2;
   }
   if (a.n_per_q) a.n_per_q[(size_t)prob * a.max_rows + qi] = cnt;
@@ -463,6 +464,27 @@ __global__ void matched_points_kernel(const orbx_keypoint* kp1, const int* n1_de
     pts2[base + i] = make_float2(kb.x, kb.y);
   }
 }
+
+// Query-sharded matching (csrc/comm.cu): rows [index_base, index_base + nq) of a larger query set against the whole
+// train set, device pointers only, asynchronous on the matcher's stream.  `out` (nq x K records) and `counts` (K = 2:
+// nq ints, may be null) may live on ANOTHER device: the epilogue stores them through peer-mapped pointers.
+int match_slice(orbx_matcher* m, int K, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* counts,
+                int index_base) {
+  if (nq <= 0) return ORBX_OK;
+  ORBX_CUDA(cudaSetDevice(m->device));
+  MatchArgs a{};
+  a.q = q;
+  a.t = t;
+  a.nq_fixed = nq;
+  a.nt_fixed = nt;
+  a.max_rows = nq;
+  a.out = out;
+  a.n_per_q = K == 2 ? counts : nullptr;
+  a.q_index_base = index_base;
+  return K == 1 ? launch_knn<1>(m, a, 1) : launch_knn<2>(m, a, 1);
+}
+
+cudaStream_t matcher_stream(orbx_matcher* m) { return m->stream; }
 
 }  // namespace orbx
 

@@ -285,7 +285,10 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort
   const uint32_t count = min(g.cand_count[fl], (uint32_t)L.cand_cap);
   const int tid = threadIdx.x;
   if (count == 0 || L.quota == 0) {
-    if (tid == 0) g.sel_count[fl] = 0;
+    if (tid == 0) {
+      g.sel_count[fl] = 0;
+      g.sel_off[fl] = kSelInline;
+    }
     return;
   }
   const uint32_t* cand = L.cand + (size_t)frame * L.cand_cap;
@@ -337,44 +340,74 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort
   }
   __syncthreads();
   uint32_t nsel = s_nsel;
-  if (nsel > (uint32_t)L.sel_cap || nsel > (uint32_t)sort_cap) {
-    if (tid == 0) atomicExch(g.flags, (int)nsel);
-    nsel = min(nsel, (uint32_t)min(L.sel_cap, sort_cap));
-  }
+  unsigned long long* buf = s_sort;  // where the selection is sorted: shared memory, or the spill arena
+  uint32_t off = kSelInline;
   uint32_t n2 = 1;
   while (n2 < nsel) n2 <<= 1;
-  for (uint32_t i = nsel + tid; i < n2; i += kSelThreads) s_sort[i] = 0ull;
+  if (nsel > (uint32_t)L.sel_cap || nsel > (uint32_t)sort_cap) {
+    // Tie flood: OpenCV's retainBest keeps EVERY entry >= the n-th best, so a level of equal responses (checkerboards,
+    // binary images) selects far more than N_l.  Such a selection is compacted again and sorted in the handle's global
+    // spill arena instead of shared memory; orient_kernel reads it from there (sel_off).
+    __syncthreads();  // everyone has read s_nsel
+    if (tid == 0) s_scratch[0] = atomicAdd(reinterpret_cast<unsigned*>(g.flags + 1), n2);
+    __syncthreads();
+    const uint32_t base = s_scratch[0];
+    if (base > g.spill_cap || n2 > g.spill_cap - base) {
+      // arena exhausted (many flooded frames in one batch): truncate and report ORBX_E_CAPACITY
+      if (tid == 0) {
+        atomicMax(g.flags, (int)nsel);
+        atomicMax(g.sticky, (int)nsel);
+      }
+      nsel = min(nsel, (uint32_t)min(L.sel_cap, sort_cap));
+      n2 = 1;
+      while (n2 < nsel) n2 <<= 1;
+    } else {
+      buf = g.spill + base;
+      off = base;
+      if (tid == 0) s_nsel = 0;
+      __syncthreads();
+      for (uint32_t i = tid; i < count; i += kSelThreads) {
+        const uint32_t k = key[i];
+        if (k != 0 && k >= thr)
+          buf[atomicAdd(&s_nsel, 1u)] = ((unsigned long long)k << 32) | (unsigned long long)(0xFFFFFFu - (cand[i] & 0xFFFFFFu));
+      }
+    }
+  }
+  for (uint32_t i = nsel + tid; i < n2; i += kSelThreads) buf[i] = 0ull;
   __syncthreads();
-  // bitonic sort, descending
+  // bitonic sort, descending (block-private region: __syncthreads orders the global-memory passes too)
   for (uint32_t k = 2; k <= n2; k <<= 1) {
     for (uint32_t j = k >> 1; j > 0; j >>= 1) {
       for (uint32_t i = tid; i < n2; i += kSelThreads) {
         const uint32_t p = i ^ j;
         if (p > i) {
-          const unsigned long long a = s_sort[i], b = s_sort[p];
+          const unsigned long long a = buf[i], b = buf[p];
           const bool desc = (i & k) == 0;
           if (desc ? (a < b) : (a > b)) {
-            s_sort[i] = b;
-            s_sort[p] = a;
+            buf[i] = b;
+            buf[p] = a;
           }
         }
       }
       __syncthreads();
     }
   }
-  unsigned long long* sel = L.sel + (size_t)frame * L.sel_cap;
-  for (uint32_t i = tid; i < nsel; i += kSelThreads) sel[i] = s_sort[i];
-  if (tid == 0) g.sel_count[fl] = nsel;
+  if (off == kSelInline) {
+    unsigned long long* sel = L.sel + (size_t)frame * L.sel_cap;
+    for (uint32_t i = tid; i < nsel; i += kSelThreads) sel[i] = s_sort[i];
+  }
+  if (tid == 0) {
+    g.sel_count[fl] = nsel;
+    g.sel_off[fl] = off;
+  }
 }
 
 int launch_select(const DevGeom& g, int sort_cap, cudaStream_t s) {
   if (g.batch == 0) return ORBX_OK;
   const size_t smem = (size_t)sort_cap * sizeof(unsigned long long);
-  static int configured = 0;
-  if (smem > 48 * 1024 && configured < (int)smem) {
+  // the opt-in is per device (a process may drive several GPUs through the `device` argument): set it on every launch
+  if (smem > 48 * 1024)
     ORBX_CUDA(cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = (int)smem;
-  }
   dim3 grid(g.nlevels, g.batch);
   select_kernel<<<grid, kSelThreads, smem, s>>>(g, sort_cap);
   ORBX_LAUNCH_CHECK();
@@ -433,8 +466,13 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
   for (int l = 0; l < kMaxLevels; ++l)
     pre[l + 1] = pre[l] + (l < g.nlevels ? g.sel_count[(size_t)frame * kMaxLevels + l] : 0u);
   const uint32_t total = pre[kMaxLevels];
-  if (blockIdx.x == 0 && threadIdx.x == 0) o.n[frame] = (int)total;
   const uint32_t limit = min(total, (uint32_t)min(o.cap, o.lvl_cap));
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    // synchronous callers get the needed size (ORBX_E_CAPACITY); on the asynchronous path nothing on the host reads
+    // n before using it as a row count, so it is clamped and the overflow is parked for orbx_detector_sync
+    o.n[frame] = o.clamp_n ? (int)limit : (int)total;
+    if (o.clamp_n && total > limit) atomicMax(g.sticky + 1, (int)total);
+  }
 
   // per-lane coefficient words: byte b of word k <-> u = -15 + 4k + b
   const int v = min(lane, 30) - 15;
@@ -488,7 +526,8 @@ __global__ void __launch_bounds__(kOrientWarps * 32) orient_kernel(DevGeom g, Ou
           first = pre[i];
         }
       const DevLevel& L = g.lv[k.l];
-      k.e = L.sel[(size_t)frame * L.sel_cap + (k.j - first)];
+      const uint32_t so = g.sel_off[(size_t)frame * kMaxLevels + k.l];
+      k.e = (so == kSelInline ? L.sel + (size_t)frame * L.sel_cap : g.spill + so)[k.j - first];
       const uint32_t pos = 0xFFFFFFu - (uint32_t)(k.e & 0xFFFFFFu);
       k.x = (int)(pos & 0xFFF), k.y = (int)(pos >> 12);
       k.aligned = L.aligned4 != 0;

@@ -14,6 +14,9 @@
 struct orbx_sequence {
   int device = 0, w = 0, h = 0, nfeatures = 0, max_frames = 0, chunk = 0, host_chunk = 0, cap = 0;
   float ratio = 0.75f;
+  int reference_filter = 0;  // 1: match_descriptors (k=1) + filter_good_matches(filter_ratio), the reference's own loop
+  float filter_ratio = 2.0f;
+  int* n_k1 = nullptr;       // [T] match counts of the k=1 pass (reference_filter)
   orbx_detector* det[2] = {nullptr, nullptr};
   orbx_matcher* mat[2] = {nullptr, nullptr};
   cudaStream_t st[2] = {nullptr, nullptr}, copy = nullptr, d2h = nullptr;
@@ -28,6 +31,11 @@ struct orbx_sequence {
   int* n_good = nullptr;
   std::vector<cudaEvent_t> events;  // pool, reused by every pass
   size_t next_event = 0;
+  // device-side timing of the passes (orbx_sequence_set_timing): t_begin is recorded when the first pass since the last
+  // reset starts, t_end when everything a pass queued has finished (re-recorded by every pass)
+  bool timing = false, have_begin = false;
+  cudaEvent_t t_begin = nullptr, t_end = nullptr;
+  int passes = 0;
 };
 
 namespace {
@@ -65,6 +73,21 @@ int join_all(orbx_sequence* s) {
   for (int i = 0; i < 4; ++i)
     for (int j = 0; j < 4; ++j)
       if (i != j) ORBX_CUDA(cudaStreamWaitEvent(all[i], e[j], 0));
+  if (s->timing && !s->have_begin) {
+    ORBX_CUDA(cudaEventRecord(s->t_begin, s->copy));  // the copy stream has just joined everything queued before
+    s->have_begin = true;
+  }
+  return ORBX_OK;
+}
+
+// end of a pass: the d2h stream waits for the other three and carries the end-of-pass timestamp
+int finish_pass(orbx_sequence* s) {
+  if (!s->timing) return ORBX_OK;
+  cudaStream_t others[3] = {s->st[0], s->st[1], s->copy};
+  for (cudaStream_t o : others)
+    if (int rc = wait_stream(s, s->d2h, o)) return rc;
+  ORBX_CUDA(cudaEventRecord(s->t_end, s->d2h));
+  ++s->passes;
   return ORBX_OK;
 }
 
@@ -80,12 +103,22 @@ int extract(orbx_sequence* s, int k, const uint8_t* frames, size_t pitch, size_t
   return ORBX_OK;
 }
 
-// pairs (t-1, t) for t in [max(a, 1), b): BFMatcher k=2 (+ cross-check) and Lowe's ratio test, batched
+// pairs (t-1, t) for t in [max(a, 1), b), batched: BFMatcher k=2 (+ cross-check) and Lowe's ratio test (north_star
+// stage 5), or - reference_filter - exactly what the reference's loop runs: k=1 + filter_good_matches
 int match(orbx_sequence* s, int k, int a, int b) {
   a = std::max(a, 1);
   if (b <= a) return ORBX_OK;
   const int npairs = b - a;
   const size_t cap = (size_t)s->cap, stride = cap * 32;
+  if (s->reference_filter) {
+    // visual_odometry.rs:106-107: match_descriptors(&prev_desc, &desc) then filter_good_matches(&matches, 2.0)
+    int rc = orbx_match_batch(s->mat[k], s->desc + (size_t)(a - 1) * stride, stride, s->n + (a - 1),
+                              s->desc + (size_t)a * stride, stride, s->n + a, npairs, s->cap, s->knn + (size_t)a * cap,
+                              s->n_k1 + a);
+    if (rc) return rc;
+    return orbx_filter_good_matches_batch(s->mat[k], s->knn + (size_t)a * cap, s->n_k1 + a, npairs, s->cap,
+                                          s->filter_ratio, s->good + (size_t)a * cap, s->n_good + a);
+  }
   int rc = orbx_knn_match2_batch(s->mat[k], s->desc + (size_t)(a - 1) * stride, stride, s->n + (a - 1),
                                  s->desc + (size_t)a * stride, stride, s->n + a, npairs, s->cap, s->knn + (size_t)a * cap * 2,
                                  s->n_per_q + (size_t)a * cap);
@@ -148,6 +181,8 @@ void orbx_sequence_destroy(orbx_sequence* s) {
   if (s->copy) cudaStreamDestroy(s->copy);
   if (s->d2h) cudaStreamDestroy(s->d2h);
   for (cudaEvent_t e : s->events) cudaEventDestroy(e);
+  if (s->t_begin) cudaEventDestroy(s->t_begin);
+  if (s->t_end) cudaEventDestroy(s->t_end);
   cudaFree(s->frames);
   cudaFree(s->kps);
   cudaFree(s->desc);
@@ -156,6 +191,7 @@ void orbx_sequence_destroy(orbx_sequence* s) {
   cudaFree(s->n_per_q);
   cudaFree(s->good);
   cudaFree(s->n_good);
+  cudaFree(s->n_k1);
   delete s;
 }
 
@@ -203,6 +239,7 @@ int orbx_sequence_create(int device, int width, int height, int nfeatures, int m
   if (!rc) rc = dev_alloc(&s->n_per_q, T * cap);
   if (!rc) rc = dev_alloc(&s->good, T * cap);
   if (!rc) rc = dev_alloc(&s->n_good, T);
+  if (!rc) rc = dev_alloc(&s->n_k1, T);
   if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = ORBX_E_CUDA;  // the memsets ran on the legacy stream
   if (rc) {
     if (rc == ORBX_E_CUDA) set_error("orbx_sequence_create: CUDA error %s", cudaGetErrorString(cudaGetLastError()));
@@ -215,6 +252,50 @@ int orbx_sequence_create(int device, int width, int height, int nfeatures, int m
 
 int orbx_sequence_capacity(const orbx_sequence* s) { return s ? s->cap : 0; }
 
+int orbx_sequence_set_timing(orbx_sequence* s, int enable) {
+  if (!s) {
+    set_error("orbx_sequence_set_timing: null handle");
+    return ORBX_E_BADARG;
+  }
+  ORBX_CUDA(cudaSetDevice(s->device));
+  if (enable && !s->t_begin) {
+    ORBX_CUDA(cudaEventCreate(&s->t_begin));
+    ORBX_CUDA(cudaEventCreate(&s->t_end));
+  }
+  s->timing = enable != 0;
+  s->have_begin = false;
+  s->passes = 0;
+  return ORBX_OK;
+}
+
+int orbx_sequence_elapsed(orbx_sequence* s, float* ms, int* passes, int reset) {
+  if (!s || !ms) {
+    set_error("orbx_sequence_elapsed: bad argument");
+    return ORBX_E_BADARG;
+  }
+  *ms = 0.0f;
+  if (passes) *passes = s->passes;
+  if (!s->timing || !s->have_begin || s->passes == 0) return ORBX_OK;
+  ORBX_CUDA(cudaSetDevice(s->device));
+  ORBX_CUDA(cudaEventSynchronize(s->t_end));
+  ORBX_CUDA(cudaEventElapsedTime(ms, s->t_begin, s->t_end));
+  if (reset) {
+    s->have_begin = false;
+    s->passes = 0;
+  }
+  return ORBX_OK;
+}
+
+int orbx_sequence_set_reference_filter(orbx_sequence* s, int enable, float ratio) {
+  if (!s || !(ratio > 0.0f)) {
+    set_error("orbx_sequence_set_reference_filter: bad argument");
+    return ORBX_E_BADARG;
+  }
+  s->reference_filter = enable ? 1 : 0;
+  s->filter_ratio = ratio;
+  return ORBX_OK;
+}
+
 int orbx_sequence_sync(orbx_sequence* s) {
   if (!s) {
     set_error("orbx_sequence_sync: null handle");
@@ -225,7 +306,14 @@ int orbx_sequence_sync(orbx_sequence* s) {
   ORBX_CUDA(cudaStreamSynchronize(s->st[0]));
   ORBX_CUDA(cudaStreamSynchronize(s->st[1]));
   ORBX_CUDA(cudaStreamSynchronize(s->d2h));
-  return ORBX_OK;
+  // a frame with more keypoints than the row capacity (tie floods) was truncated by the asynchronous batch calls: the
+  // detectors park that in a device flag, reported here once as ORBX_E_CAPACITY
+  int rc = ORBX_OK;
+  for (int k = 0; k < 2; ++k) {
+    const int r = orbx_detector_sync(s->det[k]);
+    if (r && !rc) rc = r;
+  }
+  return rc;
 }
 
 int orbx_sequence_results(orbx_sequence* s, orbx_keypoint** kps, uint8_t** desc, int** n, orbx_dmatch** good,
@@ -258,7 +346,7 @@ int orbx_sequence_run_device(orbx_sequence* s, const uint8_t* frames_dev, size_t
     if (int rc = extract(s, 0, frames_dev, pitch, frame_stride, a, b, s->chunk)) return rc;
     if (int rc = match(s, 0, a, b)) return rc;
   }
-  return ORBX_OK;
+  return finish_pass(s);
 }
 
 int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_keypoint* kps, uint8_t* desc, int* n,
@@ -308,7 +396,7 @@ int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_
     if (n_good)
       ORBX_CUDA(cudaMemcpyAsync(n_good + a, s->n_good + a, (size_t)(b - a) * sizeof(int), cudaMemcpyDeviceToHost, s->d2h));
   }
-  return ORBX_OK;
+  return finish_pass(s);
 }
 
 }  // extern "C"

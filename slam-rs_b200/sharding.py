@@ -19,12 +19,13 @@ def frame_shard(nframes, rank, world):
 
 
 def gather_rows(part, total_rows, world, dist):
-    """All-gather per-rank row blocks of unequal length into [total_rows, cols] (rank order = row order)."""
+    """All-gather per-rank row blocks of unequal length into [total_rows, ...] (rank order = row order)."""
     import torch
-    cols = part.shape[1]
+    if world == 1:
+        return part
     sizes = [query_slice(total_rows, r, world) for r in range(world)]
     maxn = max(hi - lo for lo, hi in sizes)
-    pad = torch.zeros((maxn, cols), dtype=part.dtype, device=part.device)
+    pad = torch.zeros((maxn,) + tuple(part.shape[1:]), dtype=part.dtype, device=part.device)
     pad[:part.shape[0]] = part
     bufs = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(bufs, pad)

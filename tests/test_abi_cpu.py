@@ -94,23 +94,55 @@ sys.path.insert(0, %(root)r)
 import numpy as np, torch, torch.distributed as dist
 from oracle import restated as R, synth
 from slam_rs_b200 import sharding
+from slam_rs_b200.mapmatch import MapToFrameMatcher
+from slam_rs_b200.feature import DMATCH_DTYPE
 rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"])
 dist.init_process_group("gloo")
+
+
+class OracleMatcher:
+    # stand-in for the per-rank CUDA matcher (no GPU here): same match_device / filter_good_matches contract,
+    # query_idx local to the slice it is given - exactly what the kernel returns
+    def match_device(self, q, nq, t, nt, out, n_out=None, k=1):
+        idx, d, c = R.knn(q.numpy()[:nq], t.numpy()[:nt], k)
+        rec = np.zeros((nq, k), DMATCH_DTYPE)
+        rec["query_idx"] = np.arange(nq)[:, None]
+        rec["train_idx"], rec["distance"] = idx, d
+        out[:nq] = torch.from_numpy(rec.view(np.uint8).reshape((nq, k, 16) if k == 2 else (nq, 16)))
+        if n_out is not None and k == 2:
+            n_out[:nq] = torch.from_numpy(c.astype(np.int32))
+
+    def filter_good_matches(self, m, ratio):
+        keep = R.filter_good_matches(np.stack([m["query_idx"], m["train_idx"], m["distance"]], 1), ratio)
+        return keep
+
+
 m, f = synth.map_and_frame_descriptors(4000, 301, f=0)
-# query-sharded map-to-frame matching (SURVEY.md 8e): slice the query rows, broadcast the train set
-lo, hi = sharding.query_slice(len(f), rank, world)
-train = torch.from_numpy(m.copy()) if rank == 0 else torch.zeros((len(m), 32), dtype=torch.uint8)
-dist.broadcast(train, src=0)
-idx, d, c = R.knn(f[lo:hi], train.numpy(), 2)              # stand-in for the per-rank CUDA matcher
-part = torch.from_numpy(np.concatenate([idx, d], 1).astype(np.int32))
-out = sharding.gather_rows(part, len(f), world, dist)
+# the PRODUCT class (slicing, query_idx offset, padded all-gather) over a real world-size-2 group
+mm = MapToFrameMatcher(device="cpu", rank=rank, world=world, dist=dist, matcher=OracleMatcher())
+mm.set_train(m.copy() if rank == 0 else None, rows=len(m))
+q = torch.from_numpy(f.copy()) if rank == 0 else None
+rec, cnt = mm.knn2(q, nq=len(f))
+rec = rec.numpy().view(DMATCH_DTYPE).reshape(len(f), 2)
+ri, rd, rc = R.knn(f, m, 2)
+assert np.array_equal(rec["query_idx"], np.repeat(np.arange(len(f))[:, None], 2, 1))   # global rows on every rank
+assert np.array_equal(rec["train_idx"], ri) and np.array_equal(rec["distance"], rd.astype(np.float32))
+assert np.array_equal(cnt.numpy(), rc)
+# reference orientation (map.rs:107-108): the resident rows are the queries, the frame is broadcast
+fr = torch.from_numpy(f[:97].copy()) if rank == 0 else torch.zeros((97, 32), dtype=torch.uint8)
+good = mm.match_train_as_query(fr, 2.0)
+if rank == 0:
+    want = R.filter_good_matches(R.match_k1(m, f[:97]), 2.0)
+    assert np.array_equal(np.asarray(good)[:, :2].astype(np.int64), np.asarray(want)[:, :2].astype(np.int64))
+# an empty frame is an empty result on every rank, with no collective left half-issued (ADVICE r1)
+empty = mm.match_train_as_query(torch.zeros((0, 32), dtype=torch.uint8), 2.0)
+assert (rank == 0 and len(empty) == 0) or (rank != 0 and empty is None)
 # frame sharding for extraction
 fr = sharding.frame_shard(10, rank, world)
 cnt = torch.tensor([len(fr)]); dist.all_reduce(cnt)
+assert int(cnt) == 10
+dist.barrier()
 if rank == 0:
-    ri, rd, _ = R.knn(f, m, 2)
-    assert np.array_equal(out.numpy()[:, :2], ri) and np.array_equal(out.numpy()[:, 2:], rd)
-    assert int(cnt) == 10
     print("OK")
 dist.destroy_process_group()
 '''

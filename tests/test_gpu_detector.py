@@ -122,11 +122,83 @@ def test_small_and_degenerate_images(orbx):
     assert len(det.detect(sat)) == 0
     yy, xx = np.mgrid[0:240, 0:320]
     chk = (((yy // 16) + (xx // 16)) % 2 * 200 + 20).astype(np.uint8)
+    k, d = det.detect_and_compute(chk)
+    assert_exact(compare_orb(k, d, R.orb_detect_and_compute(chk, 100), 240, 320))
+
+
+def dot_lattice(h, w, step):
+    """Isolated bright pixels on a flat background: every dot is a FAST corner with the same score and the same Harris
+    response, so both retainBest stages keep ALL of them (OpenCV keeps every entry >= the n-th best)."""
+    img = np.full((h, w), 30, np.uint8)
+    img[4::step, 4::step] = 220
+    return img
+
+
+def test_tie_floods_return_every_tied_keypoint(orbx):
+    """cv::ORB returns far more than nfeatures keypoints when a level ties at the selection threshold; so must we
+    (detector.rs:26-40 hands back whatever OpenCV returns).  Pinned to cv2 live and to the restatement."""
+    import cv2
+    det = orbx.OrbDetector(100, max_width=1241, max_height=376, max_batch=3)
+    # 704 tied keypoints on level 0 (quota 22): beyond sel_cap, sorted in the spill arena
+    img = dot_lattice(240, 320, 8)
+    kps, desc = det.detect_and_compute(img)
+    ref = R.orb_detect_and_compute(img, 100)
+    assert len(kps) == len(ref["x"]) == len(cv2.ORB_create(nfeatures=100).detect(img, None)) == 760
+    assert_exact(compare_orb(kps, desc, ref, 240, 320))
+    assert_exact(compare_orb(kps, desc, cv_ref.orb_detect_and_compute(img, 100), 240, 320))
+    # detect() alone returns the same keypoints
+    assert np.array_equal(det.detect(img), kps)
+    # ~23 k tied keypoints on level 0: beyond the shared-memory sort (16384) as well
+    big = dot_lattice(376, 1241, 4)
+    kb, db = det.detect_and_compute(big)
+    refb = cv_ref.orb_detect_and_compute(big, 100)
+    assert len(kb) == len(refb["x"]) > 20000
+    assert_exact(compare_orb(kb, db, refb, 376, 1241))
+    # binary noise and block noise (the images a SLAM front end sees on synthetic / thresholded input)
+    rng = np.random.default_rng(5)
+    for im in ((rng.integers(0, 2, (240, 320)) * 255).astype(np.uint8),
+               np.kron(rng.integers(0, 2, (30, 40)), np.ones((8, 8))).astype(np.uint8) * 255):
+        k, d = det.detect_and_compute(im)
+        assert_exact(compare_orb(k, d, cv_ref.orb_detect_and_compute(im, 100), 240, 320))
+    # batch: a flooded frame between two ordinary ones does not disturb its neighbours
+    a, c = synth.frame(240, 320, 91), synth.frame(240, 320, 92)
     try:
-        k, d = det.detect_and_compute(chk)
-        assert_exact(compare_orb(k, d, R.orb_detect_and_compute(chk, 100), 240, 320))
-    except orbx.OrbxError as e:              # tie flood beyond the selection capacity is a reported error
+        det.detect_and_compute_batch(np.stack([a, img, c]), cap=512)
+        raise AssertionError("expected ORBX_E_CAPACITY: 760 keypoints do not fit cap=512")
+    except orbx.OrbxError as e:
         assert e.code == -2
+    out = det.detect_and_compute_batch(np.stack([a, img, c]), cap=1024)
+    for (k, d), im in zip(out, (a, img, c)):
+        assert_exact(compare_orb(k, d, R.orb_detect_and_compute(im, 100), 240, 320))
+
+
+def test_async_overflow_is_clamped_and_reported(orbx):
+    """The asynchronous (device-pointer) path cannot return a needed size: rows are truncated to cap, n is clamped to
+    cap (never an out-of-bounds row count for the consumer) and the next sync reports ORBX_E_CAPACITY once."""
+    import torch
+    det = orbx.OrbDetector(100, max_width=320, max_height=240, max_batch=2)
+    imgs = np.stack([dot_lattice(240, 320, 8), synth.frame(240, 320, 93)])
+    ref = det.detect_and_compute_batch(imgs, cap=1024)
+    cap = 256
+    buf = torch.from_numpy(imgs).cuda()
+    kps = torch.zeros((2, cap, 28), dtype=torch.uint8, device="cuda")
+    desc = torch.zeros((2, cap, 32), dtype=torch.uint8, device="cuda")
+    n = torch.zeros((2,), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    det.detect_and_compute_device(buf, kps, desc, n)
+    try:
+        det.sync()
+        raise AssertionError("expected ORBX_E_CAPACITY from the sync after a truncated asynchronous batch")
+    except orbx.OrbxError as e:
+        assert e.code == -2 and "760" in str(e)
+    nn = n.cpu().numpy()
+    assert nn[0] == cap and nn[1] == len(ref[1][0])
+    # the rows that fit are the first rows of the full result; the ordinary frame is untouched
+    k0 = kps[0].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+    assert np.array_equal(k0, ref[0][0][:cap]) and np.array_equal(desc[0].cpu().numpy(), ref[0][1][:cap])
+    k1 = kps[1, :nn[1]].cpu().numpy().view(orbx.KEYPOINT_DTYPE).reshape(-1)
+    assert np.array_equal(k1, ref[1][0])
+    det.sync()  # reported once
 
 
 def test_batch_device_pointers_and_pitch(orbx):
