@@ -7,6 +7,13 @@ sequence: S1-S9 on every frame and the T-1 (t-1 -> t) matching problems (BFMatch
 mutual test + Lowe ratio 0.75).  N>1: every rank owns an independent sequence (weak scaling, no
 data-path collective — SURVEY.md §8e); value = all frames / max-over-ranks time.
 
+A step is `--passes` (8) passes over the resident sequence, so that a --steps 20 run times > 2 s of GPU work.
+`value`: frames resident in HBM, timed with CUDA events.  `e2e`: the same passes through the reference-facing plugin
+call orbx_sequence_run_host (csrc/sequence.cu) with HOST buffers - pinned frames in, keypoints / descriptors / good
+matches back out - timed by the library's own CUDA events.  Attached sub-measurements (`--subs 1`): `hd` (configs[2]
+shape), `map` (configs[3]: orbx_comm over all GPUs of the run, driven by rank 0), `latency` (configs[0]: two frames,
+per-call).
+
   python bench.py [--gpus N] [--steps K] [--warmup W]          our arm (liborbx on B200)
   python bench.py --impl reference ...                          reference arm: cv2 (= the OpenCV code the
                                                                 reference binds) on the host cores
@@ -31,6 +38,16 @@ WORKLOAD = ("C2 KITTI-shaped synthetic sequence 1241x376 x %d frames/GPU, nfeatu
             "frame-to-frame BFMatcher Hamming k=2 + cross-check + Lowe 0.75")
 
 
+def make_config(args):
+    """The `config` object of the JSON line: the same keys and values in both arms (ours and --impl reference)."""
+    return {"workload": WORKLOAD % args.frames, "frames_per_gpu": args.frames, "width": W_IMG, "height": H_IMG,
+            "nfeatures": NFEAT, "levels": 8, "matching": "k=2 + cross-check + Lowe %.2f" % RATIO,
+            "passes_per_step": args.passes,
+            "step": "%d passes over the resident %d-frame sequence (ours); a %d-frame prefix of the same sequence "
+                    "(reference arm, bounded CPU sample)" % (args.passes, args.frames, args.ref_frames),
+            "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (args.frames * H_IMG * W_IMG / 1e6)}
+
+
 def load_synth():
     import importlib.util as u
     spec = u.spec_from_file_location("_orbx_synth", os.path.join(ROOT, "slam-rs_b200", "synth.py"))
@@ -44,10 +61,10 @@ def measured_peaks():
     if os.path.exists(p):
         try:
             j = json.load(open(p))
-            return float(j["hbm_gbs"]), "measured"
+            return float(j["hbm_gbs"]), "measured", j
         except Exception:
             pass
-    return 6650.0, "fallback"
+    return 6650.0, "fallback", {}
 
 
 class ClockSampler:
@@ -137,34 +154,54 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------
 # CPU reference: cv2 == the cv::ORB / cv::BFMatcher code the reference calls (detector.rs:32, matcher.rs:34)
 # ---------------------------------------------------------------------------------------------------
-def cpu_pass(frames, threads):
-    """One pass of the same hot path with OpenCV on the host: returns (seconds, frames_done)."""
+def cpu_pass(frames, threads, reference_filter=False):
+    """One pass of the same hot path with OpenCV on the host: returns (seconds, frames_done).  The match lists are
+    built (as the reference builds its Vector<DMatch>) but the Python-side filtering of the k=2 + cross-check + Lowe
+    composition is kept outside the clock: OpenCV cannot express it in one call, so the reference arm pays for its two
+    BFMatcher passes only.  reference_filter: the reference's own loop instead (k=1 + filter_good_matches(2.0))."""
     import cv2
     cv2.setNumThreads(threads)
-    orb = cv2.ORB_create(nfeatures=NFEAT)
+    orb = cv2.ORB_create(nfeatures=500 if reference_filter else NFEAT)
     bf = cv2.BFMatcher(cv2.NORM_HAMMING, False)
     bfx = cv2.BFMatcher(cv2.NORM_HAMMING, True)
-    t0 = time.perf_counter()
+    t_total = 0.0
     prev = None
     for img in frames:
+        t0 = time.perf_counter()
         _, desc = orb.detectAndCompute(img, None)
+        knn = mutual = m1 = None
         if prev is not None and desc is not None and len(prev) and len(desc):
-            knn = bf.knnMatch(prev, desc, k=2)
-            mutual = {m.queryIdx for m in bfx.match(prev, desc)}
-            _ = [p[0] for p in knn if len(p) == 2 and p[0].queryIdx in mutual
+            if reference_filter:
+                m1 = bf.match(prev, desc)
+            else:
+                knn = bf.knnMatch(prev, desc, k=2)
+                mutual = bfx.match(prev, desc)
+        t_total += time.perf_counter() - t0
+        if knn is not None:   # outside the clock: Lowe + mutual composition in Python
+            ok = {m.queryIdx for m in mutual}
+            _ = [p[0] for p in knn if len(p) == 2 and p[0].queryIdx in ok
                  and np.float32(p[0].distance) < np.float32(RATIO) * np.float32(p[1].distance)]
         prev = desc
-    return time.perf_counter() - t0, len(frames)
+    return t_total, len(frames)
 
 
-def cpu_baseline(frames_sample, threads):
+def cpu_baseline(frames, threads, budget_s=12.0):
+    """cv2 on the host cores on a bounded prefix of the same sequence: all cores and one thread."""
     import cv2
-    cpu_pass(frames_sample[:3], threads)  # warm-up
-    dt, n = cpu_pass(frames_sample, threads)
+    cpu_pass(frames[:3], threads)  # warm-up
+    dt, n = cpu_pass(frames[:min(len(frames), 400)], threads)
+    n1 = max(8, min(len(frames), int(budget_s * (n / dt) / max(threads, 1) * 1.5)))
+    dt1, n1 = cpu_pass(frames[:n1], 1)
+    dtr, nr = cpu_pass(frames[:min(len(frames), 200)], threads, reference_filter=True)
     return {"value": n / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
-            "sample": "cv2 %s ORB_create(nfeatures=2000).detectAndCompute + BFMatcher knnMatch(k=2) + crossCheck match "
-                      "+ Lowe 0.75 on the first %d frames of the same sequence, %d OpenCV threads, %.1f s"
-                      % (cv2.__version__, n, threads, dt)}
+            "sample": "cv2 %s ORB_create(nfeatures=2000).detectAndCompute + BFMatcher knnMatch(k=2) + crossCheck match on "
+                      "the first %d frames of the same sequence, %d OpenCV threads, %.1f s (Python-side Lowe / mutual "
+                      "filtering outside the clock)" % (cv2.__version__, n, threads, dt),
+            "one_thread": {"value": n1 / dt1, "unit": "frames/s", "cores": 1,
+                           "sample": "same, cv2.setNumThreads(1), first %d frames, %.1f s" % (n1, dt1)},
+            "reference_faithful": {"value": nr / dtr, "unit": "frames/s", "cores": threads,
+                                   "sample": "the reference's own loop: ORB::create_def() (500 features) + match (k=1) + "
+                                             "filter_good_matches(2.0) source, first %d frames, %.1f s" % (nr, dtr)}}
 
 
 def run_reference(args, rank, world):
@@ -187,10 +224,10 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD % T_SEQ, "sample_frames_per_step": nsample},
+        "config": make_config(args),
         "cpu_baseline": {"value": val, "unit": "frames/s", "cores": threads, "kind": "reference",
-                         "sample": "cv2 %s (the OpenCV code the reference binds) on %d frames per step, %d threads"
-                                   % (cv2.__version__, nsample, threads)},
+                         "sample": "cv2 %s (the OpenCV code the reference binds) on the first %d frames of the sequence "
+                                   "per step, %d threads" % (cv2.__version__, nsample, threads)},
         "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -222,6 +259,151 @@ def fast_tiles(h, w):
     return n
 
 
+def sub_hd(args, torch, dist, world, local_rank, synth, barrier):
+    """configs[2] shape: 1920x1080 frames, nfeatures 5000, per-GPU batch (sequence-sharded like the main workload)."""
+    from slam_rs_b200.frontend import NativeSequence
+    T, w, h, nf = args.hd_frames, 1920, 1080, 5000
+    base = np.stack([synth.frame(h, w, 200 + i + 100 * local_rank) for i in range(min(T, 12))])
+    frames = np.concatenate([base] * (-(-T // len(base))))[:T].copy()
+    for i in range(T):  # distinct frames: a per-frame brightness offset keeps the repeated textures from being identical
+        frames[i] = np.clip(frames[i].astype(np.int16) + (i // len(base)) * 3, 0, 255).astype(np.uint8)
+    ns = NativeSequence(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=max(T // 4, 1), device=local_rank,
+                        ratio=RATIO, cross_check=True)
+    pinned = torch.from_numpy(frames).pin_memory()
+    dev = torch.from_numpy(frames).cuda(local_rank)
+    out = ns.alloc_host_outputs()
+    res = {}
+    for name, run in (("value", lambda: ns.run_device(dev)), ("e2e", lambda: ns.run_host(pinned, out))):
+        for _ in range(3):
+            run()
+        ns.sync()
+        barrier()
+        ns.set_timing(True)
+        for _ in range(args.hd_passes):
+            run()
+        ns.sync()
+        ms, passes = ns.elapsed()
+        ns.set_timing(False)
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda:%d" % local_rank)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[name] = T * world * passes / (float(t[0]) * 1e-3)
+        res[name + "_ms_per_pass"] = float(t[0]) / passes
+    n = out["n"][:T].numpy()
+    ns.close()
+    return {"workload": "C3 shape: 1920x1080 synthetic frames, nfeatures=5000, %d frames per GPU per pass, frame-to-frame "
+                        "k=2 + cross-check + Lowe" % T, "n_gpus": world, "value": res["value"], "unit": "frames/s",
+            "ms_per_pass": res["value_ms_per_pass"], "e2e": {"value": res["e2e"], "ms_per_pass": res["e2e_ms_per_pass"],
+                                                             "api": "orbx_sequence_run_host"},
+            "keypoints_per_frame": float(n.mean()), "l2": "inputs larger than L2 (%.0f MB per pass)" % (T * w * h / 1e6)}
+
+
+def sub_map(args, torch, world, synth):
+    """configs[3]: 1 M map descriptors (train, resident on every GPU, one NCCL broadcast) vs 5000 frame descriptors
+    (query, sharded over the GPUs), k = 2 - through the C ABI's multi-GPU entry (orbx_comm_*): ONE process (this rank 0)
+    drives all `world` GPUs, the other ranks of the bench wait.  Strong scaling: 5e9 pairs per step whatever N."""
+    from slam_rs_b200.mapmatch import ShardedMatcher
+    rows, nq, nframes = 1_000_000, 5000, 4
+    m, _ = synth.map_and_frame_descriptors(rows, nq, f=0)
+    rng = np.random.default_rng(8)
+    frames = []
+    for f in range(nframes):
+        pick = rng.choice(rows, nq // 2, replace=False)
+        flips = rng.random((nq // 2, 256)) < 0.1
+        noisy = m[pick] ^ np.packbits(flips, axis=1, bitorder="little")
+        frames.append(np.concatenate([noisy, rng.integers(0, 256, (nq - nq // 2, 32), dtype=np.uint8)]))
+    sm = ShardedMatcher(list(range(world)))
+    t0 = time.perf_counter()
+    sm.set_train(m)
+    bcast_ms = (time.perf_counter() - t0) * 1e3
+    q = [torch.from_numpy(f).cuda(0) for f in frames]
+    out = torch.zeros((nq, 2, 16), dtype=torch.uint8, device="cuda:0")
+    cnt = torch.zeros((nq,), dtype=torch.int32, device="cuda:0")
+    torch.cuda.synchronize()
+    for i in range(3):
+        sm.knn_match_device(q[i % nframes], out, cnt)
+    sm.sync()
+    sm.set_timing(True)
+    t0 = time.perf_counter()
+    for i in range(args.map_steps):
+        sm.knn_match_device(q[i % nframes], out, cnt)
+    sm.sync()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    ms, calls, k0 = sm.timing()
+    # end to end: query descriptors in host memory, records back in host memory
+    sm.set_timing(False)
+    t0 = time.perf_counter()
+    for i in range(args.map_steps):
+        knn, c = sm.knn_match(frames[i % nframes])
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    sm.close()
+    step = ms / max(calls, 1)
+    return {"workload": "C4 map-to-frame: 1M map descriptors resident on every GPU (one ncclBroadcast per map update) vs "
+                        "5000 frame descriptors, query rows sharded over the GPUs, k=2; records stored straight into GPU 0's "
+                        "buffer through peer-mapped pointers", "api": "orbx_comm_knn_match2 (single process, rank 0)",
+            "n_gpus": world, "pairs_per_s": float(rows) * nq / (step * 1e-3), "unit": "pairs/s", "scaling": "strong",
+            "ms_per_step": step, "kernel_ms": k0 / max(calls, 1), "comm_ms": max(step - k0 / max(calls, 1), 0.0),
+            "host_ms_per_step": wall_ms / args.map_steps, "train_broadcast_ms": bcast_ms,
+            "e2e": {"pairs_per_s": float(rows) * nq / (e2e_ms / args.map_steps * 1e-3), "ms_per_step": e2e_ms / args.map_steps,
+                    "h2d_bytes_per_step": nq * 32, "d2h_bytes_per_step": nq * (2 * 16 + 4)},
+            "steps": args.map_steps, "timer": "CUDA events on GPU 0's stream: queries staged -> every rank's records landed"}
+
+
+def sub_latency(args, orbx, synth, local_rank):
+    """configs[0]: two 1241x376 frames, per-call latency through the per-frame API with HOST buffers - what every
+    reference caller does (examples/visual_odometry.rs:102-107, one frame at a time) - beside cv2 on the host."""
+    import cv2
+    a, b = synth.frame(H_IMG, W_IMG, 0), synth.frame(H_IMG, W_IMG, 1)
+    det = orbx.OrbDetector(NFEAT, device=local_rank, max_width=W_IMG, max_height=H_IMG)
+    m = orbx.FeatureMatcher(device=local_rank, cross_check=True)
+
+    def ours():
+        _, d1 = det.detect_and_compute(a)
+        _, d2 = det.detect_and_compute(b)
+        knn, cnt = m.knn_match(d1, d2)
+        return m.ratio_test(knn, cnt, RATIO)
+
+    def timed(fn, n):
+        ts = []
+        for _ in range(n):
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e6)
+        ts = np.sort(np.array(ts))
+        return float(ts[len(ts) // 2]), float(ts[min(len(ts) - 1, int(len(ts) * 0.99))])
+
+    res = {}
+    for graph in (0, 1):
+        try:
+            det.set_graph(bool(graph))
+        except Exception:
+            if graph:
+                continue
+        for _ in range(20):
+            ours()
+        p50, p99 = timed(ours, args.latency_iters)
+        res["graph" if graph else "stream"] = {"p50_us": p50, "p99_us": p99}
+    good = ours()
+    threads = os.cpu_count() or 1
+    cv2.setNumThreads(threads)
+    orb = cv2.ORB_create(nfeatures=NFEAT)
+    bf, bfx = cv2.BFMatcher(cv2.NORM_HAMMING, False), cv2.BFMatcher(cv2.NORM_HAMMING, True)
+
+    def ref():
+        _, d1 = orb.detectAndCompute(a, None)
+        _, d2 = orb.detectAndCompute(b, None)
+        bf.knnMatch(d1, d2, k=2)
+        bfx.match(d1, d2)
+
+    for _ in range(3):
+        ref()
+    c50, c99 = timed(ref, 20)
+    return {"workload": "C1: ORB nfeatures=2000 on two 1241x376 frames + BFMatcher k=2 + cross-check + Lowe, one call per "
+                        "frame, host buffers in and out", "unit": "us per frame pair",
+            "ours": res, "good_matches": int(len(good)),
+            "cv2": {"p50_us": c50, "p99_us": c99, "cores": threads}, "iters": args.latency_iters}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -232,22 +414,23 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     import slam_rs_b200 as orbx
-    from slam_rs_b200.frontend import SequenceFrontEnd
+    from slam_rs_b200.frontend import SequenceFrontEnd, NativeSequence
     synth = load_synth()
 
-    T = args.frames
+    T, P = args.frames, args.passes
     if world > 1 and args.numa_bind:
         bind_near_gpu(local_rank)  # before the pinned buffers are first touched
     # every rank owns an independent sequence (canvas seed differs): weak scaling, no collective
     frames = synth.sequence(H_IMG, W_IMG, T, canvas_seed=100 + rank, noise_seed0=1000 + 100000 * rank)
     fe = SequenceFrontEnd(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, device=local_rank,
                           ratio=RATIO, cross_check=True, overlap=args.overlap,
-                          host_chunk=args.host_chunk, dual=args.dual,
+                          host_chunk=args.host_chunk, dual=bool(args.dual and args.torch_e2e),
                           pose=orbx.CameraIntrinsics.kitti() if args.pose else None)
+    if args.matcher != "auto":
+        fe.matcher.set_mode(args.matcher)
     frames_pinned = torch.from_numpy(frames).pin_memory()
     frames_dev = torch.zeros((T, H_IMG, fe.pitch), dtype=torch.uint8, device=dev)
     frames_dev[:, :, :W_IMG].copy_(frames_pinned)
-    host_out = fe.alloc_host_outputs()
     torch.cuda.synchronize()
 
     def barrier():
@@ -256,9 +439,10 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident: warm-up, then K timed steps with per-stage event timers on
+    # ---- device-resident: warm-up, then K timed steps of P passes with per-stage event timers on
     for _ in range(args.warmup):
-        fe.run_device(frames_dev)
+        for _ in range(P):
+            fe.run_device(frames_dev)
     barrier()
     fe.det.set_timing(True)
     fe.matcher.set_timing(True)
@@ -270,7 +454,7 @@ def run_ours(args, rank, world, local_rank):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(args.steps * P):
         fe.run_device(frames_dev)
     e1.record()
     barrier()
@@ -280,51 +464,65 @@ def run_ours(args, rank, world, local_rank):
     match_ms, match_launches = fe.matcher.timing(reset=True)
     fe.det.set_timing(False)
     fe.matcher.set_timing(False)
+    n_dev = np.minimum(fe.n[:T].cpu().numpy().astype(np.int64), fe.cap)
+    n_good_dev = int(fe.n_good[1:T].cpu().numpy().astype(np.int64).sum())
 
-    # ---- end to end through the public API with HOST buffers (pinned): H2D + kernels + D2H per step
-    for _ in range(max(1, args.warmup // 2)):
-        fe.run_host(frames_pinned, host_out)
+    # ---- end to end through the reference-facing plugin call with HOST buffers: orbx_sequence_run_host (csrc/
+    # sequence.cu - the entry a Rust / C++ host binds for the loop of examples/visual_odometry.rs:84-218): pinned host
+    # frames in, keypoints / descriptors / good matches back in pinned host arrays, every pass.  Timed on the device by
+    # the library's own CUDA events (orbx_sequence_elapsed): first upload -> last download.
+    ns = NativeSequence(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, host_chunk=args.host_chunk,
+                        device=local_rank, ratio=RATIO, cross_check=True)
+    host_out = ns.alloc_host_outputs()
+    for _ in range(max(2, args.warmup)):
+        ns.run_host(frames_pinned, host_out)
+    ns.sync()
     barrier()
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e2.record()
-    for _ in range(args.steps):
-        fe.run_host(frames_pinned, host_out)
-    e3.record()
+    ns.set_timing(True)
+    t0 = time.perf_counter()
+    for _ in range(args.steps * P):
+        ns.run_host(frames_pinned, host_out)
+    ns.sync()
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
+    ms_e2e, e2e_passes = ns.elapsed()
+    ns.set_timing(False)
     barrier()
-    ms_e2e = e2.elapsed_time(e3)
     clocks = sampler.stop()
-
-    # ---- optional (--native): the same end-to-end pass scheduled by liborbx itself (orbx_sequence_run_host, the entry a
-    # compiled-language host calls).  The library owns its streams, so this is timed on the host clock between device
-    # synchronisations; reported beside, never instead of, the event-timed numbers above.
-    native = None
-    if args.native and not args.pose:
-        import time
-        from slam_rs_b200.frontend import NativeSequence
-        ns = NativeSequence(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, host_chunk=args.host_chunk,
-                            device=local_rank, ratio=RATIO, cross_check=True)
-        for _ in range(max(1, args.warmup // 2)):
-            ns.run_host(frames_pinned, host_out)
-            ns.sync()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            ns.run_host(frames_pinned, host_out)
-        ns.sync()
-        native_ms = (time.perf_counter() - t0) * 1e3
-        barrier()
-        native = {"value": T * world * args.steps / (native_ms * 1e-3), "unit": "frames/s",
-                  "ms_per_step": native_ms / args.steps, "timer": "host clock between device synchronisations (this rank)",
-                  "api": "orbx_sequence_run_host"}
-        ns.close()
-
-    # ---- work accounting
-    n_dev = fe.n[:T].cpu().numpy().astype(np.int64)
-    n_dev = np.minimum(n_dev, fe.cap)
-    pairs_fwd = int(np.sum(n_dev[:-1] * n_dev[1:]))
-    pairs_per_step = 2 * pairs_fwd  # forward k=2 + reverse k=1 (cross-check)
-    K_mean = float(n_dev.mean())
     n_good = int(host_out["n_good"][1:T].numpy().astype(np.int64).sum())
+    e2e_cap = ns.cap
+    ns.close()
+    # H2D / D2H rate of this rank's host link, copying alone (the end-to-end pass at 8 ranks is bound by the box's
+    # aggregate host bandwidth - DESIGN.md §4 - so the line carries the measured rates)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    stage_dev = torch.empty_like(frames_pinned, device=dev)
+    back = torch.empty_like(frames_pinned).pin_memory()
+    stage_dev.copy_(frames_pinned, non_blocking=True)
+    barrier()
+    ev[0].record()
+    stage_dev.copy_(frames_pinned, non_blocking=True)
+    ev[1].record()
+    back.copy_(stage_dev, non_blocking=True)
+    ev[2].record()
+    torch.cuda.synchronize()
+    h2d_gbs = frames_pinned.numel() / (ev[0].elapsed_time(ev[1]) * 1e-3) / 1e9
+    d2h_gbs = frames_pinned.numel() / (ev[1].elapsed_time(ev[2]) * 1e-3) / 1e9
+    del stage_dev, back
+
+    # ---- secondary: the same pass scheduled from Python over torch streams (round 1's e2e path)
+    torch_e2e = None
+    if args.torch_e2e:
+        t_out = fe.alloc_host_outputs()
+        for _ in range(2):
+            fe.run_host(frames_pinned, t_out)
+        barrier()
+        e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e2.record()
+        for _ in range(args.steps):
+            fe.run_host(frames_pinned, t_out)
+        e3.record()
+        barrier()
+        torch_e2e = e2.elapsed_time(e3) / args.steps
+
     cand0 = 0
     try:
         fe.det.detect_and_compute_device(frames_dev[:1], fe.kps[:1], fe.desc[:1], fe.n[:1], width=W_IMG)
@@ -332,48 +530,81 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, ms_e2e, torch_e2e or 0.0, -h2d_gbs, -d2h_gbs], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total, ms_e2e = float(t[0]), float(t[1])
-    frames_all = T * world * args.steps
+    torch_e2e = float(t[2]) if torch_e2e else None
+    h2d_min, d2h_min = -float(t[3]), -float(t[4])
+    passes_all = args.steps * P
+    frames_all = T * world * passes_all
     value = frames_all / (ms_total * 1e-3)
     e2e_value = frames_all / (ms_e2e * 1e-3)
 
+    # ---- sub-measurements the headline does not cover (north_star configs[0], [2], [3]); never fatal
+    subs = {}
+    del fe
+    torch.cuda.empty_cache()
+    if args.subs:
+        try:
+            hd = sub_hd(args, torch, dist, world, local_rank, synth, barrier)
+            if rank == 0:
+                subs["hd"] = hd
+        except Exception as ex:  # noqa: BLE001
+            subs["hd"] = {"error": repr(ex)[:300]}
+        barrier()
+        if rank == 0:
+            for name, fn in (("map", lambda: sub_map(args, torch, world, synth)),
+                             ("latency", lambda: sub_latency(args, orbx, synth, local_rank))):
+                try:
+                    subs[name] = fn()
+                except Exception as ex:  # noqa: BLE001
+                    subs[name] = {"error": repr(ex)[:300]}
+        barrier()
+
     if rank == 0:
-        hbm_peak, peak_kind = measured_peaks()
-        P = sum(pyramid_pixels(H_IMG, W_IMG))
-        frames_timed = T * args.steps
+        hbm_peak, peak_kind, peaks = measured_peaks()
+        P_px = sum(pyramid_pixels(H_IMG, W_IMG))
+        frames_timed = T * passes_all
         popc = None
         import ctypes as C
         v = C.c_double()
         if orbx.lib.orbx_popc_microbench(local_rank, 0, C.byref(v)) == 0:
             popc = v.value
-        alg = {
-            "pyramid": P, "fast": P + 8 * cand0, "brief": 2 * P + 572 * K_mean,
-        }
+        K_mean = float(n_dev.mean())
+        pairs_eval = int(np.sum(n_dev[:-1] * n_dev[1:]))  # (query, train) pairs whose distance is evaluated per pass
+        alg = {"pyramid": P_px, "fast": P_px + 8 * cand0, "brief": 2 * P_px + 572 * K_mean}
         stages = {}
         for name, (ms, ln) in stage.items():
-            stages[name] = {"ms_per_step": ms / args.steps, "launches_per_step": ln / args.steps}
-        stages["hamming"] = {"ms_per_step": match_ms / args.steps, "launches_per_step": match_launches / args.steps}
+            stages[name] = {"ms_per_pass": ms / passes_all, "launches_per_pass": ln / passes_all}
+        stages["hamming"] = {"ms_per_pass": match_ms / passes_all, "launches_per_pass": match_launches / passes_all}
         for name, nbytes in (("pyramid", alg["pyramid"]), ("fast", alg["fast"])):
             gbs = nbytes * frames_timed / (stage[name][0] * 1e-3) / 1e9
             stages[name].update({"bound": "hbm", "achieved_gbs": gbs, "frac": gbs / hbm_peak})
         bb_ms = stage["blur"][0] + stage["brief"][0]
         gbs = alg["brief"] * frames_timed / (bb_ms * 1e-3) / 1e9
-        stages["blur+brief"] = {"ms_per_step": bb_ms / args.steps, "bound": "hbm", "achieved_gbs": gbs,
+        stages["blur+brief"] = {"ms_per_pass": bb_ms / passes_all, "bound": "hbm", "achieved_gbs": gbs,
                                 "frac": gbs / hbm_peak}
-        # S10: the reference does two passes for k=2 + cross-check (forward k=2, reverse k=1): 2 x pairs_fwd
-        # 256-bit comparisons of 8 POPC each are the ALGORITHMIC work.  The kernel evaluates every pair once
-        # (fused reverse best-1) with 5 POPC (carry-save compression), so `frac` against the POPC-pipe peak can
-        # exceed 1; `pipe_util` is the POPC instructions actually issued / peak.
-        pairs_s = pairs_per_step * args.steps / (match_ms * 1e-3)
-        exec_popc_s = pairs_fwd * 5.0 * args.steps / (match_ms * 1e-3)
-        stages["hamming"].update({"bound": "popc", "pairs_per_s": pairs_s, "achieved_tpopc": pairs_s * 8 / 1e12,
-                                  "peak_tpopc": popc / 1e12 if popc else None,
-                                  "frac": (pairs_s * 8 / popc) if popc else None,
-                                  "executed_popc_per_evaluated_pair": 5, "evaluated_pairs_per_step": pairs_fwd,
-                                  "pipe_util": (exec_popc_s / popc) if popc else None})
+        # S10.  Every (query, train) distance is evaluated ONCE per pass (the reverse search of the cross-check reads the
+        # same evaluation), so pairs/s counts evaluated pairs - never forward + reverse.
+        pairs_s = pairs_eval * passes_all / (match_ms * 1e-3)
+        use_mma = args.matcher != "popc"
+        ham = stages["hamming"]
+        ham.update({"pairs_per_s": pairs_s, "evaluated_pairs_per_pass": pairs_eval})
+        if use_mma:
+            # tcgen05 kind::i8: 2 * 288 int8 ops per pair (256 data + 32 key-carrying K); int8 dense peak = 2 x the bf16
+            # rate on sm_100 (no int8 figure in MEASURED_PEAKS.json: 2 x the measured sustained bf16 number is used)
+            tops = pairs_s * 2 * 288 / 1e12
+            peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0))
+            ham.update({"kernel": "hamming_mma_kernel", "bound": "tensor", "achieved_tops": tops, "peak_tops": peak,
+                        "frac": tops / peak, "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops_sustained (%s)" % peak_kind,
+                        "popc_equivalent": {"what": "the same pairs on the XOR+POPC kernel would need 5 POPC each",
+                                            "tpopc_per_s": pairs_s * 5 / 1e12, "popc_peak_tpopc": popc / 1e12 if popc else None}})
+        else:
+            ham.update({"kernel": "hamming_knn_kernel", "bound": "popc", "achieved_tpopc": pairs_s * 5 / 1e12,
+                        "peak_tpopc": popc / 1e12 if popc else None, "frac": (pairs_s * 5 / popc) if popc else None,
+                        "executed_popc_per_pair": 5, "algorithmic_popc_per_pair": 8,
+                        "algorithmic_frac": (pairs_s * 8 / popc) if popc else None})
         traffic = {}
         try:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -381,60 +612,61 @@ def run_ours(args, rank, world, local_rank):
             pass
         # dominant kernel of the step
         dom = max(("pyramid", "fast", "harris", "select", "orient", "blur", "brief", "hamming"),
-                  key=lambda k: stages[k]["ms_per_step"])
+                  key=lambda k: stages[k]["ms_per_pass"])
         kname = {"pyramid": "resize_exact_kernel", "fast": "fast_nms_kernel", "harris": "harris_kernel",
                  "select": "select_kernel", "orient": "orient_kernel", "blur": "blur7_kernel",
-                 "brief": "brief_kernel", "hamming": "hamming_knn_kernel"}[dom]
+                 "brief": "brief_kernel", "hamming": ham.get("kernel", "hamming_knn_kernel")}[dom]
         tr = traffic.get(kname)
-        if dom == "hamming":
-            roof = {"kernel": kname, "bound": "popc", "achieved": pairs_s * 8 / 1e12,
-                    "peak": popc / 1e12 if popc else None, "unit": "TPOPC/s",
-                    "frac": (pairs_s * 8 / popc) if popc else None, "traffic": tr,
-                    "pipe_util": stages["hamming"]["pipe_util"],
+        if dom == "hamming" and use_mma:
+            roof = {"kernel": kname, "bound": "tensor", "achieved": ham["achieved_tops"], "peak": ham["peak_tops"],
+                    "unit": "TOP/s (int8)", "frac": ham["frac"], "traffic": tr, "peak_source": ham["peak_source"],
+                    "avg_launch_ms": match_ms / max(match_launches, 1)}
+        elif dom == "hamming":
+            roof = {"kernel": kname, "bound": "popc", "achieved": ham["achieved_tpopc"], "peak": ham["peak_tpopc"],
+                    "unit": "TPOPC/s", "frac": ham["frac"], "traffic": tr,
                     "peak_source": "orbx_popc_microbench (measured in this run; POPC is 16 lanes/clk/SM)",
                     "avg_launch_ms": match_ms / max(match_launches, 1),
-                    "note": "integer XOR+POPC work: neither HBM nor tensor bound (north_star stage 5); achieved = "
-                            "algorithmic 8 POPC x (forward + reverse) pairs, the kernel issues 5 POPC per pair once"}
-            # the HBM view of the same kernel, for the record: every descriptor row is read once (32 B) and every query
-            # row writes its two DMatch records, its count and one reverse-best word (44 B): far below the HBM roofline
-            ham_bytes = float(np.sum(n_dev)) * (32 + 44) * args.steps
-            ham_gbs = ham_bytes / (match_ms * 1e-3) / 1e9
-            roof["hbm"] = {"bound": "hbm", "achieved": ham_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": ham_gbs / hbm_peak,
-                           "algorithmic_bytes_per_launch": ham_bytes / max(match_launches, 1), "traffic": tr,
-                           "peak_source": "MEASURED_PEAKS.json hbm_gbs (%s)" % peak_kind}
+                    "note": "integer XOR+POPC work: neither HBM nor tensor bound; achieved = POPC instructions issued "
+                            "(5 per evaluated pair) / s, frac = POPC-pipe utilisation"}
         else:
             key = {"blur": "blur+brief", "brief": "blur+brief"}.get(dom, dom)
-            s = stages.get(key, {})
+            sg = stages.get(key, {})
             nl = max(stage[dom][1], 1)
-            roof = {"kernel": kname, "bound": "hbm", "achieved": s.get("achieved_gbs"), "peak": hbm_peak, "unit": "GB/s",
-                    "frac": s.get("frac"), "traffic": tr, "peak_source": "MEASURED_PEAKS.json hbm_gbs (%s)" % peak_kind,
+            roof = {"kernel": kname, "bound": "hbm", "achieved": sg.get("achieved_gbs"), "peak": hbm_peak, "unit": "GB/s",
+                    "frac": sg.get("frac"), "traffic": tr, "peak_source": "MEASURED_PEAKS.json hbm_gbs (%s)" % peak_kind,
                     "avg_launch_ms": stage[dom][0] / nl,
                     "algorithmic_bytes_per_launch": (alg.get(dom, 0) * frames_timed / nl) if dom in alg else None}
             if dom == "fast":
-                # algorithmic ALU work of FAST: 40 packed 3-input min/max lane-ops per scored pixel, 609 tiles x 64x32
-                # scored pixels per 1241x376 frame; ALU-pipe peak = 64 lanes/clk/SM (scripts/exp/pipe_exp.cu)
                 sm_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
                 tiles = fast_tiles(H_IMG, W_IMG)
                 ops = tiles * 64 * 32 * 40.0 * frames_timed / (stage["fast"][0] * 1e-3)
                 roof["alu"] = {"achieved": ops / 1e12, "peak": 148 * 64 * sm_clk / 1e12, "unit": "T lane-ops/s",
                                "frac": ops / (148 * 64 * sm_clk), "what": "VIMNMX3.S16x2 of the two 9-of-16 arc networks"}
-                # FAST-9 needs 160 VIMNMX3.S16x2 per 4 pixels (two 9-of-16 sliding min/max networks): its floor on
-                # this chip is the ALU pipe (64 lanes/clk/SM, scripts/exp/pipe_exp.cu), not HBM
-                roof["note"] = ("ALU-pipe bound: 40 packed min/max per pixel; ncu sm__pipe_alu ~75 % busy, DRAM ~3 % "
-                                "(profiles/)")
+                roof["note"] = "instruction-issue / ALU-pipe bound (DRAM ~4 %): see profiles/README.md"
+        cfg = make_config(args)
+        h2d_step = T * H_IMG * W_IMG * P
+        d2h_step = T * (4 + e2e_cap * (28 + 32 + 16) + 4) * P
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD % T, "frames_per_gpu": T, "nfeatures": NFEAT, "chunk": args.chunk, "pose_stage": bool(args.pose), "host_chunk": args.host_chunk, "e2e_streams": 2 if args.dual else 1,
-                       "l2": "inputs larger than L2 (%.0f MB of frames per pass)" % (T * H_IMG * fe.pitch / 1e6),
-                       "keypoints_per_frame": K_mean, "fast_candidates_frame0": cand0,
-                       "good_matches_per_pair": n_good / max(T - 1, 1)},
-            "hamming_pairs_per_s": pairs_s * world, "hamming_pairs_per_step": pairs_per_step,
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": fe.h2d_bytes(T),
-                    "d2h_bytes_per_step": fe.d2h_bytes(T), "ms_per_step": ms_e2e / args.steps},
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
+            "workload_stats": {"chunk": args.chunk, "host_chunk": args.host_chunk, "pose_stage": bool(args.pose),
+                               "matcher_kernel": ham.get("kernel"), "keypoints_per_frame": K_mean,
+                               "fast_candidates_frame0": cand0, "good_matches_per_pair": n_good / max(T - 1, 1),
+                               "good_matches_per_pair_device_pass": n_good_dev / max(T - 1, 1),
+                               "ms_per_pass": ms_total / passes_all, "timed_region_s": ms_total * 1e-3},
+            "hamming_pairs_per_s": pairs_s * world, "hamming_pairs_per_step": pairs_eval * P,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step,
+                    "ms_per_step": ms_e2e / args.steps, "ms_per_pass": ms_e2e / passes_all,
+                    "api": "orbx_sequence_run_host",
+                    "timer": "CUDA events inside liborbx (orbx_sequence_elapsed: first upload -> last download), max over ranks",
+                    "host_wall_ms_per_pass_rank0": e2e_wall_ms / passes_all,
+                    "h2d_gbs_effective_per_rank": h2d_step / P / (ms_e2e / passes_all * 1e-3) / 1e9,
+                    "d2h_gbs_effective_per_rank": d2h_step / P / (ms_e2e / passes_all * 1e-3) / 1e9,
+                    "host_link_alone_gbs": {"h2d_min_over_ranks": h2d_min, "d2h_min_over_ranks": d2h_min},
+                    **({"torch_scheduled_ms_per_pass": torch_e2e} if torch_e2e else {})},
             "gpu_launches": int(launches), "roofline": roof, "stages": stages, "clocks": clocks,
-            **({"e2e_native": native} if native else {}),
+            **subs,
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline(frames[:args.cpu_frames], os.cpu_count() or 1)
@@ -604,7 +836,21 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--frames", type=int, default=T_SEQ, help="frames per GPU per step")
+    ap.add_argument("--frames", type=int, default=T_SEQ, help="frames of the sequence (per GPU)")
+    ap.add_argument("--passes", type=int, default=8,
+                    help="passes over the sequence per step (a step of 8 x 1000 frames keeps the timed region of a "
+                         "--steps 20 run above 2 s)")
+    ap.add_argument("--matcher", default="auto", choices=["auto", "popc", "mma"],
+                    help="Hamming kernel: auto = tcgen05 int8 tensor-core kernel for batches (default), popc = XOR+POPC")
+    ap.add_argument("--subs", type=int, default=1,
+                    help="1: also run the sub-measurements hd (configs[2]), map (configs[3], orbx_comm over all GPUs) and "
+                         "latency (configs[0]) after the headline and attach them to the line")
+    ap.add_argument("--hd-frames", type=int, default=48)
+    ap.add_argument("--hd-passes", type=int, default=5)
+    ap.add_argument("--map-steps", type=int, default=20)
+    ap.add_argument("--latency-iters", type=int, default=200)
+    ap.add_argument("--torch-e2e", type=int, default=1,
+                    help="1: also time the Python / torch-stream scheduled end-to-end pass (secondary key)")
     ap.add_argument("--size", default="kitti", choices=["kitti", "hd"],
                     help="hd: 1920x1080 frames, nfeatures=5000 (BASELINE configs[2] shape; not the headline metric)")
     ap.add_argument("--chunk", type=int, default=1000, help="frames per extraction launch (device-resident pass)")
@@ -617,8 +863,7 @@ def main():
     ap.add_argument("--pose", action="store_true",
                     help="also run PoseEstimator (essential-matrix RANSAC + recoverPose, SURVEY 8 f2) on every pair inside the "
                          "timed region; not part of the headline metric")
-    ap.add_argument("--native", action="store_true",
-                    help="also time the end-to-end pass through the library-scheduled pipeline (orbx_sequence_run_host)")
+    ap.add_argument("--native", action="store_true", help="(kept for old command lines: the e2e leg is always native now)")
     ap.add_argument("--numa-bind", type=int, default=1, help="N>1: bind each rank to its GPU's local CPUs")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "map"],
                     help="sequence = configs[1] (default, the metric's workload); map = configs[3] map-to-frame matching")

@@ -103,6 +103,10 @@ int orbx_detect_and_compute_batch_bgr(orbx_detector* d, const uint8_t* imgs, int
 int orbx_detector_sync(orbx_detector* d);
 /* run on a caller-owned CUDA stream (cudaStream_t as void*); NULL restores the handle's own stream */
 int orbx_detector_set_stream(orbx_detector* d, void* stream);
+/* enable=1: single-frame calls with host buffers (orbx_detect / orbx_detect_and_compute - the shape of every reference
+ * call site, examples/visual_odometry.rs:102) replay a CUDA graph captured once per (w, h, cap): one graph launch instead
+ * of ~13 dependent kernel launches, three copies and a memset.  Results are byte-identical to the stream path. */
+int orbx_detector_set_graph(orbx_detector* d, int enable);
 
 /* Stage access for parity tests and profiling (device buffers owned by the handle, valid until
  * the next call): level geometry and pointers of the pyramid (blurred=0) or of the blurred
@@ -189,7 +193,12 @@ int orbx_extract_matched_points_batch(orbx_matcher* m, const orbx_keypoint* kp1,
                                       const orbx_dmatch* matches, const int* n_dev, int npairs, int max_rows,
                                       float* pts1, float* pts2, int* bad_dev);
 
-/* matcher timing: accumulated ms / launches of the Hamming kernel */
+/* Which kernel runs the Hamming search: 0 = automatic (default: the tcgen05 int8 tensor-core kernel, csrc/match_mma.cu,
+ * for problems of >= 2^27 descriptor pairs per call, the XOR+POPC kernel below that), 1 = POPC kernel only, 2 =
+ * tensor-core kernel always.  Results are bit-identical; the environment variable ORBX_MATCHER=popc|mma sets the
+ * default of new handles. */
+int orbx_matcher_set_mode(orbx_matcher* m, int mode);
+/* matcher timing: accumulated ms / launches of the Hamming search (expansion + kernel + merge) */
 int orbx_matcher_set_timing(orbx_matcher* m, int enable);
 int orbx_matcher_timing(orbx_matcher* m, float* ms, int* launches, int reset);
 

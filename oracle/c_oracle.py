@@ -27,3 +27,17 @@ def knn(q, t, k):
         _lib().hamming_knn(q.ctypes.data, len(q), t.ctypes.data if len(t) else None, len(t), k, idx.ctypes.data,
                            dist.ctypes.data)
     return idx, dist, np.full(len(q), min(k, len(t)), np.int32)
+
+
+def knn_mt(q, t, k, threads=None):
+    """knn() over query chunks on several host threads (ctypes drops the GIL): the full-size checks of tests/."""
+    from concurrent.futures import ThreadPoolExecutor
+    threads = threads or min(32, os.cpu_count() or 1)
+    q = np.ascontiguousarray(q, np.uint8)
+    if len(q) < 4 * threads:
+        return knn(q, t, k)
+    bounds = np.linspace(0, len(q), threads + 1).astype(int)
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(lambda ab: knn(q[ab[0]:ab[1]], t, k), zip(bounds[:-1], bounds[1:])))
+    return (np.concatenate([p[0] for p in parts]), np.concatenate([p[1] for p in parts]),
+            np.concatenate([p[2] for p in parts]))

@@ -56,6 +56,7 @@ def _load():
         "orbx_detect_and_compute_batch_bgr": (i, [vp, vp, i, i, sz, sz, i, vp, vp, i, vp]),
         "orbx_detector_sync": (i, [vp]),
         "orbx_detector_set_stream": (i, [vp, vp]),
+        "orbx_detector_set_graph": (i, [vp, i]),
         "orbx_detector_level_info": (i, [vp, i, i, ip, ip, C.POINTER(sz), C.POINTER(sz), C.POINTER(vp)]),
         "orbx_detector_read_level": (i, [vp, i, i, i, vp, sz]),
         "orbx_detector_candidates": (i, [vp, i, i, vp, i, ip]),
@@ -101,6 +102,7 @@ def _load():
         "orbx_filter_good_matches_batch": (i, [vp, vp, vp, i, i, f, vp, vp]),
         "orbx_extract_matched_points": (i, [vp, vp, i, vp, i, vp, i, vp, vp]),
         "orbx_extract_matched_points_batch": (i, [vp, vp, vp, vp, vp, C.c_size_t, vp, vp, i, i, vp, vp, vp]),
+        "orbx_matcher_set_mode": (i, [vp, i]),
         "orbx_matcher_set_timing": (i, [vp, i]),
         "orbx_matcher_timing": (i, [vp, C.POINTER(f), ip, i]),
         "orbx_sequence_create": (i, [i, i, i, i, i, i, i, f, i, C.POINTER(vp)]),

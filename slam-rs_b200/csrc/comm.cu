@@ -116,6 +116,15 @@ void slice(int nq, int ndev, int r, int* lo, int* hi) {
   *hi = std::min(nq, (r + 1) * per);
 }
 
+// the resident train set changed: every rank expands its copy once for the tensor-core kernel (in stream order behind
+// the broadcast), so that the per-frame calls only expand their query slice
+int cache_train(orbx_comm* c) {
+  if ((double)c->nt * 64 < 134217728.0) return ORBX_OK;  // small train sets go to the POPC kernel anyway
+  for (int r = 0; r < c->ndev; ++r)
+    if (int rc = orbx::matcher_cache_train(c->m[r], c->train[r], c->nt)) return rc;
+  return ORBX_OK;
+}
+
 int run_sharded(orbx_comm* c, int K, const uint8_t* q, int nq, orbx_dmatch* out, int* counts_or_n) {
   if (!c || nq < 0 || (nq > 0 && (!q || !out))) {
     set_error("orbx_comm match: bad argument");
@@ -332,11 +341,12 @@ int orbx_comm_set_train(orbx_comm* c, const uint8_t* train, int nt) {
     c->train_cap = bytes;
   }
   c->nt = nt;
+  for (int r = 0; r < c->ndev; ++r) orbx::matcher_cache_train(c->m[r], nullptr, 0);
   if (nt == 0) return ORBX_OK;
   // to rank 0 (host or device source), then one broadcast: every other rank receives over NVLink
   ORBX_CUDA(cudaSetDevice(c->dev[0]));
   ORBX_CUDA(cudaMemcpyAsync(c->train[0], train, bytes, cudaMemcpyDefault, c->st[0]));
-  if (c->ndev == 1) return ORBX_OK;
+  if (c->ndev == 1) return cache_train(c);
   if (c->virtual_ranks) {
     ORBX_CUDA(cudaEventRecord(c->ready, c->st[0]));
     for (int r = 1; r < c->ndev; ++r) {
@@ -344,13 +354,13 @@ int orbx_comm_set_train(orbx_comm* c, const uint8_t* train, int nt) {
       ORBX_CUDA(cudaStreamWaitEvent(c->st[r], c->ready, 0));
       ORBX_CUDA(cudaMemcpyAsync(c->train[r], c->train[0], bytes, cudaMemcpyDefault, c->st[r]));
     }
-    return ORBX_OK;
+    return cache_train(c);
   }
   ORBX_NCCL(nccl().GroupStart());
   for (int r = 0; r < c->ndev; ++r)
     ORBX_NCCL(nccl().Broadcast(c->train[0], c->train[r], bytes, kNcclUint8, 0, c->nccl_comm[r], c->st[r]));
   ORBX_NCCL(nccl().GroupEnd());
-  return ORBX_OK;
+  return cache_train(c);
 }
 
 int orbx_comm_knn_match2(orbx_comm* c, const uint8_t* q, int nq, orbx_dmatch* out, int* n_per_q) {

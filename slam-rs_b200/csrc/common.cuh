@@ -66,6 +66,7 @@ constexpr int kMaxLevels = 8;
 int match_slice(orbx_matcher* m, int K, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* counts,
                 int index_base);
 cudaStream_t matcher_stream(orbx_matcher* m);
+int matcher_cache_train(orbx_matcher* m, const uint8_t* t, int nt);
 
 // CUDA-event stage timer: events are recorded on the launching stream around each stage and only
 // read back (with a synchronise) when the caller asks for the totals.

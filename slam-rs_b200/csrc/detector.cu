@@ -54,6 +54,21 @@ struct orbx_detector {
   size_t lvl_off[kMaxLevels];  // byte offset of level l inside pyr / blr for the last batch
   std::vector<int> host_n;
   EventTimer timer;
+  // CUDA-graph replay of the single-frame host call (orbx_detector_set_graph): upload, the ~13 dependent launches and
+  // the download of one (w, h, cap, descriptors?) configuration captured once and replayed with one graph launch
+  struct GraphEntry {
+    int w, h, cap, want_desc;
+    cudaGraphExec_t exec;
+  };
+  bool use_graph = false;
+  std::vector<GraphEntry> graphs;
+  uint8_t* pin_img = nullptr;  // pinned staging: the frame, tightly packed
+  uint8_t* pin_out = nullptr;  // pinned staging: n, flags, cap keypoints, cap descriptors
+  size_t pin_img_bytes = 0, pin_out_bytes = 0;
+  void drop_graphs() {
+    for (auto& g : graphs) cudaGraphExecDestroy(g.exec);
+    graphs.clear();
+  }
 };
 
 namespace {
@@ -239,6 +254,9 @@ void orbx_detector_destroy(orbx_detector* d) {
   cudaSetDevice(d->device);
   if (d->stream) cudaStreamSynchronize(d->stream);
   d->timer.destroy();
+  d->drop_graphs();
+  if (d->pin_img) cudaFreeHost(d->pin_img);
+  if (d->pin_out) cudaFreeHost(d->pin_out);
   cudaFree(d->pyr);
   cudaFree(d->blr);
   cudaFree(d->cand);
@@ -283,6 +301,14 @@ int orbx_detector_sync(orbx_detector* d) {
 int orbx_detector_set_stream(orbx_detector* d, void* stream) {
   if (!d) return ORBX_E_BADARG;
   d->stream = stream ? (cudaStream_t)stream : d->own_stream;
+  d->drop_graphs();  // captured for the previous stream's device context; cheap to rebuild
+  return ORBX_OK;
+}
+
+int orbx_detector_set_graph(orbx_detector* d, int enable) {
+  if (!d) return ORBX_E_BADARG;
+  d->use_graph = enable != 0;
+  if (!d->use_graph) d->drop_graphs();
   return ORBX_OK;
 }
 

@@ -18,12 +18,14 @@
 // Integer work only; tensor cores are deliberately not used.
 #include <cooperative_groups.h>
 #include <cuda_pipeline.h>
+#include <string.h>
 
 #include <algorithm>
 #include <mutex>
 #include <vector>
 
 #include "common.cuh"
+#include "match_mma.cuh"
 
 namespace orbx {
 
@@ -39,14 +41,18 @@ struct orbx_matcher {
   int num_sms = 148;
   cudaStream_t own_stream = nullptr, stream = nullptr;
   // staging for host-pointer calls and partial results; grown on demand
-  void* buf[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  size_t cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  void* buf[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t cap[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int mode = 0;  // 0 = auto (tensor-core kernel for large problems), 1 = POPC kernel only, 2 = tensor-core kernel always
+  // resident train set whose expanded form in buf[B_EXPT] is current (orbx_comm_set_train / matcher_cache_train)
+  const uint8_t* cached_t = nullptr;
+  int cached_nt = 0;
   orbx::EventTimer timer;
 };
 
 namespace orbx {
 
-enum { B_Q = 0, B_T, B_OUT, B_CNT, B_PART, B_REV, B_OUT2, B_CNT2 };
+enum { B_Q = 0, B_T, B_OUT, B_CNT, B_PART, B_REV, B_OUT2, B_CNT2, B_EXPQ, B_EXPT };
 
 static int ensure(orbx_matcher* m, int which, size_t bytes) {
   if (bytes <= m->cap[which]) return ORBX_OK;
@@ -400,11 +406,79 @@ __global__ void knn2_cross_mask_batch_kernel(const orbx_dmatch* knn2, const unsi
 // host-side launch logic
 // ------------------------------------------------------------------------------------------------
 // fused = also produce the reverse (train -> query) best-1 into a.rev (preset to ~0 by the caller)
+// The same search on the tensor cores (match_mma.cu): expand the descriptor sets to int8 rows, run the tcgen05 kernel
+// into per-split partial keys, and let merge_splits_kernel write the DMatch records exactly as the split POPC path does.
+template <int K>
+static int launch_knn_mma(orbx_matcher* m, MatchArgs a, int npairs, bool fused, int rows_q, int rows_t) {
+  const int rpq = (int)align_up((size_t)rows_q, kMmaTileN), rpt = (int)align_up((size_t)rows_t, kMmaTileN);
+  const size_t eq = mma_expanded_bytes(rpq), et = mma_expanded_bytes(rpt);
+  // frame-to-frame batches: problem p matches set p against set p + 1 of ONE array - expand the npairs + 1 sets once
+  const bool chain = npairs > 1 && a.nq_dev && a.nt_dev && a.q_stride == a.t_stride && a.t == a.q + a.q_stride &&
+                     a.nt_dev == a.nq_dev + 1;
+  int rc;
+  m->timer.begin(0, m->stream);
+  MmaMatchArgs g{};
+  if (chain) {
+    if ((rc = ensure(m, B_EXPQ, eq * (npairs + 1) + 256))) return rc;
+    uint8_t* e = (uint8_t*)m->buf[B_EXPQ];
+    if ((rc = launch_expand_desc(a.q, a.q_stride, a.nq_dev, 0, a.max_rows, npairs + 1, rpq, e, eq, m->stream))) return rc;
+    g.ea = e;
+    g.eb = e + eq;
+    g.ea_stride = g.eb_stride = eq;
+  } else {
+    if ((rc = ensure(m, B_EXPQ, eq * npairs + 256))) return rc;
+    if (et * npairs + 256 > m->cap[B_EXPT]) m->cached_t = nullptr;  // the buffer is about to be replaced
+    if ((rc = ensure(m, B_EXPT, et * npairs + 256))) return rc;
+    if ((rc = launch_expand_desc(a.q, a.q_stride, a.nq_dev, a.nq_fixed, a.max_rows, npairs, rpq, (uint8_t*)m->buf[B_EXPQ], eq,
+                                 m->stream)))
+      return rc;
+    const bool cached = npairs == 1 && !a.nt_dev && m->cached_t == a.t && m->cached_nt == a.nt_fixed && m->buf[B_EXPT];
+    if (!cached) {
+      m->cached_t = nullptr;
+      if ((rc = launch_expand_desc(a.t, a.t_stride, a.nt_dev, a.nt_fixed, a.max_rows, npairs, rpt, (uint8_t*)m->buf[B_EXPT],
+                                   et, m->stream)))
+        return rc;
+    }
+    g.ea = (const uint8_t*)m->buf[B_EXPQ];
+    g.eb = (const uint8_t*)m->buf[B_EXPT];
+    g.ea_stride = eq;
+    g.eb_stride = et;
+  }
+  g.nq_dev = a.nq_dev, g.nt_dev = a.nt_dev, g.nq_fixed = a.nq_fixed, g.nt_fixed = a.nt_fixed;
+  g.max_rows = a.max_rows;
+  g.max_rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
+  g.npairs = npairs;
+  g.mtiles = div_up(rows_q, 128);
+  // about four units per SM; a unit streams its whole train range, so only large train sets are split
+  const int ttiles = div_up(rows_t, kMmaTileN);
+  const long units = (long)npairs * g.mtiles;
+  int splits = units >= (long)m->num_sms * 2 ? 1 : (int)std::min<long>(ttiles, ((long)m->num_sms * 4 + units - 1) / units);
+  g.tiles_per_split = div_up(ttiles, std::max(splits, 1));
+  g.nsplits = div_up(ttiles, g.tiles_per_split);
+  g.K = K;
+  if ((rc = ensure(m, B_PART, (size_t)npairs * g.nsplits * a.max_rows * K * sizeof(unsigned long long)))) return rc;
+  g.part = (unsigned long long*)m->buf[B_PART];
+  g.rev = fused ? a.rev : nullptr;
+  g.rev_rows = a.rev_rows;
+  if ((rc = launch_hamming_mma(g, m->num_sms, m->stream))) return rc;
+  a.part = g.part;
+  a.nsplits = g.nsplits;
+  a.rows_per_split = g.tiles_per_split * kMmaTileN;
+  dim3 g2(div_up(rows_q, 256), npairs);
+  merge_splits_kernel<K><<<g2, 256, 0, m->stream>>>(a);
+  m->timer.end(m->stream);
+  ORBX_LAUNCH_CHECK();
+  return ORBX_OK;
+}
+
 template <int K>
 static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs, bool fused = false) {
   const int rows_q = a.nq_dev ? a.max_rows : a.nq_fixed;
   const int rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
   if (rows_q <= 0 || npairs <= 0) return ORBX_OK;
+  // tensor-core path for problems that fill the chip (>= 2^27 descriptor pairs); the POPC kernel below for small ones
+  if (rows_t > 0 && (m->mode == 2 || (m->mode == 0 && (double)npairs * rows_q * rows_t >= 134217728.0)))
+    return launch_knn_mma<K>(m, a, npairs, fused, rows_q, rows_t);
   const int qtiles = div_up(rows_q, kQPB);
   // about four waves of blocks (10 resident per SM) so that the last, partly filled wave costs little, but never
   // split below one tile
@@ -486,6 +560,23 @@ int match_slice(orbx_matcher* m, int K, const uint8_t* q, int nq, const uint8_t*
 
 cudaStream_t matcher_stream(orbx_matcher* m) { return m->stream; }
 
+// A train set that stays resident (the map of map-to-frame matching): expand it once, asynchronously on the matcher's
+// stream; later single-problem calls with the same (pointer, rows) reuse the expanded copy.  The caller invalidates by
+// calling this again (or with nt = 0) when the contents change.
+int matcher_cache_train(orbx_matcher* m, const uint8_t* t, int nt) {
+  m->cached_t = nullptr;
+  m->cached_nt = 0;
+  if (!t || nt <= 0) return ORBX_OK;
+  ORBX_CUDA(cudaSetDevice(m->device));
+  const int rpt = (int)align_up((size_t)nt, kMmaTileN);
+  const size_t et = mma_expanded_bytes(rpt);
+  if (int rc = ensure(m, B_EXPT, et + 256)) return rc;
+  if (int rc = launch_expand_desc(t, 0, nullptr, nt, nt, 1, rpt, (uint8_t*)m->buf[B_EXPT], et, m->stream)) return rc;
+  m->cached_t = t;
+  m->cached_nt = nt;
+  return ORBX_OK;
+}
+
 }  // namespace orbx
 
 using namespace orbx;
@@ -518,6 +609,7 @@ int orbx_matcher_create(int device, int cross_check, orbx_matcher** out) {
     return ORBX_E_CUDA;
   }
   m->stream = m->own_stream;
+  if (const char* v = getenv("ORBX_MATCHER")) m->mode = !strcmp(v, "popc") ? 1 : (!strcmp(v, "mma") ? 2 : 0);
   *out = m;
   return ORBX_OK;
 }
@@ -527,7 +619,7 @@ void orbx_matcher_destroy(orbx_matcher* m) {
   cudaSetDevice(m->device);
   cudaStreamSynchronize(m->stream);
   m->timer.destroy();
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < 10; ++i)
     if (m->buf[i]) cudaFree(m->buf[i]);
   if (m->own_stream) cudaStreamDestroy(m->own_stream);
   delete m;
@@ -543,6 +635,15 @@ int orbx_matcher_sync(orbx_matcher* m) {
 int orbx_matcher_set_stream(orbx_matcher* m, void* stream) {
   if (!m) return ORBX_E_BADARG;
   m->stream = stream ? (cudaStream_t)stream : m->own_stream;
+  return ORBX_OK;
+}
+
+int orbx_matcher_set_mode(orbx_matcher* m, int mode) {
+  if (!m || mode < 0 || mode > 2) {
+    set_error("orbx_matcher_set_mode: bad argument");
+    return ORBX_E_BADARG;
+  }
+  m->mode = mode;
   return ORBX_OK;
 }
 

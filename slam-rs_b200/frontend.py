@@ -397,6 +397,20 @@ class NativeSequence:
     def sync(self):
         self._check(self._lib.orbx_sequence_sync(self._h))
 
+    def set_reference_filter(self, enable=True, ratio=2.0):
+        """The reference's own loop (visual_odometry.rs:106-107): match_descriptors (k=1) + filter_good_matches(ratio)
+        instead of k=2 + cross-check + Lowe; ``good`` / ``n_good`` then hold that filter's survivors."""
+        self._check(self._lib.orbx_sequence_set_reference_filter(self._h, 1 if enable else 0, float(ratio)))
+
+    def set_timing(self, enable=True):
+        self._check(self._lib.orbx_sequence_set_timing(self._h, 1 if enable else 0))
+
+    def elapsed(self, reset=True):
+        """(device milliseconds from the start of the first pass since the last reset to the end of the last, passes)."""
+        ms, n = self._C.c_float(0), self._C.c_int(0)
+        self._check(self._lib.orbx_sequence_elapsed(self._h, self._C.byref(ms), self._C.byref(n), 1 if reset else 0))
+        return ms.value, n.value
+
     def results_to_host(self, T):
         """Device results of the last pass copied to numpy (synchronises): dict like alloc_host_outputs()."""
         C = self._C

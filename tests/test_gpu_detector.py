@@ -201,6 +201,31 @@ def test_async_overflow_is_clamped_and_reported(orbx):
     det.sync()  # reported once
 
 
+def test_graph_replay_returns_identical_bytes(orbx):
+    """orbx_detector_set_graph: the single-frame host call replayed as one CUDA graph must return the same bytes as the
+    stream path, across repeated calls, a change of image size (tables re-uploaded, graphs dropped), detect-only calls
+    and a capacity retry."""
+    a, b, c = synth.frame(376, 1241, 0), synth.frame(376, 1241, 1), synth.frame(240, 320, 2)
+    ref = orbx.OrbDetector(2000, max_width=1241, max_height=376)
+    det = orbx.OrbDetector(2000, max_width=1241, max_height=376)
+    det.set_graph(True)
+    for img in (a, b, a, c, b, c):
+        k0, d0 = ref.detect_and_compute(img)
+        k1, d1 = det.detect_and_compute(img)
+        assert np.array_equal(k0, k1) and np.array_equal(d0, d1) and len(k0) > 0
+        assert np.array_equal(ref.detect(img), det.detect(img))
+    # more keypoints than the default cap: the graph path reports the needed size like the stream path
+    small = orbx.OrbDetector(100, max_width=320, max_height=240)
+    small.set_graph(True)
+    lat = dot_lattice(240, 320, 8)
+    k, d = small.detect_and_compute(lat)
+    k2, d2 = orbx.OrbDetector(100, max_width=320, max_height=240).detect_and_compute(lat)
+    assert len(k) == 760 and np.array_equal(k, k2) and np.array_equal(d, d2)
+    det.set_graph(False)
+    k1, d1 = det.detect_and_compute(a)
+    assert np.array_equal(k1, ref.detect_and_compute(a)[0])
+
+
 def test_batch_device_pointers_and_pitch(orbx):
     import torch
     h, w, nf, B = 200, 333, 400, 5

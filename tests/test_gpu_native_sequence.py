@@ -62,3 +62,64 @@ def test_native_bad_arguments():
     import torch
     with pytest.raises(s.OrbxError):
         ns.run_device(torch.zeros((5, 240, 320), dtype=torch.uint8, device="cuda"))   # T > max_frames
+
+
+def test_native_reference_filter_mode_and_timing():
+    """orbx_sequence_set_reference_filter: the pairs are matched exactly as the reference's loop does
+    (examples/visual_odometry.rs:106-107: match_descriptors k=1, no cross-check, then filter_good_matches(2.0)),
+    pinned to the oracle's restatement of matcher.rs:24-66; orbx_sequence_elapsed reports the device time of the passes."""
+    import torch
+    from oracle import synth, restated as R
+    import slam_rs_b200 as orbx
+    from slam_rs_b200.frontend import NativeSequence
+    T, h, w, nf = 6, 240, 320, 300
+    seq = synth.sequence(h, w, T, canvas_seed=61)
+    ns = NativeSequence(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=2)
+    ns.set_reference_filter(True, 2.0)
+    out = ns.alloc_host_outputs()
+    ns.set_timing(True)
+    pinned = torch.from_numpy(seq).pin_memory()
+    for _ in range(3):
+        ns.run_host(pinned, out)
+    ns.sync()
+    ms, passes = ns.elapsed()
+    assert passes == 3 and 0 < ms < 10_000
+    n, ng = out["n"].numpy(), out["n_good"].numpy()
+    desc = out["desc"].numpy()
+    good = out["good"].numpy().view(orbx.DMATCH_DTYPE).reshape(T, ns.cap)
+    for t in range(1, T):
+        want = R.filter_good_matches(R.match_k1(desc[t - 1, :n[t - 1]], desc[t, :n[t]]), 2.0)
+        got = good[t, :ng[t]]
+        assert ng[t] == len(want) > 0
+        assert np.array_equal(got["query_idx"], want[:, 0]) and np.array_equal(got["train_idx"], want[:, 1])
+        assert np.array_equal(got["distance"], want[:, 2].astype(np.float32))
+    # back to the north_star composition on the same handle
+    ns.set_reference_filter(False, 2.0)
+    ns.run_host(pinned, out)
+    ns.sync()
+    m = orbx.FeatureMatcher(cross_check=True)
+    knn, cnt = m.knn_match(desc[0, :n[0]], desc[1, :n[1]])
+    lowe = m.ratio_test(knn, cnt, 0.75)
+    g1 = out["good"].numpy().view(orbx.DMATCH_DTYPE).reshape(T, ns.cap)[1, :out["n_good"].numpy()[1]]
+    assert np.array_equal(g1, lowe)
+
+
+def test_native_sequence_reports_tie_flood_truncation():
+    """A frame with more keypoints than the sequence's row capacity (a tie flood, see test_gpu_detector.py) is truncated
+    to the capacity - n never exceeds it - and orbx_sequence_sync returns ORBX_E_CAPACITY once."""
+    import torch
+    from oracle import synth
+    import slam_rs_b200 as orbx
+    from slam_rs_b200.frontend import NativeSequence
+    from tests.test_gpu_detector import dot_lattice
+    T, h, w, nf = 4, 240, 320, 100
+    seq = np.stack([synth.frame(h, w, 70), dot_lattice(h, w, 8), synth.frame(h, w, 71), synth.frame(h, w, 72)])
+    ns = NativeSequence(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=2)
+    out = ns.alloc_host_outputs()
+    ns.run_host(torch.from_numpy(seq).pin_memory(), out)
+    with pytest.raises(orbx.OrbxError) as e:
+        ns.sync()
+    assert e.value.code == -2
+    n = out["n"].numpy()
+    assert n[1] == ns.cap and n.max() <= ns.cap and n[0] > 0 and n[2] > 0
+    ns.sync()                                                                  # reported once
