@@ -7,7 +7,7 @@ sequence: S1-S9 on every frame and the T-1 (t-1 -> t) matching problems (BFMatch
 mutual test + Lowe ratio 0.75).  N>1: every rank owns an independent sequence (weak scaling, no
 data-path collective — SURVEY.md §8e); value = all frames / max-over-ranks time.
 
-A step is `--passes` (8) passes over the resident sequence, so that a --steps 20 run times > 2 s of GPU work.
+A step is `--passes` (10) passes over the resident sequence, so that a --steps 20 run times > 2 s of GPU work.
 `value`: frames resident in HBM, timed with CUDA events.  `e2e`: the same passes through the reference-facing plugin
 call orbx_sequence_run_host (csrc/sequence.cu) with HOST buffers - pinned frames in, keypoints / descriptors / good
 matches back out - timed by the library's own CUDA events.  Attached sub-measurements (`--subs 1`): `hd` (configs[2]
@@ -837,8 +837,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=T_SEQ, help="frames of the sequence (per GPU)")
-    ap.add_argument("--passes", type=int, default=8,
-                    help="passes over the sequence per step (a step of 8 x 1000 frames keeps the timed region of a "
+    ap.add_argument("--passes", type=int, default=10,
+                    help="passes over the sequence per step (a step of 10 x 1000 frames keeps the timed region of a "
                          "--steps 20 run above 2 s)")
     ap.add_argument("--matcher", default="auto", choices=["auto", "popc", "mma"],
                     help="Hamming kernel: auto = tcgen05 int8 tensor-core kernel for batches (default), popc = XOR+POPC")
