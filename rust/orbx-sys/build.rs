@@ -8,7 +8,12 @@ fn main() {
     let out = PathBuf::from(env::var("OUT_DIR").unwrap());
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     let mut objs = vec![];
-    for f in ["api", "match", "detector", "pyramid", "fast", "select", "brief", "ingest", "mapstore", "triangulate", "pose"] {
+    // the source list is the Makefile's (one place to add a file): "SRCS := api.cu match.cu ..."
+    let mk = std::fs::read_to_string(csrc.join("Makefile")).expect("csrc/Makefile");
+    let srcs: Vec<String> = mk.lines().find(|l| l.starts_with("SRCS")).expect("SRCS line")
+        .split(":=").nth(1).unwrap().split_whitespace().map(|f| f.trim_end_matches(".cu").to_string()).collect();
+    println!("cargo:rerun-if-changed={}", csrc.join("Makefile").display());
+    for f in srcs.iter() {
         let src = csrc.join(format!("{f}.cu"));
         let obj = out.join(format!("{f}.o"));
         let st = Command::new(&nvcc)
@@ -26,5 +31,6 @@ fn main() {
     println!("cargo:rustc-link-lib=static=orbx");
     println!("cargo:rustc-link-search=native=/usr/local/cuda/lib64");
     println!("cargo:rustc-link-lib=dylib=cudart");
+    println!("cargo:rustc-link-lib=dylib=dl");  // csrc/comm.cu binds NCCL at run time (dlopen of libnccl.so.2)
     println!("cargo:rustc-link-lib=dylib=stdc++");
 }

@@ -15,20 +15,35 @@ fn err(code: i32) -> Box<dyn Error> {
 /// A borrowed 8-bit single-channel image (what `&Mat` CV_8UC1 is on the reference side).
 pub struct Gray<'a> { pub data: &'a [u8], pub width: i32, pub height: i32, pub pitch: usize }
 
-pub struct OrbDetector { h: *mut sys::orbx_detector, max_features: i32 }
+pub struct OrbDetector { h: *mut sys::orbx_detector, max_features: i32, nfeatures: i32, device: i32, max_w: i32, max_h: i32, graph: bool }
 
 impl OrbDetector {
-    /// detector.rs:15-18 — unlike the reference, `max_features` is honoured.
-    pub fn new(max_features: i32) -> Result<Self, Box<dyn Error>> {
+    /// detector.rs:15-18 - unlike the reference (which forwards to `ORB::create_def()` and keeps 500), `max_features`
+    /// is honoured; `new_reference_faithful` restores the reference's behaviour.  Device scratch is sized on the first
+    /// image (and re-sized when a larger image arrives), not for the 4095 x 4095 maximum.
+    pub fn new(max_features: i32) -> Result<Self, Box<dyn Error>> { Self::with_options(max_features, max_features, 0) }
+    /// `ORB::create_def()` exactly as detector.rs:16: nfeatures stays 500, `max_features` is only echoed (detector.rs:42-44).
+    pub fn new_reference_faithful(max_features: i32) -> Result<Self, Box<dyn Error>> { Self::with_options(max_features, 500, 0) }
+    pub fn with_options(max_features: i32, nfeatures: i32, device: i32) -> Result<Self, Box<dyn Error>> {
+        Ok(Self { h: ptr::null_mut(), max_features, nfeatures, device, max_w: 0, max_h: 0, graph: false })
+    }
+    /// Replay single-frame calls as one CUDA graph (orbx_detector_set_graph): same bytes, lower per-call latency.
+    pub fn set_graph(&mut self, enable: bool) { self.graph = enable; if !self.h.is_null() { unsafe { sys::orbx_detector_set_graph(self.h, enable as i32) }; } }
+    fn ensure(&mut self, w: i32, h: i32) -> Result<(), Box<dyn Error>> {
+        if !self.h.is_null() && w <= self.max_w && h <= self.max_h { return Ok(()); }
+        if !self.h.is_null() { unsafe { sys::orbx_detector_destroy(self.h) }; self.h = ptr::null_mut(); }
         let mut p = unsafe { let mut p = std::mem::zeroed(); sys::orbx_default_params(&mut p); p };
-        p.nfeatures = max_features;
-        let mut h = ptr::null_mut();
-        let rc = unsafe { sys::orbx_detector_create(&p, 0, 4095, 4095, 1, &mut h) };
-        if rc != 0 { return Err(err(rc)); }
-        Ok(Self { h, max_features })
+        p.nfeatures = self.nfeatures;
+        let (mw, mh) = (w.max(self.max_w).max(16), h.max(self.max_h).max(16));
+        let rc = unsafe { sys::orbx_detector_create(&p, self.device, mw, mh, 1, &mut self.h) };
+        if rc != 0 { self.h = ptr::null_mut(); return Err(err(rc)); }
+        self.max_w = mw; self.max_h = mh;
+        if self.graph { unsafe { sys::orbx_detector_set_graph(self.h, 1) }; }
+        Ok(())
     }
     fn run(&mut self, img: &Gray, with_desc: bool) -> Result<(Vec<KeyPoint>, Vec<u8>), Box<dyn Error>> {
-        let mut cap = (self.max_features + self.max_features / 4 + 256) as usize;
+        self.ensure(img.width, img.height)?;
+        let mut cap = (self.nfeatures + self.nfeatures / 4 + 256) as usize;
         loop {
             let mut kps = vec![KeyPoint::default(); cap];
             let mut desc = vec![0u8; if with_desc { cap * 32 } else { 0 }];
@@ -50,17 +65,35 @@ impl OrbDetector {
     /// detector.rs:42-44
     pub fn max_features(&self) -> i32 { self.max_features }
 }
-impl Drop for OrbDetector { fn drop(&mut self) { unsafe { sys::orbx_detector_destroy(self.h) } } }
+impl Drop for OrbDetector { fn drop(&mut self) { if !self.h.is_null() { unsafe { sys::orbx_detector_destroy(self.h) } } } }
 
 pub struct FeatureMatcher { h: *mut sys::orbx_matcher }
 
 impl FeatureMatcher {
-    /// matcher.rs:15-21
-    pub fn new() -> Result<Self, Box<dyn Error>> {
+    /// matcher.rs:15-21: `BFMatcher::create(NORM_HAMMING, crossCheck = false)`
+    pub fn new() -> Result<Self, Box<dyn Error>> { Self::with_options(false, 0) }
+    /// `BFMatcher::create(NORM_HAMMING, crossCheck = true)`: `match_descriptors` keeps mutual nearest pairs only, and
+    /// `knn_match` zeroes the count of queries that fail the mutual test (the north_star's k=2 + cross-check composition)
+    pub fn new_cross_check() -> Result<Self, Box<dyn Error>> { Self::with_options(true, 0) }
+    pub fn with_options(cross_check: bool, device: i32) -> Result<Self, Box<dyn Error>> {
         let mut h = ptr::null_mut();
-        let rc = unsafe { sys::orbx_matcher_create(0, 0, &mut h) };
+        let rc = unsafe { sys::orbx_matcher_create(device, cross_check as i32, &mut h) };
         if rc != 0 { return Err(err(rc)); }
         Ok(Self { h })
+    }
+    /// `BFMatcher::knnMatch(k = 2)`: per query row up to two matches in ascending (distance, train index) order
+    pub fn knn_match(&mut self, desc1: &[u8], desc2: &[u8]) -> Result<Vec<Vec<DMatch>>, Box<dyn Error>> {
+        let (nq, nt) = (desc1.len() / 32, desc2.len() / 32);
+        if nq == 0 { return Ok(Vec::new()); }
+        let mut out = vec![DMatch::default(); nq * 2];
+        let mut cnt = vec![0i32; nq];
+        let rc = unsafe { sys::orbx_knn_match2(self.h, desc1.as_ptr(), nq as i32, desc2.as_ptr(), nt as i32, out.as_mut_ptr(), cnt.as_mut_ptr()) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((0..nq).map(|i| out[2 * i..2 * i + (cnt[i].clamp(0, 2) as usize)].to_vec()).collect())
+    }
+    /// Lowe's ratio test on a `knn_match` result: keeps m[0] iff two matches exist and m[0].distance < ratio * m[1].distance
+    pub fn ratio_test(&self, knn: &[Vec<DMatch>], ratio: f32) -> Vec<DMatch> {
+        knn.iter().filter(|m| m.len() == 2 && m[0].distance < ratio * m[1].distance).map(|m| m[0]).collect()
     }
     /// matcher.rs:24-37 — desc1/desc2: N x 32 bytes; either side empty -> empty result
     pub fn match_descriptors(&mut self, desc1: &[u8], desc2: &[u8]) -> Result<Vec<DMatch>, Box<dyn Error>> {
@@ -202,7 +235,11 @@ impl Sequence {
         if rc != 0 { return Err(err(rc)); }
         Ok(Self { h, width, height })
     }
-    /// `frames`: T tightly packed 8-bit gray images (T * height * width bytes)
+    /// Match the pairs exactly as the reference's loop does (visual_odometry.rs:106-107): `match_descriptors` (k=1, no
+    /// cross-check) then `filter_good_matches(ratio)` (2.0 there) instead of k=2 + cross-check + Lowe.
+    pub fn with_reference_filter(self, ratio: f32) -> Self { unsafe { sys::orbx_sequence_set_reference_filter(self.h, 1, ratio) }; self }
+    /// `frames`: T tightly packed 8-bit gray images (T * height * width bytes).  A frame with more keypoints than the row
+    /// capacity (a tie flood) is truncated to it and reported as an `Err` by the sync below.
     pub fn run(&mut self, frames: &[u8]) -> Result<Vec<FrameResult>, Box<dyn Error>> {
         let t = frames.len() / (self.width * self.height);
         let cap = unsafe { sys::orbx_sequence_capacity(self.h) } as usize;
@@ -216,10 +253,107 @@ impl Sequence {
         let rc = unsafe { sys::orbx_sequence_sync(self.h) };
         if rc != 0 { return Err(err(rc)); }
         Ok((0..t).map(|i| {
-            let (k, g) = (n[i] as usize, if i > 0 { n_good[i] as usize } else { 0 });
+            let (k, g) = ((n[i].max(0) as usize).min(cap), if i > 0 { (n_good[i].max(0) as usize).min(cap) } else { 0 });
             FrameResult { keypoints: kps[i * cap..i * cap + k].to_vec(), descriptors: desc[i * cap * 32..(i * cap + k) * 32].to_vec(),
                           good_matches: good[i * cap..i * cap + g].to_vec() }
         }).collect())
     }
 }
 impl Drop for Sequence { fn drop(&mut self) { unsafe { sys::orbx_sequence_destroy(self.h) } } }
+
+/// Mirror of mapping::Map (src/mapping/map.rs:8-150) with positions, descriptors and observation counts resident in
+/// HBM (orbx_map_*): ids are handed out sequentially as in map.rs:31-37.
+pub struct Map { h: *mut sys::orbx_map }
+
+impl Map {
+    /// map.rs:21-28; `capacity` = total number of points ever added
+    pub fn new(intrinsics: CameraIntrinsics, capacity: usize) -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_map_create(0, capacity as i32, intrinsics.fx, intrinsics.fy, intrinsics.cx, intrinsics.cy, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h })
+    }
+    /// map.rs:31-37: returns the id of the first new point
+    pub fn add_points(&mut self, points: &[MapPoint]) -> Result<usize, Box<dyn Error>> {
+        let n = points.len();
+        let mut xyz = Vec::with_capacity(3 * n);
+        let (mut desc, mut has, mut obs) = (vec![0u8; 32 * n], vec![0u8; n], vec![0i32; n]);
+        for (i, p) in points.iter().enumerate() {
+            xyz.extend_from_slice(&p.position);
+            if let Some(d) = &p.descriptor { desc[32 * i..32 * i + 32].copy_from_slice(&d[..32]); has[i] = 1; }
+            obs[i] = p.observations as i32;
+        }
+        let mut first = 0i64;
+        let rc = unsafe { sys::orbx_map_add_points(self.h, xyz.as_ptr(), desc.as_ptr(), has.as_ptr(), obs.as_ptr(), n as i32, &mut first) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(first as usize)
+    }
+    /// map.rs:45-47
+    pub fn size(&self) -> usize { unsafe { sys::orbx_map_size(self.h) as usize } }
+    /// map.rs:72-118: projection cull, `match_descriptors(map, frame)` (query = map rows) and `filter_good_matches(2.0)`;
+    /// returns (map_point_id, keypoint_idx) pairs.  `descriptors`: K x 32 bytes of the frame.
+    pub fn find_matches(&mut self, descriptors: &[u8], pose: &Pose, matcher: &mut FeatureMatcher) -> Result<Vec<(usize, usize)>, Box<dyn Error>> {
+        let cap = self.size().max(1);
+        let mut pairs = vec![0i32; 2 * cap];
+        let (mut n, mut vis) = (0i32, 0i32);
+        let rc = unsafe { sys::orbx_map_find_matches(self.h, matcher.h, pose.0.as_ptr(), pose.1.as_ptr(), descriptors.as_ptr(),
+            (descriptors.len() / 32) as i32, pairs.as_mut_ptr(), cap as i32, &mut n, &mut vis) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((0..n as usize).map(|i| (pairs[2 * i] as usize, pairs[2 * i + 1] as usize)).collect())
+    }
+    /// map.rs:121-127
+    pub fn update_observations(&mut self, matches: &[(usize, usize)]) {
+        let flat: Vec<i32> = matches.iter().flat_map(|&(a, b)| [a as i32, b as i32]).collect();
+        unsafe { sys::orbx_map_update_observations(self.h, flat.as_ptr(), matches.len() as i32) };
+    }
+    /// map.rs:130-137
+    pub fn prune_outliers(&mut self) -> usize { let mut r = 0i32; unsafe { sys::orbx_map_prune_outliers(self.h, &mut r) }; r as usize }
+    /// number of map.rs:140-145 `stable_points()`
+    pub fn stable_count(&self) -> usize { let mut c = 0i32; unsafe { sys::orbx_map_stable_count(self.h, &mut c) }; c as usize }
+    /// map.rs:147-150
+    pub fn clear(&mut self) { unsafe { sys::orbx_map_clear(self.h) }; }
+}
+impl Drop for Map { fn drop(&mut self) { unsafe { sys::orbx_map_destroy(self.h) } } }
+
+/// Query-sharded map-to-frame matching over the GPUs of one box (orbx_comm_*, csrc/comm.cu): the train set (the map's
+/// descriptors, map.rs:107) is made resident on every GPU with one NCCL broadcast, the query rows are sliced over the
+/// GPUs and every GPU's kernel stores its records straight into GPU `devices[0]`'s buffer.
+pub struct ShardedMatcher { h: *mut sys::orbx_comm }
+
+impl ShardedMatcher {
+    pub fn new(devices: &[i32]) -> Result<Self, Box<dyn Error>> {
+        let mut h = ptr::null_mut();
+        let rc = unsafe { sys::orbx_comm_create(devices.as_ptr(), devices.len() as i32, &mut h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(Self { h })
+    }
+    /// `train`: T x 32 bytes (host); call again after every map update
+    pub fn set_train(&mut self, train: &[u8]) -> Result<(), Box<dyn Error>> {
+        let rc = unsafe { sys::orbx_comm_set_train(self.h, train.as_ptr(), (train.len() / 32) as i32) };
+        if rc != 0 { return Err(err(rc)); }
+        let rc = unsafe { sys::orbx_comm_sync(self.h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(())
+    }
+    /// matcher.rs:24-37 over all GPUs: one DMatch per query row
+    pub fn match_descriptors(&mut self, desc: &[u8]) -> Result<Vec<DMatch>, Box<dyn Error>> {
+        let nq = desc.len() / 32;
+        let mut out = vec![DMatch::default(); nq.max(1)];
+        let mut n = 0i32;
+        let rc = unsafe { sys::orbx_comm_match(self.h, desc.as_ptr(), nq as i32, out.as_mut_ptr(), &mut n) };
+        if rc != 0 { return Err(err(rc)); }
+        out.truncate(n as usize);
+        Ok(out)
+    }
+    /// `BFMatcher::knnMatch(k = 2)` over all GPUs
+    pub fn knn_match(&mut self, desc: &[u8]) -> Result<Vec<Vec<DMatch>>, Box<dyn Error>> {
+        let nq = desc.len() / 32;
+        if nq == 0 { return Ok(Vec::new()); }
+        let mut out = vec![DMatch::default(); nq * 2];
+        let mut cnt = vec![0i32; nq];
+        let rc = unsafe { sys::orbx_comm_knn_match2(self.h, desc.as_ptr(), nq as i32, out.as_mut_ptr(), cnt.as_mut_ptr()) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok((0..nq).map(|i| out[2 * i..2 * i + (cnt[i].clamp(0, 2) as usize)].to_vec()).collect())
+    }
+}
+impl Drop for ShardedMatcher { fn drop(&mut self) { unsafe { sys::orbx_comm_destroy(self.h) } } }

@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
   const int nunits = a.npairs * a.mtiles;
   if (warp == 0) {
     // ===== producer: bulk copies global -> shared, completion on the full barriers
-    if (lane == 0) {
+    if (lane == 0 && !(a.mode & 8)) {
       uint32_t ua = 0, ub = 0;  // units / B tiles issued so far
       for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
         const int p = u / a.mtiles, mt = u - p * a.mtiles;
@@ -257,14 +257,14 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
         const int p = u / a.mtiles, mt = u - p * a.mtiles;
         const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
         if (mt * kTileM >= nq || nt <= 0) continue;
-        mbar_wait(a_full, ua & 1);
+        if (!(a.mode & 8)) mbar_wait(a_full, ua & 1);
         ++ua;
         const int ntiles = (nt + kTileN - 1) / kTileN;
         for (int n = 0; n < ntiles; ++n, ++ub) {
           const int s = ub & 1, buf = n & 1;
           mbar_wait(t_empty + buf, (tcount[buf] & 1) ^ 1);
           ++tcount[buf];
-          mbar_wait(b_full + s, (ub >> 1) & 1);
+          if (!(a.mode & 8)) mbar_wait(b_full + s, (ub >> 1) & 1);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBBytes);
 #pragma unroll
@@ -380,6 +380,191 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
         }
       }
       asm volatile("bar.sync 5, 512;" ::: "memory");
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+// ================================================================================================ v3
+// B-RESIDENT order: a unit is (problem, 256-row train tile); the B tile is loaded once and the query tiles stream
+// through a three-stage A ring (41 KB per tile-MMA from L2 instead of 82 KB).  The best-2 of every (query tile,
+// train tile) goes to a per-train-tile partial (merged by a later kernel), the reverse best-1 as before.
+constexpr int kAStages = 3;
+constexpr int kSmemV3 = kBBytes + kAStages * kABytes + kGroups * 4 * 128 * 4 + 2 * 128 * 2 * 8 + 256;
+
+struct MmaArgsV3 {
+  const uint8_t* ea;
+  const uint8_t* eb;
+  size_t ea_stride, eb_stride;
+  const int* nq_dev;
+  const int* nt_dev;
+  int max_rows, npairs, ntiles_max;
+  unsigned long long* part;  // [problem][ntiles_max][max_rows][2]
+  unsigned long long* rev;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel_v3(MmaArgsV3 a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sB = smem;
+  uint8_t* sA = smem + kBBytes;
+  int* s_col = reinterpret_cast<int*>(smem + kBBytes + kAStages * kABytes);                        // [4 groups][4][128]
+  unsigned long long* s_half = reinterpret_cast<unsigned long long*>(s_col + kGroups * 4 * 128);  // [2 buffers][128][2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_half + 2 * 128 * 2);
+  uint64_t* b_full = bars + 0;
+  uint64_t* b_empty = bars + 1;
+  uint64_t* a_full = bars + 2;   // [3]
+  uint64_t* a_empty = bars + 5;  // [3]
+  uint64_t* t_full = bars + 8;   // [2]
+  uint64_t* t_empty = bars + 10; // [2]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(b_full, 1);
+    mbar_init(b_empty, 1);
+    for (int i = 0; i < kAStages; ++i) mbar_init(a_full + i, 1), mbar_init(a_empty + i, 1);
+    for (int i = 0; i < 2; ++i) mbar_init(t_full + i, 1), mbar_init(t_empty + i, 8);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+
+  const int nunits = a.npairs * a.ntiles_max;
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t ub = 0, ua = 0;
+      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int p = u / a.ntiles_max, n = u - p * a.ntiles_max;
+        const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+        if (n * kTileN >= nt || nq <= 0) continue;
+        mbar_wait(b_empty, (ub & 1) ^ 1);
+        mbar_expect_tx(b_full, kBBytes);
+        bulk_g2s(sB, a.eb + p * a.eb_stride + (size_t)n * kBBytes, kBBytes, b_full);
+        ++ub;
+        const int mtiles = (nq + kTileM - 1) / kTileM;
+        for (int mt = 0; mt < mtiles; ++mt, ++ua) {
+          const int s = ua % kAStages;
+          mbar_wait(a_empty + s, ((ua / kAStages) & 1) ^ 1);
+          mbar_expect_tx(a_full + s, kABytes);
+          bulk_g2s(sA + s * kABytes, a.ea + p * a.ea_stride + (size_t)mt * kABytes, kABytes, a_full + s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      uint32_t ub = 0, ua = 0, tcount0 = 0, tcount1 = 0;
+      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int p = u / a.ntiles_max, n = u - p * a.ntiles_max;
+        const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+        if (n * kTileN >= nt || nq <= 0) continue;
+        mbar_wait(b_full, ub & 1);
+        ++ub;
+        const int mtiles = (nq + kTileM - 1) / kTileM;
+        for (int mt = 0; mt < mtiles; ++mt, ++ua) {
+          const int s = ua % kAStages, buf = mt & 1;
+          const uint32_t tcnt = buf ? tcount1 : tcount0;
+          mbar_wait(t_empty + buf, (tcnt & 1) ^ 1);
+          if (buf) ++tcount1; else ++tcount0;
+          mbar_wait(a_full + s, (ua / kAStages) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sa = smem_u32(sA + s * kABytes), sb = smem_u32(sB);
+#pragma unroll
+          for (int k = 0; k < kKBytes / 32; ++k)
+            mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+          mma_commit(a_empty + s);
+          mma_commit(t_full + buf);
+        }
+        mma_commit(b_empty);
+      }
+    }
+  } else {
+    const int g = (warp - 2) >> 2, q = warp & 3;
+    const int buf = g >> 1, half = g & 1;
+    const int row = 32 * q + lane;
+    int* col = s_col + g * 4 * 128;
+    unsigned long long* hx = s_half + buf * 256;
+    uint32_t tc = 0;
+    for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+      const int p = u / a.ntiles_max, n = u - p * a.ntiles_max;
+      const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
+      if (n * kTileN >= nt || nq <= 0) continue;
+      const int mtiles = (nq + kTileM - 1) / kTileM;
+      const int nt0 = n * kTileN;
+      for (int mt = buf; mt < mtiles; mt += 2, ++tc) {
+        const int qi = mt * kTileM + row;
+        const bool active = qi < nq;
+        const int rowbias = active ? 127 - row : -(1 << 30);
+        mbar_wait(t_full + buf, tc & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        int m1 = INT_MIN, m2 = INT_MIN;
+        const uint32_t tbase = tmem + buf * kTileN + half * 128 + ((uint32_t)(32 * q) << 16);
+        int va[32], vb[32];
+        tmem_ld32(tbase, va);
+        tmem_wait32(va);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          int* v = (ch & 1) ? vb : va;
+          int* vn = (ch & 1) ? va : vb;
+          if (ch < 3) tmem_ld32(tbase + 32 * (ch + 1), vn);
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const int x = v[j], y = v[j + 1];
+            const int hi = max(x, y), lo = min(x, y);
+            const int t = min(m1, hi);
+            m1 = max(m1, hi);
+            m2 = max3(m2, t, lo);
+            if (a.rev) {
+              const int rx = __reduce_max_sync(0xFFFFFFFFu, x * 128 + rowbias);
+              const int ry = __reduce_max_sync(0xFFFFFFFFu, y * 128 + rowbias);
+              if (lane == 0) *reinterpret_cast<int2*>(col + q * 128 + 32 * ch + j) = make_int2(rx, ry);
+            }
+          }
+          if (ch < 3) tmem_wait32(vn);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(t_empty + buf);
+        // the two column halves of this (query tile, train tile) meet in shared memory; half 0 writes the partial
+        unsigned long long k1 = ~0ull, k2 = ~0ull;
+        if (m1 > kInvalid) k1 = ((unsigned long long)(unsigned)(128 - (m1 >> 9)) << 32) | (unsigned long long)(nt0 + 255 - (m1 & 511));
+        if (m2 > kInvalid) k2 = ((unsigned long long)(unsigned)(128 - (m2 >> 9)) << 32) | (unsigned long long)(nt0 + 255 - (m2 & 511));
+        if (half == 1) {
+          hx[2 * row] = k1;
+          hx[2 * row + 1] = k2;
+        }
+        asm volatile("bar.sync %0, 256;" ::"r"(6 + buf) : "memory");
+        if (half == 0) {
+          const unsigned long long o1 = hx[2 * row], o2 = hx[2 * row + 1];
+          const unsigned long long hi = max(k1, o1);
+          k1 = min(k1, o1);
+          k2 = min(min(k2, o2), hi);
+          if (active) {
+            unsigned long long* o = a.part + (((size_t)p * a.ntiles_max + n) * a.max_rows + qi) * 2;
+            *reinterpret_cast<ulonglong2*>(o) = make_ulonglong2(k1, k2);
+          }
+        }
+        if (a.rev) {
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+          const int c = (warp - 2 - 4 * g) * 32 + lane;
+          const int n0 = nt0 + half * 128;
+          const int m = max(max(col[c], col[128 + c]), max(col[256 + c], col[384 + c]));
+          if (n0 + c < nt && m > kInvalid * 128) {
+            const unsigned d = (unsigned)(128 - (m >> 16));
+            const unsigned r = (unsigned)(127 - (m & 127));
+            atomicMin(a.rev + (size_t)p * a.max_rows + n0 + c,
+                      ((unsigned long long)d << 32) | (unsigned long long)(mt * kTileM + r));
+          }
+        }
+        asm volatile("bar.sync %0, 256;" ::"r"(6 + buf) : "memory");  // hx / col are rewritten by the next tile of this buffer
+      }
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -506,7 +691,7 @@ int main(int argc, char** argv) {
   // where the time goes: the same launch with parts of the epilogue switched off
   const struct { const char* name; bool rev; int mode; } exps[] = {
       {"full", true, 0}, {"no reverse (k=2 only)", false, 0}, {"no reverse, no best-2 math", false, 2},
-      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"reverse only (no best-2 math)", true, 2}};
+      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"MMA only: no copies either", false, 14}, {"reverse only (no best-2 math)", true, 2}};
   for (auto& e : exps) {
     MmaArgs b = a;
     b.rev = e.rev ? d_rev : nullptr;
@@ -519,6 +704,61 @@ int main(int argc, char** argv) {
     float ms;
     cudaEventElapsedTime(&ms, e1, e2);
     printf("  %-58s %.3f ms\n", e.name, ms);
+  }
+  // ---- v3: B-resident order, per-train-tile partials
+  {
+    const int ntiles_max = rows_padded / kTileN;
+    unsigned long long* d_part;
+    CK(cudaMalloc(&d_part, (size_t)npairs * ntiles_max * cap * 2 * 8));
+    CK(cudaFuncSetAttribute(hamming_mma_kernel_v3, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemV3));
+    MmaArgsV3 b{};
+    b.ea = d_ea, b.eb = d_ea + estride, b.ea_stride = b.eb_stride = estride;
+    b.nq_dev = d_n, b.nt_dev = d_n + 1, b.max_rows = cap, b.npairs = npairs, b.ntiles_max = ntiles_max;
+    b.part = d_part;
+    for (int withrev = 1; withrev >= 0; --withrev) {
+      b.rev = withrev ? d_rev : nullptr;
+      for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaMemset(d_part, 0xFF, (size_t)npairs * ntiles_max * cap * 2 * 8));
+        CK(cudaMemset(d_rev, 0xFF, (size_t)npairs * cap * sizeof(unsigned long long)));
+        cudaEventRecord(e1);
+        hamming_mma_kernel_v3<<<sms, kThreads, kSmemV3>>>(b);
+        cudaEventRecord(e2);
+        CK(cudaDeviceSynchronize());
+        float ms;
+        cudaEventElapsedTime(&ms, e1, e2);
+        printf("v3 (B resident, smem %d)%s rep %d: %.3f ms\n", kSmemV3, withrev ? "" : " no reverse", rep, ms);
+      }
+      if (!withrev) break;
+      std::vector<unsigned long long> part((size_t)npairs * ntiles_max * cap * 2), rev3((size_t)npairs * cap);
+      CK(cudaMemcpy(part.data(), d_part, part.size() * 8, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(rev3.data(), d_rev, rev3.size() * 8, cudaMemcpyDeviceToHost));
+      long bad3 = 0, chk3 = 0;
+      for (int p : check_pairs) {
+        if (p < 0 || p >= npairs) continue;
+        const int nq = n[p], nt = n[p + 1];
+        for (int i = 0; i < nq; ++i) {
+          unsigned long long b1 = ~0ull, b2 = ~0ull;
+          for (int t = 0; t < (nt + kTileN - 1) / kTileN; ++t)
+            for (int k = 0; k < 2; ++k) {
+              const unsigned long long key = part[(((size_t)p * ntiles_max + t) * cap + i) * 2 + k];
+              const unsigned long long hi = std::max(b1, key);
+              b1 = std::min(b1, key);
+              b2 = std::min(b2, hi);
+            }
+          const unsigned long long* o = &best[((size_t)p * cap + i) * 2];  // v2 results, already checked against the CPU
+          ++chk3;
+          if (o[0] != b1 || o[1] != b2) {
+            if (bad3 < 10) printf("v3 pair %d query %d: got %016llx %016llx want %016llx %016llx\n", p, i, b1, b2, o[0], o[1]);
+            ++bad3;
+          }
+        }
+        for (int j = 0; j < nt; ++j) {
+          ++chk3;
+          if (rev3[(size_t)p * cap + j] != rev[(size_t)p * cap + j]) ++bad3;
+        }
+      }
+      printf("v3 checked %ld results, %ld mismatches -> %s\n", chk3, bad3, bad3 ? "FAIL" : "OK (bit-exact)");
+    }
   }
   return bad ? 1 : 0;
 }

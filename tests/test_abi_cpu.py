@@ -29,6 +29,32 @@ def test_library_exports_every_header_symbol():
     assert set(syms) == set(s.SYMBOLS), set(syms) ^ set(s.SYMBOLS)
 
 
+def test_rust_ffi_crate_mirrors_the_header():
+    """rust/orbx-sys/src/lib.rs is GENERATED from include/orbx.h (scripts/gen_rust_sys.py): it must be current, declare
+    exactly the header's symbols, and its build.rs must compile every .cu the Makefile links (the crate
+    omitted sequence.cu and 20 symbols)."""
+    import re
+    import subprocess
+    import sys
+    rc = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "gen_rust_sys.py"), "--check"]).returncode
+    assert rc == 0, "rust/orbx-sys/src/lib.rs is stale: run python scripts/gen_rust_sys.py"
+    rs = open(os.path.join(ROOT, "rust", "orbx-sys", "src", "lib.rs")).read()
+    assert set(re.findall(r"pub fn (orbx_\w+)", rs)) == set(header_symbols())
+    mk = open(os.path.join(ROOT, "slam-rs_b200", "csrc", "Makefile")).read()
+    srcs = set(re.search(r"^SRCS\s*:=\s*(.*)$", mk, re.M).group(1).split())
+    on_disk = {f for f in os.listdir(os.path.join(ROOT, "slam-rs_b200", "csrc")) if f.endswith(".cu")}
+    assert srcs == on_disk, srcs ^ on_disk
+    build_rs = open(os.path.join(ROOT, "rust", "orbx-sys", "build.rs")).read()
+    assert "Makefile" in build_rs and "SRCS" in build_rs          # the crate takes its source list from the Makefile
+    safe = open(os.path.join(ROOT, "rust", "orbx", "src", "lib.rs")).read()
+    for name in ("fn knn_match", "fn ratio_test", "fn new_cross_check", "pub struct Map", "fn find_matches",
+                 "pub struct ShardedMatcher", "fn new_reference_faithful"):
+        assert name in safe, name
+    types = set(re.findall(r"pub (?:enum|struct) (orbx_\w+)", rs))
+    for call in set(re.findall(r"sys::(orbx_\w+)", safe)) - types:   # every call the safe crate makes exists in the header
+        assert call in header_symbols(), call
+
+
 def test_struct_layouts_match_opencv():
     import slam_rs_b200 as s
     from slam_rs_b200 import _ffi
