@@ -81,7 +81,6 @@ int launch_repack_gray(const uint8_t* src, size_t spitch, size_t sstride, uint8_
                        int h, int batch, cudaStream_t s);
 int launch_resize(const ResizeArgs& a, int batch, cudaStream_t s);
 int launch_fast(const DevGeom& g, cudaStream_t s);
-bool fast_tma_legal(const uint8_t* img, size_t pitch, size_t stride);
 int launch_harris(const DevGeom& g, cudaStream_t s);
 int launch_select(const DevGeom& g, int sort_cap, cudaStream_t s);
 int launch_orient(const DevGeom& g, const OutArgs& o, cudaStream_t s);
