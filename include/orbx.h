@@ -179,6 +179,20 @@ int orbx_match_batch(orbx_matcher* m, const uint8_t* q, size_t q_stride, const i
                      const uint8_t* t, size_t t_stride, const int* nt_dev, int npairs, int max_rows,
                      orbx_dmatch* out, int* n_out_dev);
 
+/* BFMatcher::knnMatch(k=2) like orbx_knn_match2, without any allocation.  This entry point has NO counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid it).  No handle: the partial-key scratch of the
+ * train-split search lives in a file-scope device array inside liborbx (8 MiB, held by every GPU that loads the library
+ * until exit), so the call makes no cudaMalloc / cudaFree and creates no stream or event.  q (nq x 32), t (nt x 32), out
+ * (nq x 2) and n_per_q (nq) must be DEVICE memory of `device`; the work is enqueued on `stream` (a cudaStream_t; NULL =
+ * the default stream) and the call returns without synchronising.  Limits: nq <= 8192 and nt <= 64 x 65536 rows per call
+ * (ORBX_E_CAPACITY beyond, with a clear message); no cross-check.  Results are bit-identical to orbx_knn_match2.  All
+ * calls on one GPU share the one scratch array: calls whose kernels may overlap on the GPU (different streams) race -
+ * serialise them.  The array keeps the previous call's contents; nothing in it has to start at zero (every slot a call
+ * reads is written by that call first). */
+int orbx_knn_match2_static(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* n_per_q,
+                           void* stream);
+
 /* replaces PoseEstimator::extract_matched_points (src/odometry/pose.rs:27-44; SURVEY.md §8 f2, first step):
  * pts1[i] = kp1[matches[i].query_idx].pt, pts2[i] = kp2[matches[i].train_idx].pt as (x, y) fp32 pairs, match
  * order preserved.  An index outside its keypoint array is the reference's `Vector::get(..)?` error:

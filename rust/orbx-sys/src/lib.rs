@@ -92,6 +92,7 @@ extern "C" {
     pub fn orbx_filter_good_matches(m: *mut orbx_matcher, in_: *const orbx_dmatch, n: c_int, ratio: f32, out: *mut orbx_dmatch, n_out: *mut c_int) -> c_int;
     pub fn orbx_filter_good_matches_batch(m: *mut orbx_matcher, in_: *const orbx_dmatch, n_dev: *const c_int, npairs: c_int, max_rows: c_int, ratio: f32, out: *mut orbx_dmatch, n_out_dev: *mut c_int) -> c_int;
     pub fn orbx_match_batch(m: *mut orbx_matcher, q: *const u8, q_stride: usize, nq_dev: *const c_int, t: *const u8, t_stride: usize, nt_dev: *const c_int, npairs: c_int, max_rows: c_int, out: *mut orbx_dmatch, n_out_dev: *mut c_int) -> c_int;
+    pub fn orbx_knn_match2_static(device: c_int, q: *const u8, nq: c_int, t: *const u8, nt: c_int, out: *mut orbx_dmatch, n_per_q: *mut c_int, stream: *mut c_void) -> c_int;
     pub fn orbx_extract_matched_points(m: *mut orbx_matcher, kp1: *const orbx_keypoint, n1: c_int, kp2: *const orbx_keypoint, n2: c_int, matches: *const orbx_dmatch, n: c_int, pts1: *mut f32, pts2: *mut f32) -> c_int;
     pub fn orbx_extract_matched_points_batch(m: *mut orbx_matcher, kp1: *const orbx_keypoint, n1_dev: *const c_int, kp2: *const orbx_keypoint, n2_dev: *const c_int, kp_stride: usize, matches: *const orbx_dmatch, n_dev: *const c_int, npairs: c_int, max_rows: c_int, pts1: *mut f32, pts2: *mut f32, bad_dev: *mut c_int) -> c_int;
     pub fn orbx_matcher_set_mode(m: *mut orbx_matcher, mode: c_int) -> c_int;

@@ -94,6 +94,7 @@ def _load():
         "orbx_matcher_set_stream": (i, [vp, vp]),
         "orbx_match": (i, [vp, vp, i, vp, i, vp, vp]),
         "orbx_knn_match2": (i, [vp, vp, i, vp, i, vp, vp]),
+        "orbx_knn_match2_static": (i, [i, vp, i, vp, i, vp, vp, vp]),
         "orbx_knn_match2_batch": (i, [vp, vp, sz, vp, vp, sz, vp, i, i, vp, vp]),
         "orbx_match_batch": (i, [vp, vp, sz, vp, vp, sz, vp, i, i, vp, vp]),
         "orbx_ratio_test": (i, [vp, vp, vp, i, f, vp, vp]),

@@ -958,6 +958,113 @@ int orbx_filter_good_matches_batch(orbx_matcher* m, const orbx_dmatch* in, const
 }
 
 // ------------------------------------------------------------------------------------------------
+// Allocation-free k=2 search (no counterpart in the reference).
+// Callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it) get
+// the train-split Hamming search with its partial-key scratch in a file-scope device array instead of the handle's
+// cudaMalloc'ed buffer.  The array costs kNoAllocScratchBytes (8 MiB) on every GPU that loads liborbx, until exit.
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace orbx {
+constexpr int kNoAllocMaxQueries = 8192;  // query rows per call
+constexpr int kNoAllocMaxSplits = 64;     // train ranges per call (each <= 65536 rows)
+constexpr size_t kNoAllocScratchWords = (size_t)kNoAllocMaxQueries * kNoAllocMaxSplits * 2;  // u64 keys: 8 MiB
+// [split][query][2] packed (dist << 32 | train_idx).  In HOST code this name is only a stand-in for the symbol: the
+// device address comes from cudaGetSymbolAddress (no_alloc_scratch below), once per device.
+static __device__ __align__(256) unsigned long long g_noalloc_part[kNoAllocScratchWords];
+
+// device address of g_noalloc_part and the SM count of `device` (which must be current), looked up once per device
+static int no_alloc_scratch(int device, unsigned long long** ptr, int* sms) {
+  constexpr int kMaxDev = 64;
+  static unsigned long long* addr[kMaxDev] = {nullptr};
+  static int nsm[kMaxDev] = {0};
+  static std::mutex mu;
+  if (device < 0 || device >= kMaxDev) {
+    set_error("orbx_knn_match2_static: device %d out of range", device);
+    return ORBX_E_BADARG;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    void* p = nullptr;
+    ORBX_CUDA(cudaGetSymbolAddress(&p, g_noalloc_part));
+    int n = 0;
+    ORBX_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device));
+    addr[device] = (unsigned long long*)p;
+    nsm[device] = n;
+  }
+  *ptr = addr[device];
+  *sms = nsm[device];
+  return ORBX_OK;
+}
+}  // namespace orbx
+
+extern "C" {
+
+int orbx_knn_match2_static(int device, const uint8_t* q, int nq, const uint8_t* t, int nt, orbx_dmatch* out, int* n_per_q,
+                           void* stream) {
+  if (nq < 0 || nt < 0 || (nq > 0 && (!q || !out || !n_per_q)) || (nt > 0 && nq > 0 && !t)) {
+    set_error("orbx_knn_match2_static: bad argument");
+    return ORBX_E_BADARG;
+  }
+  if (nq == 0) return ORBX_OK;
+  if (nq > kNoAllocMaxQueries) {
+    set_error("orbx_knn_match2_static: %d query rows exceed the static scratch (at most %d per call; use orbx_knn_match2)",
+              nq, kNoAllocMaxQueries);
+    return ORBX_E_CAPACITY;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    set_error("orbx_knn_match2_static: CUDA device %d unavailable (there is no CPU fallback)", device);
+    return ORBX_E_CUDA;
+  }
+  ORBX_CUDA(cudaSetDevice(device));
+  if (!is_device_ptr(q) || !is_device_ptr(out) || !is_device_ptr(n_per_q) || (nt > 0 && !is_device_ptr(t))) {
+    set_error("orbx_knn_match2_static: q, t, out and n_per_q must be device memory (staging would allocate)");
+    return ORBX_E_BADARG;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  if (nt == 0) {  // matcher.rs:29-31: an empty side is an empty result
+    ORBX_CUDA(cudaMemsetAsync(n_per_q, 0, sizeof(int) * (size_t)nq, s));
+    return ORBX_OK;
+  }
+  unsigned long long* part = nullptr;
+  int sms = 148;
+  if (int rc = no_alloc_scratch(device, &part, &sms)) return rc;
+  // the split rule of launch_knn: about four waves of blocks, ranges of whole 256-row tiles, at most 65536 rows each
+  const int qtiles = div_up(nq, kQPB);
+  int splits = qtiles >= sms * 4 ? 1 : std::min(std::max(1, div_up(sms * 40, qtiles)), std::max(1, div_up(nt, kTile)));
+  splits = std::min(splits, kNoAllocMaxSplits);
+  int rps = (int)align_up((size_t)div_up(nt, splits), kTile);
+  if (rps > kMaxSplitRows) rps = kMaxSplitRows;
+  splits = div_up(nt, rps);
+  if (splits > kNoAllocMaxSplits) {
+    set_error("orbx_knn_match2_static: %d train rows exceed the static scratch (at most %d per call; use orbx_knn_match2)",
+              nt, kNoAllocMaxSplits * kMaxSplitRows);
+    return ORBX_E_CAPACITY;
+  }
+  MatchArgs a{};
+  a.q = q;
+  a.t = t;
+  a.nq_fixed = nq;
+  a.nt_fixed = nt;
+  a.max_rows = nq;
+  a.out = out;
+  a.n_per_q = n_per_q;
+  a.rows_per_split = rps;
+  a.nsplits = splits;
+  a.part = part;  // every (split, active query) slot is written by the launch below before the merge reads it:
+                  // nothing in the array has to start at zero, and nothing of an earlier call is read
+  hamming_knn_kernel<2, false><<<dim3(qtiles, splits, 1), kQPB, 0, s>>>(a);
+  ORBX_LAUNCH_CHECK();
+  if (splits > 1) {
+    merge_splits_kernel<2><<<dim3(div_up(nq, 256), 1), 256, 0, s>>>(a);
+    ORBX_LAUNCH_CHECK();
+  }
+  return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // SURVEY.md §8 f2 (first step): PoseEstimator::extract_matched_points
 // ------------------------------------------------------------------------------------------------
 int orbx_extract_matched_points(orbx_matcher* m, const orbx_keypoint* kp1, int n1, const orbx_keypoint* kp2, int n2,
