@@ -411,8 +411,12 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device — liborbx has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        # host-side barrier for the phases in which rank 0 alone drives ALL GPUs (sub_map): a NCCL barrier would leave a
+        # spinning kernel of every other rank on the GPUs rank 0 is timing (and time-slice against it)
+        host_group = dist.new_group(backend="gloo")
     import slam_rs_b200 as orbx
     from slam_rs_b200.frontend import SequenceFrontEnd, NativeSequence
     synth = load_synth()
@@ -560,7 +564,9 @@ def run_ours(args, rank, world, local_rank):
                     subs[name] = fn()
                 except Exception as ex:  # noqa: BLE001
                     subs[name] = {"error": repr(ex)[:300]}
-        barrier()
+        torch.cuda.synchronize()
+        if host_group is not None:
+            dist.barrier(group=host_group)  # the other ranks wait on the host: their GPUs stay idle for rank 0
 
     if rank == 0:
         hbm_peak, peak_kind, peaks = measured_peaks()

@@ -123,3 +123,58 @@ def test_native_sequence_reports_tie_flood_truncation():
     n = out["n"].numpy()
     assert n[1] == ns.cap and n.max() <= ns.cap and n[0] > 0 and n[2] > 0
     ns.sync()                                                                  # reported once
+
+
+def test_bench_configuration_1000_frames_vs_cv2():
+    """The pass bench.py times - BASELINE configs[1]: the 1000-frame 1241x376 sequence, nfeatures 2000, ONE 1000-frame
+    launch set on the device (chunk=1000, tensor-core matcher) and the 167-frame pipeline of orbx_sequence_run_host -
+    compared with cv2 (the OpenCV code the reference binds) on 32 sampled frames and 32 sampled pairs, with the
+    size-independent properties on all 999 pairs, and the two passes with each other on every byte."""
+    import torch
+    from oracle import synth, cv_ref, restated as R
+    import slam_rs_b200 as orbx
+    from slam_rs_b200.frontend import NativeSequence
+    from tests.util import compare_orb
+    T, h, w, nf = 1000, 376, 1241, 2000
+    seq = synth.sequence(h, w, T)
+    ns = NativeSequence(w, h, nfeatures=nf, max_frames=T, chunk=1000, host_chunk=167)
+    cap = ns.cap
+    dev = torch.from_numpy(seq).cuda()
+    torch.cuda.synchronize()
+    ns.run_device(dev)
+    res = ns.results_to_host(T)
+    n, ng = res["n"], res["n_good"]
+    assert n.min() > 0 and n.max() <= cap and ng[1:].min() > 0
+    kps = res["kps"].view(orbx.KEYPOINT_DTYPE).reshape(T, cap)
+    good = res["good"].view(orbx.DMATCH_DTYPE).reshape(T, cap)
+    rng = np.random.default_rng(3)
+    frames = sorted(set([0, T - 1, 166, 167, 500] + list(rng.choice(T, 27, replace=False))))
+    for t in frames:                                                 # extraction vs cv2, bit for bit
+        st = compare_orb(kps[t, :n[t]], res["desc"][t, :n[t]], cv_ref.orb_detect_and_compute(seq[t], nf), h, w)
+        assert st["missing"] == 0 and st["extra"] == 0 and st["desc_bits_diff"] == 0, (t, st)
+        assert st["resp_eq"] == st["angle_eq"] == st["pt_eq"] == st["common"], (t, st)
+    pairs = sorted(set([1, T - 1, 167, 168] + list(rng.choice(np.arange(1, T), 28, replace=False))))
+    for t in pairs:                                                  # matching vs cv2 BFMatcher on the same rows
+        d0, d1 = res["desc"][t - 1, :n[t - 1]], res["desc"][t, :n[t]]
+        idx, dist, c = cv_ref.knn2(d0, d1)
+        mutual = np.zeros(len(d0), bool)
+        mutual[cv_ref.match_k1(d0, d1, cross_check=True)[:, 0]] = True
+        keep = R.ratio_test(idx, dist, c, 0.75) & mutual
+        g = good[t, :ng[t]]
+        assert np.array_equal(g["query_idx"], np.nonzero(keep)[0]), t
+        assert np.array_equal(g["train_idx"], idx[keep, 0]) and np.array_equal(g["distance"], dist[keep, 0].astype(np.float32))
+    for t in range(1, T):                                            # properties of every pair
+        g = good[t, :ng[t]]
+        assert np.all(np.diff(g["query_idx"]) > 0) and len(np.unique(g["train_idx"])) == len(g)
+        q, tr = res["desc"][t - 1][g["query_idx"]], res["desc"][t][g["train_idx"]]
+        assert np.array_equal(np.unpackbits(q ^ tr, axis=1).sum(1), g["distance"].astype(np.int64))
+    # the end-to-end pass (host buffers, 167-frame pipeline stages) returns the same bytes
+    out = ns.alloc_host_outputs()
+    ns.run_host(torch.from_numpy(seq).pin_memory(), out)
+    ns.sync()
+    assert np.array_equal(out["n"].numpy(), n) and np.array_equal(out["n_good"].numpy()[1:], ng[1:])
+    ok, od, og = out["kps"].numpy(), out["desc"].numpy(), out["good"].numpy()
+    for t in range(T):
+        assert np.array_equal(ok[t, :n[t]], res["kps"][t, :n[t]]) and np.array_equal(od[t, :n[t]], res["desc"][t, :n[t]]), t
+        if t:
+            assert np.array_equal(og[t, :ng[t]], res["good"][t, :ng[t]]), t
