@@ -124,6 +124,16 @@ __device__ __forceinline__ uint64_t make_desc_rt(uint32_t saddr, int lbo, int sb
   d |= (uint64_t)1 << 46;
   return d;
 }
+// timing experiment: 128-byte swizzled K-major atoms (8 rows x 128 B, SBO = 1024 B)
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)((1024 >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
   // K-major, SWIZZLE_NONE: LBO = 128 B (next 16-byte K chunk), SBO = kGroupBytes (next 8-row group), version 1 (sm_100)
   uint64_t d = 0;
@@ -268,8 +278,16 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBBytes);
 #pragma unroll
-          for (int k = 0; k < kKBytes / 32; ++k)  // last step: aux slices, chunks 16-17 of A against chunks 18-19 of B
-            mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+          for (int k = 0; k < kKBytes / 32; ++k) {  // last step: aux slices, chunks 16-17 of A against chunks 18-19 of B
+            if (a.mode & 16) {  // layout timing only (operands are garbage): SW128 atoms, 4 K-steps of 32 B per atom
+              if (k < 8)
+                mma_i8(tmem + buf * kTileN, make_desc_sw128(sa + (k >> 2) * 16384 + (k & 3) * 32),
+                       make_desc_sw128(sb + (k >> 2) * 32768 + (k & 3) * 32), k > 0);
+              else
+                mma_i8(tmem + buf * kTileN, make_desc(sa), make_desc(sb), 1);
+            } else
+              mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+          }
           mma_commit(b_empty + s);
           mma_commit(t_full + buf);
         }
@@ -691,7 +709,7 @@ int main(int argc, char** argv) {
   // where the time goes: the same launch with parts of the epilogue switched off
   const struct { const char* name; bool rev; int mode; } exps[] = {
       {"full", true, 0}, {"no reverse (k=2 only)", false, 0}, {"no reverse, no best-2 math", false, 2},
-      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"MMA only: no copies either", false, 14}, {"reverse only (no best-2 math)", true, 2}};
+      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"MMA only: no copies either", false, 14}, {"MMA only, SW128 descriptors (layout timing, garbage data)", false, 30}, {"reverse only (no best-2 math)", true, 2}};
   for (auto& e : exps) {
     MmaArgs b = a;
     b.rev = e.rev ? d_rev : nullptr;
