@@ -448,10 +448,12 @@ def run_ours(args, rank, world, local_rank):
         for _ in range(P):
             fe.run_device(frames_dev)
     barrier()
-    fe.det.set_timing(True)
-    fe.matcher.set_timing(True)
-    fe.det.timing(reset=True)
-    fe.matcher.timing(reset=True)
+    inline_timers = bool(args.stage_timers)
+    if inline_timers:
+        fe.det.set_timing(True)
+        fe.matcher.set_timing(True)
+        fe.det.timing(reset=True)
+        fe.matcher.timing(reset=True)
     launches0 = orbx.launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -464,6 +466,18 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     ms_total = e0.elapsed_time(e1)
     launches = orbx.launch_count() - launches0
+    stage_passes = args.steps * P
+    if not inline_timers:
+        # --stage-timers 0: the timed region above ran without the per-stage events; the stage breakdown comes from P
+        # further passes with the timers on (measured difference of the headline: +0.3 %)
+        fe.det.set_timing(True)
+        fe.matcher.set_timing(True)
+        fe.det.timing(reset=True)
+        fe.matcher.timing(reset=True)
+        for _ in range(P):
+            fe.run_device(frames_dev)
+        torch.cuda.synchronize()
+        stage_passes = P
     stage = fe.det.timing(reset=True)
     match_ms, match_launches = fe.matcher.timing(reset=True)
     fe.det.set_timing(False)
@@ -571,7 +585,7 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         hbm_peak, peak_kind, peaks = measured_peaks()
         P_px = sum(pyramid_pixels(H_IMG, W_IMG))
-        frames_timed = T * passes_all
+        frames_timed = T * stage_passes  # frames behind the per-stage event times
         popc = None
         import ctypes as C
         v = C.c_double()
@@ -582,18 +596,18 @@ def run_ours(args, rank, world, local_rank):
         alg = {"pyramid": P_px, "fast": P_px + 8 * cand0, "brief": 2 * P_px + 572 * K_mean}
         stages = {}
         for name, (ms, ln) in stage.items():
-            stages[name] = {"ms_per_pass": ms / passes_all, "launches_per_pass": ln / passes_all}
-        stages["hamming"] = {"ms_per_pass": match_ms / passes_all, "launches_per_pass": match_launches / passes_all}
+            stages[name] = {"ms_per_pass": ms / stage_passes, "launches_per_pass": ln / stage_passes}
+        stages["hamming"] = {"ms_per_pass": match_ms / stage_passes, "launches_per_pass": match_launches / stage_passes}
         for name, nbytes in (("pyramid", alg["pyramid"]), ("fast", alg["fast"])):
             gbs = nbytes * frames_timed / (stage[name][0] * 1e-3) / 1e9
             stages[name].update({"bound": "hbm", "achieved_gbs": gbs, "frac": gbs / hbm_peak})
         bb_ms = stage["blur"][0] + stage["brief"][0]
         gbs = alg["brief"] * frames_timed / (bb_ms * 1e-3) / 1e9
-        stages["blur+brief"] = {"ms_per_pass": bb_ms / passes_all, "bound": "hbm", "achieved_gbs": gbs,
+        stages["blur+brief"] = {"ms_per_pass": bb_ms / stage_passes, "bound": "hbm", "achieved_gbs": gbs,
                                 "frac": gbs / hbm_peak}
         # S10.  Every (query, train) distance is evaluated ONCE per pass (the reverse search of the cross-check reads the
         # same evaluation), so pairs/s counts evaluated pairs - never forward + reverse.
-        pairs_s = pairs_eval * passes_all / (match_ms * 1e-3)
+        pairs_s = pairs_eval * stage_passes / (match_ms * 1e-3)
         use_mma = args.matcher != "popc"
         ham = stages["hamming"]
         ham.update({"pairs_per_s": pairs_s, "evaluated_pairs_per_pass": pairs_eval})
@@ -855,6 +869,9 @@ def main():
     ap.add_argument("--hd-passes", type=int, default=5)
     ap.add_argument("--map-steps", type=int, default=20)
     ap.add_argument("--latency-iters", type=int, default=200)
+    ap.add_argument("--stage-timers", type=int, default=1,
+                    help="1: per-stage CUDA events inside the timed region (stages run serially); 0: timed region without "
+                         "them, stage breakdown from extra passes")
     ap.add_argument("--torch-e2e", type=int, default=1,
                     help="1: also time the Python / torch-stream scheduled end-to-end pass (secondary key)")
     ap.add_argument("--size", default="kitti", choices=["kitti", "hd"],
