@@ -11,8 +11,8 @@ A step is `--passes` (10) passes over the resident sequence, so that a --steps 2
 `value`: frames resident in HBM, timed with CUDA events.  `e2e`: the same passes through the reference-facing plugin
 call orbx_sequence_run_host (csrc/sequence.cu) with HOST buffers - pinned frames in, keypoints / descriptors / good
 matches back out - timed by the library's own CUDA events.  Attached sub-measurements (`--subs 1`): `hd` (configs[2]
-shape), `map` (configs[3]: orbx_comm over all GPUs of the run, driven by rank 0), `latency` (configs[0]: two frames,
-per-call).
+shape), `seqs` (configs[4] shape: 8 pre-staged sequences per GPU), `map` (configs[3]: orbx_comm over all GPUs of the
+run, driven by rank 0), `latency` (configs[0]: two frames, per-call).
 
   python bench.py [--gpus N] [--steps K] [--warmup W]          our arm (liborbx on B200)
   python bench.py --impl reference ...                          reference arm: cv2 (= the OpenCV code the
@@ -298,6 +298,62 @@ def sub_hd(args, torch, dist, world, local_rank, synth, barrier):
             "keypoints_per_frame": float(n.mean()), "l2": "inputs larger than L2 (%.0f MB per pass)" % (T * w * h / 1e6)}
 
 
+def sub_seqs(args, torch, dist, world, local_rank, frames_pinned, barrier):
+    """configs[4]: 64 independent sequences on 8 GPUs = S = 8 sequences of 1000 frames per GPU (29.9 GB of frames over the
+    box), all pre-staged - in HBM for `value`, in pinned host memory for `e2e` - and run back to back through the native
+    sequence front end.  Sequences 1..7 of a rank are derived from its sequence 0 on the device (horizontal / vertical
+    flip / time reversal, the 8 combinations): different images, keypoints and descriptors, no extra host synthesis."""
+    from slam_rs_b200.frontend import NativeSequence
+    S = args.seqs
+    T = frames_pinned.shape[0]
+    base = frames_pinned.cuda(local_rank, non_blocking=True)
+    dev_seqs, host_seqs = [], []
+    for k in range(S):
+        v = base
+        dims = [d for b, d in ((1, 2), (2, 1), (4, 0)) if k & b]
+        if dims:
+            v = torch.flip(base, dims)
+        v = v.contiguous()
+        dev_seqs.append(v)
+        h = torch.empty(v.shape, dtype=v.dtype).pin_memory()
+        h.copy_(v)
+        host_seqs.append(h)
+    torch.cuda.synchronize()
+    ns = NativeSequence(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, host_chunk=args.host_chunk,
+                        device=local_rank, ratio=RATIO, cross_check=True)
+    outs = [ns.alloc_host_outputs(), ns.alloc_host_outputs()]
+    res, kp = {}, []
+    for name, run in (("value", lambda k: ns.run_device(dev_seqs[k])),
+                      ("e2e", lambda k: ns.run_host(host_seqs[k], outs[k & 1]))):
+        for k in range(min(S, 2)):
+            run(k)
+        ns.sync()
+        barrier()
+        ns.set_timing(True)
+        for k in range(S):
+            run(k)
+            if name == "e2e" and k >= 1:
+                ns.wait_pass(1)  # sequence k-1 is complete on the host while sequence k runs: consume it
+                kp.append(float(outs[(k - 1) & 1]["n"][:T].numpy().mean()))
+        ns.sync()
+        if name == "e2e":
+            kp.append(float(outs[(S - 1) & 1]["n"][:T].numpy().mean()))
+        ms, passes = ns.elapsed()
+        ns.set_timing(False)
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda:%d" % local_rank)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[name] = T * world * passes / (float(t[0]) * 1e-3)
+        res[name + "_ms"] = float(t[0]) / passes
+    ns.close()
+    return {"workload": "C5 shape: %d independent 1241x376 sequences of %d frames (%d per GPU), pre-staged, frame-to-frame "
+                        "k=2 + cross-check + Lowe" % (S * world, T, S), "n_gpus": world, "sequences": S * world,
+            "staged_gb": S * world * T * H_IMG * W_IMG / 1e9, "value": res["value"], "unit": "frames/s",
+            "ms_per_sequence": res["value_ms"],
+            "e2e": {"value": res["e2e"], "ms_per_sequence": res["e2e_ms"], "api": "orbx_sequence_run_host"},
+            "keypoints_per_frame_by_sequence": kp}
+
+
 def sub_map(args, torch, world, synth):
     """configs[3]: 1 M map descriptors (train, resident on every GPU, one NCCL broadcast) vs 5000 frame descriptors
     (query, sharded over the GPUs), k = 2 - through the C ABI's multi-GPU entry (orbx_comm_*): ONE process (this rank 0)
@@ -491,15 +547,18 @@ def run_ours(args, rank, world, local_rank):
     # the library's own CUDA events (orbx_sequence_elapsed): first upload -> last download.
     ns = NativeSequence(W_IMG, H_IMG, nfeatures=NFEAT, max_frames=T, chunk=args.chunk, host_chunk=args.host_chunk,
                         device=local_rank, ratio=RATIO, cross_check=True)
-    host_out = ns.alloc_host_outputs()
-    for _ in range(max(2, args.warmup)):
-        ns.run_host(frames_pinned, host_out)
+    # consecutive run_host calls are pipelined into each other (sequence.cu): as a streaming host would, the passes
+    # alternate two sets of pinned result arrays, so the set of pass k stays untouched while pass k+1 runs
+    host_outs = [ns.alloc_host_outputs(), ns.alloc_host_outputs()]
+    host_out = host_outs[(args.steps * P - 1) & 1]  # the set the last timed pass writes
+    for i in range(max(2, args.warmup)):
+        ns.run_host(frames_pinned, host_outs[i & 1])
     ns.sync()
     barrier()
     ns.set_timing(True)
     t0 = time.perf_counter()
-    for _ in range(args.steps * P):
-        ns.run_host(frames_pinned, host_out)
+    for i in range(args.steps * P):
+        ns.run_host(frames_pinned, host_outs[i & 1])
     ns.sync()
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     ms_e2e, e2e_passes = ns.elapsed()
@@ -570,6 +629,14 @@ def run_ours(args, rank, world, local_rank):
                 subs["hd"] = hd
         except Exception as ex:  # noqa: BLE001
             subs["hd"] = {"error": repr(ex)[:300]}
+        barrier()
+        try:
+            sq = sub_seqs(args, torch, dist, world, local_rank, frames_pinned, barrier)
+            if rank == 0:
+                subs["seqs"] = sq
+        except Exception as ex:  # noqa: BLE001
+            subs["seqs"] = {"error": repr(ex)[:300]}
+        torch.cuda.empty_cache()
         barrier()
         if rank == 0:
             for name, fn in (("map", lambda: sub_map(args, torch, world, synth)),
@@ -867,6 +934,7 @@ def main():
                          "latency (configs[0]) after the headline and attach them to the line")
     ap.add_argument("--hd-frames", type=int, default=48)
     ap.add_argument("--hd-passes", type=int, default=5)
+    ap.add_argument("--seqs", type=int, default=8, help="sequences per GPU of the configs[4] sub-measurement")
     ap.add_argument("--map-steps", type=int, default=20)
     ap.add_argument("--latency-iters", type=int, default=200)
     ap.add_argument("--stage-timers", type=int, default=1,
@@ -878,7 +946,7 @@ def main():
                     help="hd: 1920x1080 frames, nfeatures=5000 (BASELINE configs[2] shape; not the headline metric)")
     ap.add_argument("--chunk", type=int, default=1000, help="frames per extraction launch (device-resident pass)")
     ap.add_argument("--dual", type=int, default=1, help="1: alternate e2e pipeline stages between two streams")
-    ap.add_argument("--host-chunk", type=int, default=167,
+    ap.add_argument("--host-chunk", type=int, default=250,
                     help="frames per pipeline stage of the end-to-end pass (H2D / kernels / D2H overlap)")
     ap.add_argument("--cpu-frames", type=int, default=500, help="frames of the sequence timed for cpu_baseline")
     ap.add_argument("--ref-frames", type=int, default=250, help="frames per step of the reference arm")

@@ -343,17 +343,26 @@ int orbx_sequence_set_reference_filter(orbx_sequence* s, int enable, float ratio
 int orbx_sequence_run_device(orbx_sequence* s, const uint8_t* frames_dev, size_t pitch, size_t frame_stride, int T);
 /* HOST frames, tightly packed [T][height][width] (pinned memory for copy / compute overlap), results to host arrays
  * (pinned likewise; any may be NULL): kps T x cap, desc T x cap x 32, n T, good T x cap, n_good T.  Upload, kernels
- * and download of consecutive chunks overlap on four streams. */
+ * and download of consecutive chunks overlap on four streams.  Consecutive calls are pipelined into each other (the
+ * device staging and result arrays exist twice and the calls alternate between them, so the next sequence's uploads and
+ * kernels run under the tail of the last one; chunk-level events keep every device buffer safe): a host that streams many sequences (64 independent sequences, BASELINE configs[4]) alternates
+ * two sets of host result arrays and calls orbx_sequence_wait_pass(s, 1) to consume sequence k while k+1 runs.  The
+ * host arrays of a call belong to the library until that call's pass has finished. */
 int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_keypoint* kps, uint8_t* desc, int* n,
                            orbx_dmatch* good, int* n_good);
-/* device pointers of the last pass's results (layout as above; valid until destroy) */
+/* Blocks until the run call issued `back` calls before the most recent one has finished, downloads included (back = 0:
+ * the most recent call; 0 <= back <= 2).  Unlike orbx_sequence_sync() it does not wait for later calls and does not
+ * report truncation (ORBX_E_CAPACITY comes from orbx_sequence_sync()). */
+int orbx_sequence_wait_pass(orbx_sequence* s, int back);
+/* device pointers of the last pass's results (layout as above; orbx_sequence_run_host alternates between two sets of
+ * device arrays, so ask again after every run call) */
 int orbx_sequence_results(orbx_sequence* s, orbx_keypoint** kps, uint8_t** desc, int** n, orbx_dmatch** good,
                           int** n_good);
 int orbx_sequence_sync(orbx_sequence* s);
 /* Device-side timing of whole passes: with enable=1, CUDA events bracket everything the run calls queue on the handle's
  * four streams.  orbx_sequence_elapsed() waits for the last pass and returns the milliseconds from the start of the
- * first pass since the last reset to the end of the last one (consecutive passes run back to back: each pass starts
- * after everything the previous one queued), and how many passes that covers. */
+ * first pass since the last reset to the end of the last one (first upload / first kernel -> last download; consecutive
+ * run_host passes overlap at their seams as described above), and how many passes that covers. */
 int orbx_sequence_set_timing(orbx_sequence* s, int enable);
 int orbx_sequence_elapsed(orbx_sequence* s, float* ms, int* passes, int reset);
 

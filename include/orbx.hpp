@@ -215,7 +215,7 @@ class Sequence {
     std::vector<orbx_dmatch> good;
     std::vector<int> n_good;
   };
-  Sequence(int width, int height, int nfeatures, int max_frames, int device = 0, int chunk = 1000, int host_chunk = 167,
+  Sequence(int width, int height, int nfeatures, int max_frames, int device = 0, int chunk = 1000, int host_chunk = 250,
            float ratio = 0.75f, bool cross_check = true)
       : max_frames_(max_frames) {
     check(orbx_sequence_create(device, width, height, nfeatures, max_frames, chunk, host_chunk, ratio, cross_check ? 1 : 0,
@@ -235,6 +235,13 @@ class Sequence {
     check(orbx_sequence_sync(h_));
     return r;
   }
+  // Streaming form: queue a sequence into caller-owned (pinned) result arrays and return at once; consecutive calls are
+  // pipelined into each other.  wait_pass(1) blocks until the call before the most recent one has finished.
+  void run_async(const uint8_t* frames, int T, orbx_keypoint* kps, uint8_t* desc, int* n, orbx_dmatch* good, int* n_good) {
+    check(orbx_sequence_run_host(h_, frames, T, kps, desc, n, good, n_good));
+  }
+  void wait_pass(int back = 0) { check(orbx_sequence_wait_pass(h_, back)); }
+  void sync() { check(orbx_sequence_sync(h_)); }
 
  private:
   orbx_sequence* h_ = nullptr;

@@ -130,6 +130,7 @@ extern "C" {
     pub fn orbx_sequence_set_reference_filter(s: *mut orbx_sequence, enable: c_int, ratio: f32) -> c_int;
     pub fn orbx_sequence_run_device(s: *mut orbx_sequence, frames_dev: *const u8, pitch: usize, frame_stride: usize, T: c_int) -> c_int;
     pub fn orbx_sequence_run_host(s: *mut orbx_sequence, frames: *const u8, T: c_int, kps: *mut orbx_keypoint, desc: *mut u8, n: *mut c_int, good: *mut orbx_dmatch, n_good: *mut c_int) -> c_int;
+    pub fn orbx_sequence_wait_pass(s: *mut orbx_sequence, back: c_int) -> c_int;
     pub fn orbx_sequence_results(s: *mut orbx_sequence, kps: *mut *mut orbx_keypoint, desc: *mut *mut u8, n: *mut *mut c_int, good: *mut *mut orbx_dmatch, n_good: *mut *mut c_int) -> c_int;
     pub fn orbx_sequence_sync(s: *mut orbx_sequence) -> c_int;
     pub fn orbx_sequence_set_timing(s: *mut orbx_sequence, enable: c_int) -> c_int;

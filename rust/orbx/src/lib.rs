@@ -231,7 +231,7 @@ pub struct Sequence { h: *mut sys::orbx_sequence, width: usize, height: usize }
 impl Sequence {
     pub fn new(width: usize, height: usize, max_features: i32, max_frames: usize) -> Result<Self, Box<dyn Error>> {
         let mut h = ptr::null_mut();
-        let rc = unsafe { sys::orbx_sequence_create(0, width as i32, height as i32, max_features, max_frames as i32, 1000, 167, 0.75, 1, &mut h) };
+        let rc = unsafe { sys::orbx_sequence_create(0, width as i32, height as i32, max_features, max_frames as i32, 1000, 250, 0.75, 1, &mut h) };
         if rc != 0 { return Err(err(rc)); }
         Ok(Self { h, width, height })
     }
@@ -257,6 +257,30 @@ impl Sequence {
             FrameResult { keypoints: kps[i * cap..i * cap + k].to_vec(), descriptors: desc[i * cap * 32..(i * cap + k) * 32].to_vec(),
                           good_matches: good[i * cap..i * cap + g].to_vec() }
         }).collect())
+    }
+}
+impl Sequence {
+    /// Streaming form of `run`: queue a sequence into caller-owned result arrays (`cap` = `capacity()` rows per frame) and
+    /// return at once; consecutive calls are pipelined into each other.  The arrays belong to the library until
+    /// `wait_pass` / `sync` says the call has finished, hence `unsafe`.
+    pub unsafe fn run_async(&mut self, frames: &[u8], kps: *mut KeyPoint, desc: *mut u8, n: *mut i32, good: *mut DMatch,
+                            n_good: *mut i32) -> Result<(), Box<dyn Error>> {
+        let t = frames.len() / (self.width * self.height);
+        let rc = sys::orbx_sequence_run_host(self.h, frames.as_ptr(), t as i32, kps, desc, n, good, n_good);
+        if rc != 0 { return Err(err(rc)); }
+        Ok(())
+    }
+    pub fn capacity(&self) -> usize { unsafe { sys::orbx_sequence_capacity(self.h) as usize } }
+    /// Block until the call issued `back` calls before the most recent one has finished (0 = the most recent).
+    pub fn wait_pass(&mut self, back: i32) -> Result<(), Box<dyn Error>> {
+        let rc = unsafe { sys::orbx_sequence_wait_pass(self.h, back) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(())
+    }
+    pub fn sync(&mut self) -> Result<(), Box<dyn Error>> {
+        let rc = unsafe { sys::orbx_sequence_sync(self.h) };
+        if rc != 0 { return Err(err(rc)); }
+        Ok(())
     }
 }
 impl Drop for Sequence { fn drop(&mut self) { unsafe { sys::orbx_sequence_destroy(self.h) } } }

@@ -10,6 +10,6 @@ python - <<PY
 import json
 j=json.load(open("gpurun_out/${TAG}_bench_${N}gpu.json"))
 print("value %.0f e2e %.0f n_gpus %d" % (j["value"], j["e2e"]["value"], j["n_gpus"]))
-for k in ("hd","map","latency"):
+for k in ("hd","seqs","map","latency"):
     print(k, {a:b for a,b in j.get(k,{}).items() if a not in ("workload","timer","api")})
 PY

@@ -113,6 +113,7 @@ def _load():
         "orbx_sequence_run_host": (i, [vp, vp, i, vp, vp, vp, vp, vp]),
         "orbx_sequence_results": (i, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
         "orbx_sequence_sync": (i, [vp]),
+        "orbx_sequence_wait_pass": (i, [vp, i]),
         "orbx_sequence_set_reference_filter": (i, [vp, i, f]),
         "orbx_sequence_set_timing": (i, [vp, i]),
         "orbx_sequence_elapsed": (i, [vp, C.POINTER(f), ip, i]),

@@ -449,10 +449,22 @@ static int launch_knn_mma(orbx_matcher* m, MatchArgs a, int npairs, bool fused, 
   g.max_rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
   g.npairs = npairs;
   g.mtiles = div_up(rows_q, 128);
-  // about four units per SM; a unit streams its whole train range, so only large train sets are split
+  // A unit streams its whole train range and the persistent CTAs take units round-robin, so a pass lasts
+  // ceil(units * splits / SMs) waves of (tiles_per_split + ~2 tiles of per-unit cost: A tile fetch, drain, partial store).
+  // Few units (one large train set): pick the split count that minimises that, i.e. one that fills whole waves.
   const int ttiles = div_up(rows_t, kMmaTileN);
   const long units = (long)npairs * g.mtiles;
-  int splits = units >= (long)m->num_sms * 2 ? 1 : (int)std::min<long>(ttiles, ((long)m->num_sms * 4 + units - 1) / units);
+  int splits = 1;
+  if (units < (long)m->num_sms * 2) {
+    const long smax = std::min<long>(ttiles, std::max<long>(1, (long)m->num_sms * 16 / units));
+    long best = -1;
+    for (long sp = 1; sp <= smax; ++sp) {
+      const long tps = div_up(ttiles, (int)sp), ns = div_up(ttiles, (int)tps);
+      const long waves = (units * ns + m->num_sms - 1) / m->num_sms;
+      const long cost = waves * (tps + 2);
+      if (best < 0 || cost < best) best = cost, splits = (int)sp;
+    }
+  }
   g.tiles_per_split = div_up(ttiles, std::max(splits, 1));
   g.nsplits = div_up(ttiles, g.tiles_per_split);
   g.K = K;

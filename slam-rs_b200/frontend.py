@@ -349,7 +349,7 @@ class NativeSequence:
     host (include/orbx.hpp, rust/orbx) calls.  Frames and results are numpy / torch CPU arrays (pinned for overlap) or
     CUDA tensors; no torch stream is involved - the library owns its four streams."""
 
-    def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=1000, host_chunk=167, device=0, ratio=0.75,
+    def __init__(self, width, height, nfeatures=2000, max_frames=1000, chunk=1000, host_chunk=250, device=0, ratio=0.75,
                  cross_check=True):
         import ctypes as C
         from ._ffi import lib, check
@@ -396,6 +396,12 @@ class NativeSequence:
 
     def sync(self):
         self._check(self._lib.orbx_sequence_sync(self._h))
+
+    def wait_pass(self, back=0):
+        """Block until the run call issued ``back`` calls before the most recent one has finished (downloads included);
+        consecutive run_host calls are pipelined into each other, so a streaming host alternates two output sets and
+        consumes sequence k with ``wait_pass(1)`` while sequence k+1 runs."""
+        self._check(self._lib.orbx_sequence_wait_pass(self._h, int(back)))
 
     def set_reference_filter(self, enable=True, ratio=2.0):
         """The reference's own loop (visual_odometry.rs:106-107): match_descriptors (k=1) + filter_good_matches(ratio)

@@ -53,6 +53,66 @@ def test_native_equals_python_front_end(host_chunk):
     _valid_rows_equal(res["good"][1:], want["good"].numpy()[1:], ng[1:], "good (device pass)")
 
 
+def test_native_pipelined_passes_are_identical_to_serial_ones():
+    """Consecutive run_host calls with the same T are pipelined into each other (chunk-level events instead of a join
+    between the passes): every pass must return exactly what it returns when the passes are separated by a sync, also
+    with different sequences in flight, a device pass or another T in between, and wait_pass(1) must cover the call
+    before the most recent one."""
+    import torch
+    from oracle import synth
+    import slam_rs_b200 as s
+    from slam_rs_b200.frontend import NativeSequence
+    T, h, w, nf = 26, 240, 320, 400
+    seqs = [torch.from_numpy(synth.sequence(h, w, T, canvas_seed=70 + k, noise_seed0=500 * k)).pin_memory() for k in range(3)]
+    ns = NativeSequence(w, h, nfeatures=nf, max_frames=T, chunk=T, host_chunk=4)   # 8 chunks per pass
+    keys = ("n", "kps", "desc", "n_good", "good")
+
+    def snapshot(out):
+        return {k: out[k].numpy().copy() for k in keys}
+
+    def same(got, want, what):
+        n, ng = want["n"], want["n_good"]
+        assert np.array_equal(got["n"], n), what
+        _valid_rows_equal(got["kps"], want["kps"], n, what + " kps")
+        _valid_rows_equal(got["desc"], want["desc"], n, what + " desc")
+        assert np.array_equal(got["n_good"][1:], ng[1:]), what
+        _valid_rows_equal(got["good"][1:], want["good"][1:], ng[1:], what + " good")
+
+    serial = []
+    for k in range(3):                                                         # serial: one pass, one sync
+        out = ns.alloc_host_outputs()
+        ns.run_host(seqs[k], out)
+        ns.sync()
+        serial.append(snapshot(out))
+        dev = seqs[k].cuda()
+        ns.run_device(dev)                                                     # a device pass ends the pipelining (join)
+        ns.sync()
+    assert not np.array_equal(serial[0]["desc"], serial[1]["desc"])
+
+    outs = [ns.alloc_host_outputs() for _ in range(3)]
+    order = [0, 1, 2, 1, 0, 2, 2, 0]
+    for rep in range(3):
+        for i, k in enumerate(order):                                          # back to back, no sync in between
+            ns.run_host(seqs[k], outs[i % 3])
+            if i >= 1:
+                ns.wait_pass(1)                                                # the call before this one has finished
+                same(snapshot(outs[(i - 1) % 3]), serial[order[i - 1]], "pipelined pass %d of round %d" % (i - 1, rep))
+        ns.wait_pass(0)
+        same(snapshot(outs[(len(order) - 1) % 3]), serial[order[-1]], "last pass of round %d" % rep)
+        if rep == 0:                                                           # a shorter sequence in between: joins
+            short = ns.alloc_host_outputs()
+            ns.run_host(seqs[0][:9], short)
+            ns.sync()
+            got = snapshot(short)
+            assert np.array_equal(got["n"][:9], serial[0]["n"][:9])
+            _valid_rows_equal(got["desc"][:9], serial[0]["desc"][:9], serial[0]["n"][:9], "short pass")
+    ns.sync()
+    with pytest.raises(s.OrbxError):
+        ns.wait_pass(5)
+    ns.wait_pass(2)
+    ns.close()
+
+
 def test_native_bad_arguments():
     import slam_rs_b200 as s
     from slam_rs_b200.frontend import NativeSequence
