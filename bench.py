@@ -933,7 +933,7 @@ def main():
                     help="1: also run the sub-measurements hd (configs[2]), map (configs[3], orbx_comm over all GPUs) and "
                          "latency (configs[0]) after the headline and attach them to the line")
     ap.add_argument("--hd-frames", type=int, default=48)
-    ap.add_argument("--hd-passes", type=int, default=5)
+    ap.add_argument("--hd-passes", type=int, default=20)
     ap.add_argument("--seqs", type=int, default=8, help="sequences per GPU of the configs[4] sub-measurement")
     ap.add_argument("--map-steps", type=int, default=20)
     ap.add_argument("--latency-iters", type=int, default=200)

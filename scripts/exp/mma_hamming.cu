@@ -156,9 +156,48 @@ __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t
       "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
       : "memory");
 }
+// rate probes (operands are garbage): the same tile shape issued as kind::f8f6f4 (e4m3 x e4m3 -> f32) and as
+// kind::f16 (bf16 x bf16 -> f32, K = 16 elements = the same 32 bytes per row)
+constexpr uint32_t kIdescF8 = (1u << 4) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+constexpr uint32_t kIdescBf16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+__device__ __forceinline__ void mma_f8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdescF8), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdescBf16), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// converged-warp issue (see mma_rate.cu): warp-uniform operands, one elected lane issues
+__device__ __forceinline__ void mma_i8_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xFFFFFFFFu, v, 0); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int* v) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -259,8 +298,38 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one elected thread
-    if (lane == 0) {
+    // ===== MMA issuer: converged warp + elect (mode & 128), else one thread (the round-2 product until the rate probe)
+    if (a.mode & 128) {
+      const uint32_t tm = (uint32_t)uniform((int)tmem);
+      uint32_t ua = 0, ub = 0, tc0 = 0, tc1 = 0;
+      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+        const int p = u / a.mtiles, mt = u - p * a.mtiles;
+        const int nq = uniform(min(a.nq_dev[p], a.max_rows)), nt = uniform(min(a.nt_dev[p], a.max_rows));
+        if (mt * kTileM >= nq || nt <= 0) continue;
+        if (!(a.mode & 8)) mbar_wait(a_full, ua & 1);
+        ++ua;
+        const int ntiles = (nt + kTileN - 1) / kTileN;
+        for (int n = 0; n < ntiles; ++n, ++ub) {
+          const int s = ub & 1, buf = n & 1;
+          const uint32_t tcnt = buf ? tc1 : tc0;
+          if (!(a.mode & 256)) mbar_wait(t_empty + buf, (tcnt & 1) ^ 1);
+          if (buf) ++tc1; else ++tc0;
+          if (!(a.mode & 8)) mbar_wait(b_full + s, (ub >> 1) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBBytes);
+#pragma unroll
+          for (int k = 0; k < kKBytes / 32; ++k)
+            mma_i8_elect(tm + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+          mma_commit_elect(b_empty + s);
+          mma_commit_elect(t_full + buf);
+        }
+        mma_commit_elect(a_empty);
+      }
+      if ((a.mode & 256) && (a.mode & 8)) {  // free-running probe: nobody waited for the MMAs; a_full is unused without copies
+        mma_commit_elect(a_full);
+        mbar_wait(a_full, 0);
+      }
+    } else if (lane == 0) {
       uint32_t ua = 0, ub = 0;
       uint32_t tcount[2] = {0, 0};  // tiles issued into each TMEM buffer
       for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
@@ -285,7 +354,11 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
                        make_desc_sw128(sb + (k >> 2) * 32768 + (k & 3) * 32), k > 0);
               else
                 mma_i8(tmem + buf * kTileN, make_desc(sa), make_desc(sb), 1);
-            } else
+            } else if (a.mode & 32)
+              mma_f8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+            else if (a.mode & 64)
+              mma_bf16(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+            else
               mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
           }
           mma_commit(b_empty + s);
@@ -301,7 +374,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
     const int row = 32 * q + lane;                // row of the A tile
     int* col = s_col + g * 4 * 128;
     uint32_t tc = 0;  // tiles drained from this group's buffer
-    for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
+    for (int u = blockIdx.x; u < nunits && !(a.mode & 256); u += gridDim.x) {
       const int p = u / a.mtiles, mt = u - p * a.mtiles;
       const int nq = min(a.nq_dev[p], a.max_rows), nt = min(a.nt_dev[p], a.max_rows);
       if (mt * kTileM >= nq || nt <= 0) continue;
@@ -313,11 +386,17 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
       for (int n = buf; n < ntiles; n += 2, ++tc) {
         mbar_wait(t_full + buf, tc & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (a.mode & 512) {  // handshake only
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_empty + buf);
+          continue;
+        }
         int m1 = INT_MIN, m2 = INT_MIN;
         const uint32_t tbase = tmem + buf * kTileN + half * 128 + ((uint32_t)(32 * q) << 16);
         int va[32], vb[32];
         if (!(a.mode & 4)) tmem_ld32(tbase, va);
-        tmem_wait32(va);
+        if (!(a.mode & 1024)) tmem_wait32(va);
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           int* v = (ch & 1) ? vb : va;
@@ -325,6 +404,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
           if (ch < 3 && !(a.mode & 4)) tmem_ld32(tbase + 32 * (ch + 1), vn);  // in flight while this chunk is reduced
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
+            if (a.mode & 2048) break;
             const int x = v[j], y = v[j + 1];
             if (!(a.mode & 2)) {
               const int hi = max(x, y), lo = min(x, y);
@@ -340,7 +420,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaArgs a) {
               if (lane == 0) *reinterpret_cast<int2*>(col + q * 128 + 32 * ch + j) = make_int2(rx, ry);
             }
           }
-          if (ch < 3) tmem_wait32(vn);
+          if (ch < 3 && !(a.mode & 1024)) tmem_wait32(vn);
         }
         // this warp's share of the TMEM buffer is free for the MMA of tile n + 2
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -709,7 +789,19 @@ int main(int argc, char** argv) {
   // where the time goes: the same launch with parts of the epilogue switched off
   const struct { const char* name; bool rev; int mode; } exps[] = {
       {"full", true, 0}, {"no reverse (k=2 only)", false, 0}, {"no reverse, no best-2 math", false, 2},
-      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"MMA only: no copies either", false, 14}, {"MMA only, SW128 descriptors (layout timing, garbage data)", false, 30}, {"reverse only (no best-2 math)", true, 2}};
+      {"no reverse, no math, no TMEM loads (MMA + copies only)", false, 6}, {"MMA only: no copies either", false, 14}, {"MMA only, SW128 descriptors (layout timing, garbage data)", false, 30}, {"reverse only (no best-2 math)", true, 2},
+      {"converged-warp issue: full", true, 128}, {"converged-warp issue: no reverse (k=2 only)", false, 128},
+      {"converged-warp issue: no reverse, no best-2 math", false, 128 | 2},
+      {"converged-warp issue: no reverse, no math, no TMEM loads", false, 128 | 6},
+      {"converged-warp issue: MMA only (no copies)", false, 128 | 14},
+      {"converged-warp issue: reverse only (no best-2 math)", true, 128 | 2},
+      {"converged-warp issue: MMA only, no tcgen05.wait::ld", false, 128 | 14 | 1024},
+      {"converged-warp issue: MMA only, no inner loop", false, 128 | 14 | 2048},
+      {"converged-warp issue: MMA only, no wait::ld, no inner loop", false, 128 | 14 | 1024 | 2048},
+      {"converged-warp issue: MMA only, epilogue = wait + arrive only", false, 128 | 14 | 512},
+      {"converged-warp issue: MMA only, free running (no epilogue warps, no TMEM handshake)", false, 128 | 14 | 256},
+      {"MMA only, issued as kind::f8f6f4 (rate probe, garbage data)", false, 14 | 32},
+      {"MMA only, issued as kind::f16 bf16 (rate probe, garbage data)", false, 14 | 64}};
   for (auto& e : exps) {
     MmaArgs b = a;
     b.rev = e.rev ? d_rev : nullptr;

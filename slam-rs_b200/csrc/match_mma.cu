@@ -144,6 +144,32 @@ __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// The same two, called by a whole CONVERGED warp with warp-uniform operands; one elected lane issues.  This is what keeps
+// the descriptors in uniform registers: a single thread inside `if (lane == 0)` makes the compiler wrap every UTCIMMA in
+// an ELECT / R2UR.BROADCAST / BRA.U.ANY loop, 214 cycles per 128 x 256 x 32 MMA instead of the tensor pipe's 128
+// (scripts/exp/mma_rate.cu, profiles/r02_mma_rate.log).
+__device__ __forceinline__ void mma_i8_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+      "}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+// lane 0's value, known to the compiler as warp-uniform
+__device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xFFFFFFFFu, v, 0); }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int* v) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -188,6 +214,9 @@ __device__ __forceinline__ Unit decode_unit(const MmaMatchArgs& a, int u) {
   return w;
 }
 
+// REV: also produce the reverse (train -> query) best-1; a compile-time switch, so that the k-best-only search (map-to-frame)
+// carries none of the reverse search's instructions or branches
+template <bool REV>
 __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
@@ -245,17 +274,20 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: one elected thread
-    if (lane == 0) {
+    // ===== MMA issuer: the whole warp walks the tile loop converged (every value in it is warp-uniform), one elected
+    // lane issues the MMAs and commits
+    {
+      const uint32_t tm = (uint32_t)uniform((int)tmem);
       uint32_t ua = 0, ub = 0;
       uint32_t tcount0 = 0, tcount1 = 0;  // tiles issued into each TMEM buffer
       for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
         const Unit w = decode_unit(a, u);
-        if (!w.live) continue;
+        const int live = uniform(w.live ? 1 : 0), tile0 = uniform(w.tile0), tile1 = uniform(w.tile1);
+        if (!live) continue;
         mbar_wait(a_full, ua & 1);
         ++ua;
-        for (int n = w.tile0; n < w.tile1; ++n, ++ub) {
-          const int s = ub & 1, buf = (n - w.tile0) & 1;
+        for (int n = tile0; n < tile1; ++n, ++ub) {
+          const int s = ub & 1, buf = (n - tile0) & 1;
           const uint32_t tcnt = buf ? tcount1 : tcount0;
           mbar_wait(t_empty + buf, (tcnt & 1) ^ 1);
           if (buf) ++tcount1; else ++tcount0;
@@ -264,11 +296,11 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
           const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBBytes);
 #pragma unroll
           for (int k = 0; k < kKBytes / 32; ++k)  // last step: aux slices, chunks 16-17 of A against chunks 18-19 of B
-            mma_i8(tmem + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
-          mma_commit(b_empty + s);
-          mma_commit(t_full + buf);
+            mma_i8_elect(tm + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+          mma_commit_elect(b_empty + s);
+          mma_commit_elect(t_full + buf);
         }
-        mma_commit(a_empty);
+        mma_commit_elect(a_empty);
       }
     }
   } else {
@@ -305,7 +337,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
             const int t = min(m1, hi);
             m1 = max(m1, hi);
             m2 = max3(m2, t, lo);
-            if (a.rev) {
+            if (REV) {
               const int rx = __reduce_max_sync(0xFFFFFFFFu, x * 128 + rowbias);
               const int ry = __reduce_max_sync(0xFFFFFFFFu, y * 128 + rowbias);
               if (lane == 0) *reinterpret_cast<int2*>(col + q * 128 + 32 * ch + j) = make_int2(rx, ry);
@@ -333,7 +365,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
           b1 = min(b1, k2);
           b2 = min(b2, hi);
         }
-        if (a.rev) {
+        if (REV) {
           // column maxima over the 128 rows: four quarter results per column -> one RED.MIN per (unit, column)
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
           const int c = (warp - 2 - 4 * g) * 32 + lane;
@@ -390,9 +422,14 @@ int launch_expand_desc(const uint8_t* desc, size_t desc_stride, const int* n_dev
 }
 
 int launch_hamming_mma(const MmaMatchArgs& a, int num_sms, cudaStream_t s) {
-  ORBX_CUDA(cudaFuncSetAttribute(hamming_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   const int nunits = a.npairs * a.nsplits * a.mtiles;
-  hamming_mma_kernel<<<std::min(num_sms, nunits), kThreads, kSmemBytes, s>>>(a);
+  if (a.rev) {
+    ORBX_CUDA(cudaFuncSetAttribute(hamming_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    hamming_mma_kernel<true><<<std::min(num_sms, nunits), kThreads, kSmemBytes, s>>>(a);
+  } else {
+    ORBX_CUDA(cudaFuncSetAttribute(hamming_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    hamming_mma_kernel<false><<<std::min(num_sms, nunits), kThreads, kSmemBytes, s>>>(a);
+  }
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }
