@@ -670,6 +670,284 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel_v3(MmaArgsV3 a
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
+// ================================================================================================ v4
+// CTA PAIR (cta_group::2): a cluster of two CTAs owns a unit (problem, PAIR of 128-query tiles).  CTA r keeps the A tile
+// of query tile 2 * pair + r and loads only rows 128 r .. 128 r + 127 of every 256-row train tile: one tcgen05.mma
+// with M = 256 (issued by CTA 0) multiplies both A tiles with both B halves, read from the two CTAs' shared memory, and
+// leaves rows of A tile r x all 256 columns in CTA r's TMEM.  41 KB instead of 82 KB from L2 per 128 x 256 tile - the
+// one-CTA kernel pulls 148 x 82 KB per ~1800 cycles = the chip's L2 -> SM limit (~6.3 KB per cycle).
+//   barriers (same offsets in both CTAs): a_full / b_full[2] filled by the CTA's own bulk copies; CTA 1's warp 1 relays
+//   them to CTA 0 (remote arrive on a_peer / b_peer[2]); a_empty / b_empty[2] / t_full[2] arrive in BOTH CTAs by the
+//   multicast commit of CTA 0; t_empty[2] lives in CTA 0 and counts the 16 epilogue warps of the two CTAs that share
+//   the TMEM buffer.
+constexpr int kBHalf = kBBytes / 2;
+constexpr int kSmemV4 = kABytes + kStages * kBHalf + kGroups * 4 * 128 * 4 + 128 * 8 * 8 + 256;
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+constexpr uint32_t kIdesc2 = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTileN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+__device__ __forceinline__ void mma2_i8_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc2), "r"(accumulate)
+      : "memory");
+}
+// completion of everything issued so far arrives on the barrier at this offset in both CTAs of the pair
+__device__ __forceinline__ void mma2_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t.reg .b16 m;\n\tmov.b16 m, 3;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(
+          smem_u32(bar))
+      : "memory");
+}
+
+template <bool REV>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) hamming_mma_kernel_v4(MmaArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kABytes;
+  int* s_col = reinterpret_cast<int*>(smem + kABytes + kStages * kBHalf);
+  unsigned long long* s_merge = reinterpret_cast<unsigned long long*>(s_col + kGroups * 4 * 128);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_merge + 128 * 8);
+  uint64_t* a_full = bars + 0;
+  uint64_t* a_empty = bars + 1;
+  uint64_t* b_full = bars + 2;   // [2]
+  uint64_t* b_empty = bars + 4;  // [2]
+  uint64_t* t_full = bars + 6;   // [2]
+  uint64_t* t_empty = bars + 8;  // [2]  CTA 0's are used
+  uint64_t* a_peer = bars + 10;  //      CTA 0's: CTA 1's A tile has landed
+  uint64_t* b_peer = bars + 11;  // [2]  CTA 0's: CTA 1's B half has landed
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 13);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_rank();
+  if (threadIdx.x == 0) {
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1);
+    mbar_init(a_peer, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(b_full + i, 1);
+      mbar_init(b_empty + i, 1);
+      mbar_init(b_peer + i, 1);
+      mbar_init(t_full + i, 1);
+      mbar_init(t_empty + i, 16);  // the epilogue warps of both CTAs that drain this buffer
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+
+  const int mpairs = (a.mtiles + 1) / 2;
+  const int nunits = a.npairs * mpairs;
+  const int cid = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+  // a unit is live for the PAIR (both CTAs walk the same tiles); rows of a query tile past nq are inactive
+#define V4_UNIT                                                                                   \
+  const int p = u / mpairs, mp = u - p * mpairs;                                                  \
+  const int nq = uniform(min(a.nq_dev[p], a.max_rows)), nt = uniform(min(a.nt_dev[p], a.max_rows)); \
+  if (2 * mp * kTileM >= nq || nt <= 0) continue;                                                 \
+  const int mt = 2 * mp + (int)rank;                                                              \
+  const int ntiles = (nt + kTileN - 1) / kTileN;
+
+  if (warp == 0) {
+    // ===== producer (each CTA: its A tile, its half of every B tile); the warp stays converged, lane 0 copies
+    {
+      uint32_t ua = 0, ub = 0;
+      for (int u = cid; u < nunits; u += nclusters) {
+        V4_UNIT
+        mbar_wait(a_empty, (ua & 1) ^ 1);
+        if (lane == 0) {
+          mbar_expect_tx(a_full, kABytes);
+          bulk_g2s(sA, a.ea + p * a.ea_stride + (size_t)mt * kABytes, kABytes, a_full);
+        }
+        ++ua;
+        for (int n = 0; n < ntiles; ++n, ++ub) {
+          const int s = ub & 1;
+          mbar_wait(b_empty + s, ((ub >> 1) & 1) ^ 1);
+          if (lane == 0) {
+            mbar_expect_tx(b_full + s, kBHalf);
+            bulk_g2s(sB + s * kBHalf, a.eb + p * a.eb_stride + (size_t)n * kBBytes + (size_t)rank * kBHalf, kBHalf, b_full + s);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp == 1 && rank == 1) {
+    // ===== relay: tell CTA 0 that this CTA's operands have landed
+    uint32_t ua = 0, ub = 0;
+    for (int u = cid; u < nunits; u += nclusters) {
+      V4_UNIT
+      (void)mt;
+      mbar_wait(a_full, ua & 1);
+      ++ua;
+      if (lane == 0) mbar_arrive_remote(a_peer, 0);
+      for (int n = 0; n < ntiles; ++n, ++ub) {
+        const int s = ub & 1;
+        mbar_wait(b_full + s, (ub >> 1) & 1);
+        if (lane == 0) mbar_arrive_remote(b_peer + s, 0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (CTA 0): converged warp, one elected lane
+    const uint32_t tm = (uint32_t)uniform((int)tmem);
+    uint32_t ua = 0, ub = 0, tc0 = 0, tc1 = 0;
+    for (int u = cid; u < nunits; u += nclusters) {
+      V4_UNIT
+      (void)mt;
+      mbar_wait(a_full, ua & 1);
+      mbar_wait_cluster(a_peer, ua & 1);
+      ++ua;
+      for (int n = 0; n < ntiles; ++n, ++ub) {
+        const int s = ub & 1, buf = n & 1;
+        const uint32_t tcnt = buf ? tc1 : tc0;
+        mbar_wait_cluster(t_empty + buf, (tcnt & 1) ^ 1);
+        if (buf) ++tc1; else ++tc0;
+        mbar_wait(b_full + s, (ub >> 1) & 1);
+        mbar_wait_cluster(b_peer + s, (ub >> 1) & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t sa = smem_u32(sA), sb = smem_u32(sB + s * kBHalf);
+#pragma unroll
+        for (int k = 0; k < kKBytes / 32; ++k)
+          mma2_i8_elect(tm + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
+        mma2_commit_elect(b_empty + s);
+        mma2_commit_elect(t_full + buf);
+      }
+      mma2_commit_elect(a_empty);
+    }
+  } else {
+    // ===== epilogue (both CTAs, each on its own TMEM): as v2, t_empty arrivals go to CTA 0
+    const int g = (warp - 2) >> 2, q = warp & 3;
+    const int buf = g >> 1, half = g & 1;
+    const int row = 32 * q + lane;
+    int* col = s_col + g * 4 * 128;
+    uint32_t tc = 0;
+    for (int u = cid; u < nunits; u += nclusters) {
+      V4_UNIT
+      const int qi = mt * kTileM + row;
+      const bool active = qi < nq;
+      const int rowbias = active ? 127 - row : -(1 << 30);
+      unsigned long long b1 = ~0ull, b2 = ~0ull;
+      for (int n = buf; n < ntiles; n += 2, ++tc) {
+        mbar_wait(t_full + buf, tc & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        int m1 = INT_MIN, m2 = INT_MIN;
+        const uint32_t tbase = tmem + buf * kTileN + half * 128 + ((uint32_t)(32 * q) << 16);
+        int va[32], vb[32];
+        tmem_ld32(tbase, va);
+        tmem_wait32(va);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          int* v = (ch & 1) ? vb : va;
+          int* vn = (ch & 1) ? va : vb;
+          if (ch < 3) tmem_ld32(tbase + 32 * (ch + 1), vn);
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const int x = v[j], y = v[j + 1];
+            const int hi = max(x, y), lo = min(x, y);
+            const int t = min(m1, hi);
+            m1 = max(m1, hi);
+            m2 = max3(m2, t, lo);
+            if (REV) {
+              const int rx = __reduce_max_sync(0xFFFFFFFFu, x * 128 + rowbias);
+              const int ry = __reduce_max_sync(0xFFFFFFFFu, y * 128 + rowbias);
+              if (lane == 0) *reinterpret_cast<int2*>(col + q * 128 + 32 * ch + j) = make_int2(rx, ry);
+            }
+          }
+          if (ch < 3) tmem_wait32(vn);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(t_empty + buf, 0);
+        const int nt0 = n * kTileN;
+        if (m1 > kInvalid) {
+          const unsigned long long k1 =
+              ((unsigned long long)(unsigned)(128 - (m1 >> 9)) << 32) | (unsigned long long)(nt0 + 255 - (m1 & 511));
+          const unsigned long long hi = max(b1, k1);
+          b1 = min(b1, k1);
+          b2 = min(b2, hi);
+        }
+        if (m2 > kInvalid) {
+          const unsigned long long k2 =
+              ((unsigned long long)(unsigned)(128 - (m2 >> 9)) << 32) | (unsigned long long)(nt0 + 255 - (m2 & 511));
+          const unsigned long long hi = max(b1, k2);
+          b1 = min(b1, k2);
+          b2 = min(b2, hi);
+        }
+        if (REV) {
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+          const int c = (warp - 2 - 4 * g) * 32 + lane;
+          const int n0 = nt0 + half * 128;
+          const int m = max(max(col[c], col[128 + c]), max(col[256 + c], col[384 + c]));
+          if (n0 + c < nt && m > kInvalid * 128) {
+            const unsigned d = (unsigned)(128 - (m >> 16));
+            const unsigned r = (unsigned)(127 - (m & 127));
+            atomicMin(a.rev + (size_t)p * a.max_rows + n0 + c,
+                      ((unsigned long long)d << 32) | (unsigned long long)(mt * kTileM + r));
+          }
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
+        }
+      }
+      if (g > 0) {
+        s_merge[((g - 1) * 128 + row) * 2] = b1;
+        s_merge[((g - 1) * 128 + row) * 2 + 1] = b2;
+      }
+      asm volatile("bar.sync 5, 512;" ::: "memory");
+      if (g == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const unsigned long long o1 = s_merge[(k * 128 + row) * 2], o2 = s_merge[(k * 128 + row) * 2 + 1];
+          const unsigned long long hi = max(b1, o1);
+          b1 = min(b1, o1);
+          b2 = min(min(b2, o2), hi);
+        }
+        if (active) {
+          unsigned long long* o = a.best + ((size_t)p * a.max_rows + qi) * 2;
+          o[0] = b1;
+          o[1] = b2;
+        }
+      }
+      asm volatile("bar.sync 5, 512;" ::: "memory");
+    }
+  }
+#undef V4_UNIT
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
 // ------------------------------------------------------------------------------------------------ host
 static unsigned popc256(const uint8_t* a, const uint8_t* b) {
   unsigned d = 0;
@@ -868,6 +1146,48 @@ int main(int argc, char** argv) {
         }
       }
       printf("v3 checked %ld results, %ld mismatches -> %s\n", chk3, bad3, bad3 ? "FAIL" : "OK (bit-exact)");
+    }
+  }
+  // ---- v4: CTA pairs (cta_group::2), each CTA loads half of every B tile
+  if (!getenv("SKIP_V4")) {
+    CK(cudaFuncSetAttribute(hamming_mma_kernel_v4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemV4));
+    CK(cudaFuncSetAttribute(hamming_mma_kernel_v4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemV4));
+    const int grid = sms & ~1;
+    for (int withrev = 1; withrev >= 0; --withrev) {
+      MmaArgs b = a;
+      b.mode = 0;
+      b.rev = withrev ? d_rev : nullptr;
+      for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaMemset(d_best, 0xFF, (size_t)npairs * cap * 2 * sizeof(unsigned long long)));
+        CK(cudaMemset(d_rev, 0xFF, (size_t)npairs * cap * sizeof(unsigned long long)));
+        cudaEventRecord(e1);
+        if (withrev)
+          hamming_mma_kernel_v4<true><<<grid, kThreads, kSmemV4>>>(b);
+        else
+          hamming_mma_kernel_v4<false><<<grid, kThreads, kSmemV4>>>(b);
+        cudaEventRecord(e2);
+        CK(cudaDeviceSynchronize());
+        float ms;
+        cudaEventElapsedTime(&ms, e1, e2);
+        printf("v4 (CTA pair, smem %d)%s rep %d: %.3f ms\n", kSmemV4, withrev ? "" : " no reverse", rep, ms);
+      }
+      std::vector<unsigned long long> best4(best.size()), rev4(rev.size());
+      CK(cudaMemcpy(best4.data(), d_best, best4.size() * 8, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(rev4.data(), d_rev, rev4.size() * 8, cudaMemcpyDeviceToHost));
+      long bad4 = 0;
+      for (size_t i = 0; i < best.size(); ++i)
+        if (best4[i] != best[i]) {
+          if (bad4 < 8) printf("v4 best[%zu] (pair %zu row %zu k %zu): got %016llx want %016llx\n", i, i / (2 * cap), (i / 2) % cap, i & 1, best4[i], best[i]);
+          ++bad4;
+        }
+      if (withrev)
+        for (size_t i = 0; i < rev.size(); ++i)
+          if (rev4[i] != rev[i]) {
+            if (bad4 < 16) printf("v4 rev[%zu]: got %016llx want %016llx\n", i, rev4[i], rev[i]);
+            ++bad4;
+          }
+      printf("v4 compared %zu + %zu results with v2, %ld mismatches -> %s\n", best.size(), withrev ? rev.size() : (size_t)0, bad4,
+             bad4 ? "FAIL" : "OK (bit-exact)");
     }
   }
   return bad ? 1 : 0;

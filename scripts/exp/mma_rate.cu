@@ -214,6 +214,130 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int N, int layout, int src
   if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
+// TMEM read rate: `nwarps` warps (warp w reads lanes 32 (w % 4) ..+31) read 256 columns with tcgen05.ld 32x32b.x32, `iters`
+// times; reported per 128 lanes x 256 columns x 4 B = 128 KB (one accumulator tile of the matcher)
+template <int inflight>
+__global__ void __launch_bounds__(512, 1) ldtm_kernel(int iters, Result* out, int* sink) {
+  __shared__ uint32_t s_tmem;
+  if (threadIdx.x < 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s_tmem;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t tbase = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + (warp >> 2) * (256 / (blockDim.x / 128));
+  const int ncols = 256 / (blockDim.x / 128);  // columns per warp: the warps that share a lane quarter split the 256 columns
+  int acc = 0;
+  __syncthreads();
+  const long long c0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+    for (int c = 0; c < ncols; c += 32 * inflight) {
+      int v[inflight][32];
+#pragma unroll
+      for (int k = 0; k < inflight; ++k)
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[k][0]), "=r"(v[k][1]), "=r"(v[k][2]), "=r"(v[k][3]), "=r"(v[k][4]), "=r"(v[k][5]), "=r"(v[k][6]), "=r"(v[k][7]),
+              "=r"(v[k][8]), "=r"(v[k][9]), "=r"(v[k][10]), "=r"(v[k][11]), "=r"(v[k][12]), "=r"(v[k][13]), "=r"(v[k][14]),
+              "=r"(v[k][15]), "=r"(v[k][16]), "=r"(v[k][17]), "=r"(v[k][18]), "=r"(v[k][19]), "=r"(v[k][20]), "=r"(v[k][21]),
+              "=r"(v[k][22]), "=r"(v[k][23]), "=r"(v[k][24]), "=r"(v[k][25]), "=r"(v[k][26]), "=r"(v[k][27]), "=r"(v[k][28]),
+              "=r"(v[k][29]), "=r"(v[k][30]), "=r"(v[k][31])
+            : "r"(tbase + c + 32 * k)
+            : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < inflight; ++k) acc ^= v[k][0] ^ v[k][31];
+    }
+  }
+  __syncthreads();
+  const long long c1 = clock64();
+  if (threadIdx.x == 0) out[blockIdx.x].cycles = c1 - c0;
+  if (acc == 0x12345678) *sink = acc;
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+// cta_group::2: a cluster of two CTAs, CTA 0's warp 0 issues M = 256 MMAs (A tile and B half of each CTA in its own
+// shared memory), multicast commit to both CTAs; cycles per MMA as seen by the issuer
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) rate2_kernel(int N, int tiles, int depth, int kper, Result* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bars[3];
+  __shared__ uint32_t s_tmem;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  for (int i = threadIdx.x; i < kSmem / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x01FF01FFu * (1 + (i & 1));
+  if (threadIdx.x == 0) {
+    mbar_init(bars, 1);
+    mbar_init(bars + 1, 1);
+    mbar_init(bars + 2, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x < 32) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = s_tmem;
+  if (rank == 0 && threadIdx.x < 32) {
+    const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+    const uint32_t sa = smem_u32(smem), sb = sa + 128 * kRowBytes;
+    uint32_t ph[2] = {0, 0};
+    long long c0 = clock64();
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int t = 0; t < tiles; ++t) {
+      const int buf = t & 1;
+      if (t >= depth) {
+        const int wb = (t - depth) & 1;
+        mbar_wait(bars + wb, ph[wb] & 1);
+        ++ph[wb];
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      }
+      const uint32_t d = tmem + buf * 256;
+#pragma unroll
+      for (int k = 0; k < 9; ++k)
+        if (k < kper)
+          asm volatile(
+              "{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+              "@e tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+              "l"(desc_none(sa + k * 256, kGroup)), "l"(desc_none(sb + k * 256, kGroup)), "r"(idesc), "r"((uint32_t)(k > 0))
+              : "memory");
+      asm volatile(
+          "{\n\t.reg .pred e;\n\t.reg .b16 m;\n\tmov.b16 m, 3;\n\telect.sync _|e, 0xffffffff;\n\t"
+          "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(
+              smem_u32(bars + buf))
+          : "memory");
+    }
+    asm volatile(
+        "{\n\t.reg .pred e;\n\t.reg .b16 m;\n\tmov.b16 m, 3;\n\telect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(
+            smem_u32(bars + 2))
+        : "memory");
+    mbar_wait(bars + 2, 0);
+    long long c1 = clock64();
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (threadIdx.x == 0) {
+      out[blockIdx.x >> 1].cycles = c1 - c0;
+      out[blockIdx.x >> 1].ns = t1 - t0;
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (threadIdx.x < 32) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
 template <int KIND>
 int run(const char* kind, int grid, int N, int layout, int src, int tiles, int depth, int kper, Result* d_out) {
   CK(cudaFuncSetAttribute(rate_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
@@ -237,7 +361,46 @@ int main() {
   setvbuf(stdout, nullptr, _IONBF, 0);
   Result* d_out;
   CK(cudaMalloc(&d_out, sizeof(Result) * 148));
+  {
+    int* sink;
+    CK(cudaMalloc(&sink, 4));
+    for (int grid : {1, 148})
+      for (int threads : {128, 256, 512})
+        for (int inflight : {1, 2}) {
+          const int iters = 2000;
+          for (int rep = 0; rep < 2; ++rep) {
+            if (inflight == 1)
+              ldtm_kernel<1><<<grid, threads>>>(iters, d_out, sink);
+            else
+              ldtm_kernel<2><<<grid, threads>>>(iters, d_out, sink);
+          }
+          CK(cudaDeviceSynchronize());
+          Result h[148];
+          CK(cudaMemcpy(h, d_out, sizeof(Result) * grid, cudaMemcpyDeviceToHost));
+          long long cmax = 0;
+          for (int i = 0; i < grid; ++i) cmax = h[i].cycles > cmax ? h[i].cycles : cmax;
+          printf("LDTM 32x32b.x32: grid %3d, %2d warps, %d loads in flight per warp: %7.1f cycles per 128 KB tile (%.1f B/cycle/SM)\n", grid,
+                 threads / 32, inflight, (double)cmax / iters, 131072.0 * iters / cmax);
+        }
+  }
   const int tiles = 2000;
+  CK(cudaFuncSetAttribute(rate2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+  for (int grid : {2, 148})
+    for (int N : {256, 128})
+      for (int depth : {2, tiles}) {
+        for (int rep = 0; rep < 2; ++rep) rate2_kernel<<<grid, 128, kSmem>>>(N, tiles, depth, 9, d_out);
+        CK(cudaDeviceSynchronize());
+        Result h[74];
+        CK(cudaMemcpy(h, d_out, sizeof(Result) * (grid / 2), cudaMemcpyDeviceToHost));
+        long long cmax = 0;
+        unsigned long long nmax = 0;
+        for (int i = 0; i < grid / 2; ++i) {
+          cmax = h[i].cycles > cmax ? h[i].cycles : cmax;
+          nmax = h[i].ns > nmax ? h[i].ns : nmax;
+        }
+        printf("i8 cta_group::2 (M 256) grid %3d N %3d depth %4d: %7.1f cycles per MMA, %6.1f ns per group of 9, clock %.0f MHz\n", grid, N,
+               depth, (double)cmax / (tiles * 9.0), (double)nmax / tiles, 1e3 * cmax / (double)nmax);
+      }
   for (int grid : {1, 148}) {
     for (int N : {256, 128}) {
       run<0>("i8", grid, N, 0, 0, tiles, 2, 9, d_out);
