@@ -176,7 +176,9 @@ void slice(int nq, int ndev, int r, int* lo, int* hi) {
 // the resident train set changed: every rank expands its copy once for the tensor-core kernel (in stream order behind
 // the broadcast), so that the per-frame calls only expand their query slice
 int cache_train(orbx_comm* c) {
-  if ((double)c->nt * 64 < 134217728.0) return ORBX_OK;  // small train sets go to the POPC kernel anyway
+  // a slice goes to the tensor-core kernel when slice rows x train rows >= 2^27: below 2^27 / 8192 train rows no
+  // sensible slice does, and the expanded copy (320 B per row) would be dead weight
+  if (c->nt < 16384) return ORBX_OK;
   for (int r = 0; r < c->ndev; ++r)
     if (int rc = orbx::matcher_cache_train(c->m[r], c->train[r], c->nt)) return rc;
   return ORBX_OK;

@@ -488,8 +488,12 @@ static int launch_knn(orbx_matcher* m, MatchArgs a, int npairs, bool fused = fal
   const int rows_q = a.nq_dev ? a.max_rows : a.nq_fixed;
   const int rows_t = a.nt_dev ? a.max_rows : a.nt_fixed;
   if (rows_q <= 0 || npairs <= 0) return ORBX_OK;
-  // tensor-core path for problems that fill the chip (>= 2^27 descriptor pairs); the POPC kernel below for small ones
-  if (rows_t > 0 && (m->mode == 2 || (m->mode == 0 && (double)npairs * rows_q * rows_t >= 134217728.0)))
+  // tensor-core path for problems that fill the chip (>= 2^27 descriptor pairs); the POPC kernel below for small ones.
+  // Against a RESIDENT train set (matcher_cache_train: its expansion is already paid) the tensor cores win from 2^23
+  // pairs on: 128 queries x 1 M rows take 0.67 ms on the POPC pipe.
+  const bool resident = npairs == 1 && !a.nt_dev && m->cached_t == a.t && m->cached_nt == a.nt_fixed && m->buf[B_EXPT];
+  const double pairs = (double)npairs * rows_q * rows_t;
+  if (rows_t > 0 && (m->mode == 2 || (m->mode == 0 && (pairs >= 134217728.0 || (resident && pairs >= 8388608.0)))))
     return launch_knn_mma<K>(m, a, npairs, fused, rows_q, rows_t);
   const int qtiles = div_up(rows_q, kQPB);
   // about four waves of blocks (10 resident per SM) so that the last, partly filled wave costs little, but never

@@ -62,14 +62,16 @@ def test_sharded_device_pointers_and_train_update(orbx):
     """Device-resident queries / results on devices[0] (asynchronous path) and a second set_train (map update)."""
     import torch
     from slam_rs_b200.mapmatch import ShardedMatcher
-    m, f = synth.map_and_frame_descriptors(9000, 640, f=1)
+    m, f = synth.map_and_frame_descriptors(40000, 640, f=1)
     for devs in device_lists()[1:]:
         sm = ShardedMatcher(devs)
         q = torch.from_numpy(f).cuda(0)
         out = torch.zeros((len(f), 2, 16), dtype=torch.uint8, device="cuda:0")
         cnt = torch.zeros((len(f),), dtype=torch.int32, device="cuda:0")
         torch.cuda.synchronize()
-        for train in (m[:4000], m):                         # the larger set re-allocates and re-broadcasts
+        # the larger sets re-allocate and re-broadcast; from 16384 rows on the ranks keep an expanded copy of the train set
+        # for the tensor-core kernel, which every set_train must refresh
+        for train in (m[:4000], m[:20000], m[20000:], m):
             sm.set_train(torch.from_numpy(train).cuda(0))
             sm.knn_match_device(q, out, cnt)
             sm.sync()
