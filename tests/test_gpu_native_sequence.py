@@ -107,6 +107,20 @@ def test_native_pipelined_passes_are_identical_to_serial_ones():
             assert np.array_equal(got["n"][:9], serial[0]["n"][:9])
             _valid_rows_equal(got["desc"][:9], serial[0]["desc"][:9], serial[0]["n"][:9], "short pass")
     ns.sync()
+    # different lengths back to back without a sync: the chunk-level waits go by frame range, not by chunk index
+    short = ns.alloc_host_outputs()
+    ns.run_host(seqs[0], outs[0])
+    ns.run_host(seqs[1][:9], short)
+    ns.run_host(seqs[2], outs[2])
+    ns.run_host(seqs[0][:17], outs[1])
+    ns.sync()
+    same(snapshot(outs[0]), serial[0], "long pass before a short one")
+    same(snapshot(outs[2]), serial[2], "long pass after a short one")
+    for got, k, n9 in ((snapshot(short), 1, 9), (snapshot(outs[1]), 0, 17)):
+        assert np.array_equal(got["n"][:n9], serial[k]["n"][:n9])
+        _valid_rows_equal(got["desc"][:n9], serial[k]["desc"][:n9], serial[k]["n"][:n9], "short pipelined pass desc")
+        assert np.array_equal(got["n_good"][1:n9], serial[k]["n_good"][1:n9])
+        _valid_rows_equal(got["good"][1:n9], serial[k]["good"][1:n9], serial[k]["n_good"][1:n9], "short pipelined pass good")
     with pytest.raises(s.OrbxError):
         ns.wait_pass(5)
     ns.wait_pass(2)
