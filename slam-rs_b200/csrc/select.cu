@@ -375,6 +375,36 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(DevGeom g, int sort
   }
   for (uint32_t i = nsel + tid; i < n2; i += kSelThreads) buf[i] = 0ull;
   __syncthreads();
+  if (off == kSelInline && n2 <= (uint32_t)kSelThreads) {
+    // The usual case (a level's selection fits one element per thread): bitonic sort with the element in a register -
+    // partner exchange by warp shuffle while the partner is in the same warp (j < 32), through shared memory otherwise:
+    // 10 instead of 45 block barriers for 512 keys.  Keys are unique (position in the low word), so the result is the
+    // same permutation as the generic loop's below.
+    unsigned long long v = (uint32_t)tid < n2 ? s_sort[tid] : 0ull;
+    for (uint32_t k = 2; k <= n2; k <<= 1) {
+      for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+        unsigned long long o;
+        if (j >= 32) {
+          __syncthreads();  // everyone has read its partner of the stage before
+          if ((uint32_t)tid < n2) s_sort[tid] = v;
+          __syncthreads();
+          o = (uint32_t)tid < n2 ? s_sort[tid ^ j] : 0ull;
+        } else {
+          o = __shfl_xor_sync(0xFFFFFFFFu, v, (int)j);
+        }
+        // descending runs where (i & k) == 0: there the lower index of a pair keeps the larger key
+        const bool keep_max = (((uint32_t)tid & j) == 0) == (((uint32_t)tid & k) == 0);
+        v = keep_max ? max(v, o) : min(v, o);
+      }
+    }
+    unsigned long long* sel = L.sel + (size_t)frame * L.sel_cap;
+    if ((uint32_t)tid < nsel) sel[tid] = v;
+    if (tid == 0) {
+      g.sel_count[fl] = nsel;
+      g.sel_off[fl] = off;
+    }
+    return;
+  }
   // bitonic sort, descending (block-private region: __syncthreads orders the global-memory passes too)
   for (uint32_t k = 2; k <= n2; k <<= 1) {
     for (uint32_t j = k >> 1; j > 0; j >>= 1) {
