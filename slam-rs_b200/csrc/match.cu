@@ -21,6 +21,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -453,14 +454,16 @@ static int launch_knn_mma(orbx_matcher* m, MatchArgs a, int npairs, bool fused, 
   // ceil(units * splits / SMs) waves of (tiles_per_split + ~2 tiles of per-unit cost: A tile fetch, drain, partial store).
   // Few units (one large train set): pick the split count that minimises that, i.e. one that fills whole waves.
   const int ttiles = div_up(rows_t, kMmaTileN);
-  const long units = (long)npairs * g.mtiles;
+  const bool pair = mma_use_pairs(g.mtiles, fused) && m->num_sms >= 2;
+  const long units = (long)npairs * (pair ? (g.mtiles + 1) / 2 : g.mtiles);
+  const long workers = pair ? std::max(m->num_sms / 2, 1) : m->num_sms;
   int splits = 1;
-  if (units < (long)m->num_sms * 2) {
-    const long smax = std::min<long>(ttiles, std::max<long>(1, (long)m->num_sms * 16 / units));
+  if (units < workers * 2) {
+    const long smax = std::min<long>(ttiles, std::max<long>(1, workers * 16 / units));
     long best = -1;
     for (long sp = 1; sp <= smax; ++sp) {
       const long tps = div_up(ttiles, (int)sp), ns = div_up(ttiles, (int)tps);
-      const long waves = (units * ns + m->num_sms - 1) / m->num_sms;
+      const long waves = (units * ns + workers - 1) / workers;
       const long cost = waves * (tps + 2);
       if (best < 0 || cost < best) best = cost, splits = (int)sp;
     }

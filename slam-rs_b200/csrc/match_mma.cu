@@ -25,6 +25,7 @@
 #include <limits.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "match_mma.cuh"
 
@@ -170,6 +171,40 @@ __device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
 }
 // lane 0's value, known to the compiler as warp-uniform
 __device__ __forceinline__ int uniform(int v) { return __shfl_sync(0xFFFFFFFFu, v, 0); }
+
+// ---- CTA pairs that share their B tiles (PAIR instances of the kernel)
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// bulk copy global -> the same shared-memory offset of BOTH CTAs of the pair; every destination CTA's barrier at the
+// offset of `bar` receives the bytes
+__device__ __forceinline__ void bulk_g2s_pair(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b16 m;\n\t"
+      "mov.b16 m, 3;\n\t"
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], m;\n\t"
+      "}" ::"r"(smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// completion of the MMAs issued so far arrives on the barrier at this offset in both CTAs of the pair
+__device__ __forceinline__ void mma_commit_pair_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred e;\n\t"
+      ".reg .b16 m;\n\t"
+      "mov.b16 m, 3;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t"
+      "}" ::"r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int* v) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -199,10 +234,15 @@ struct Unit {
   int p, sp, mt, nq, nt, tile0, tile1;  // tiles [tile0, tile1) of the train set
   bool live;
 };
-__device__ __forceinline__ Unit decode_unit(const MmaMatchArgs& a, int u) {
+// PAIR: a unit is a PAIR of query tiles, CTA `rank` of the cluster takes tile 2 * pair + rank; the unit is live for the
+// pair (both CTAs walk the same train tiles, which they share), rows of a query tile past nq are simply inactive
+template <bool PAIR>
+__device__ __forceinline__ Unit decode_unit(const MmaMatchArgs& a, int u, int rank) {
   Unit w;
-  w.mt = u % a.mtiles;
-  const int r = u / a.mtiles;
+  const int per = PAIR ? (a.mtiles + 1) >> 1 : a.mtiles;
+  const int m0 = u % per;
+  w.mt = PAIR ? 2 * m0 + rank : m0;
+  const int r = u / per;
   w.sp = r % a.nsplits;
   w.p = r / a.nsplits;
   w.nq = a.nq_dev ? min(a.nq_dev[w.p], a.max_rows) : a.nq_fixed;
@@ -210,13 +250,18 @@ __device__ __forceinline__ Unit decode_unit(const MmaMatchArgs& a, int u) {
   const int ntiles = (w.nt + kTileN - 1) / kTileN;
   w.tile0 = min(ntiles, w.sp * a.tiles_per_split);
   w.tile1 = min(ntiles, w.tile0 + a.tiles_per_split);
-  w.live = w.mt * kTileM < w.nq && w.tile0 < w.tile1;
+  w.live = (PAIR ? 2 * m0 : m0) * kTileM < w.nq && w.tile0 < w.tile1;
   return w;
 }
 
 // REV: also produce the reverse (train -> query) best-1; a compile-time switch, so that the k-best-only search (map-to-frame)
 // carries none of the reverse search's instructions or branches
-template <bool REV>
+// PAIR: launched as clusters of two CTAs that take the two query tiles of a pair and SHARE every B tile: each CTA loads
+// one half (41 KB) and the bulk copy multicasts it into both CTAs' shared memory, so a 128 x 256 tile costs 41 KB
+// instead of 82 KB of L2 -> SM traffic (the limit of the k-best-only search: 148 x 82 KB per 1800-cycle tile is the
+// chip's LTS rate).  Everything else stays per CTA - own A tile, own MMAs (cta_group::1), own TMEM hand-off; only the
+// B ring is coupled: a stage is refilled when BOTH CTAs have consumed it (their commits arrive on both b_empty).
+template <bool REV, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sA = smem;
@@ -238,7 +283,7 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
     mbar_init(a_empty, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(b_full + i, 1);
-      mbar_init(b_empty + i, 1);
+      mbar_init(b_empty + i, PAIR ? 2 : 1);  // PAIR: this CTA's and the peer's MMA warp
       mbar_init(t_full + i, 1);
       mbar_init(t_empty + i, 8);  // one arrival per epilogue warp of the two groups that share the buffer
     }
@@ -250,16 +295,20 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = *s_tmem;
 
-  const int nunits = a.npairs * a.nsplits * a.mtiles;
+  const int rank = PAIR ? (int)cluster_rank() : 0;
+  const int cid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nworkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int nunits = a.npairs * a.nsplits * (PAIR ? (a.mtiles + 1) >> 1 : a.mtiles);
   if (warp == 0) {
     // ===== producer: bulk copies global -> shared, completion on the full barriers
     if (lane == 0) {
       uint32_t ua = 0, ub = 0;  // units / B tiles issued so far
-      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-        const Unit w = decode_unit(a, u);
+      for (int u = cid; u < nunits; u += nworkers) {
+        const Unit w = decode_unit<PAIR>(a, u, rank);
         if (!w.live) continue;
         mbar_wait(a_empty, (ua & 1) ^ 1);
         mbar_expect_tx(a_full, kABytes);
@@ -268,8 +317,12 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
         for (int n = w.tile0; n < w.tile1; ++n, ++ub) {
           const int s = ub & 1;
           mbar_wait(b_empty + s, ((ub >> 1) & 1) ^ 1);
-          mbar_expect_tx(b_full + s, kBBytes);
-          bulk_g2s(sB + s * kBBytes, a.eb + (size_t)w.p * a.eb_stride + (size_t)n * kBBytes, kBBytes, b_full + s);
+          mbar_expect_tx(b_full + s, kBBytes);  // PAIR: half from this CTA's copy, half from the peer's
+          const uint8_t* src = a.eb + (size_t)w.p * a.eb_stride + (size_t)n * kBBytes;
+          if (PAIR)
+            bulk_g2s_pair(sB + s * kBBytes + rank * (kBBytes / 2), src + rank * (kBBytes / 2), kBBytes / 2, b_full + s);
+          else
+            bulk_g2s(sB + s * kBBytes, src, kBBytes, b_full + s);
         }
       }
     }
@@ -280,8 +333,8 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
       const uint32_t tm = (uint32_t)uniform((int)tmem);
       uint32_t ua = 0, ub = 0;
       uint32_t tcount0 = 0, tcount1 = 0;  // tiles issued into each TMEM buffer
-      for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-        const Unit w = decode_unit(a, u);
+      for (int u = cid; u < nunits; u += nworkers) {
+        const Unit w = decode_unit<PAIR>(a, u, rank);
         const int live = uniform(w.live ? 1 : 0), tile0 = uniform(w.tile0), tile1 = uniform(w.tile1);
         if (!live) continue;
         mbar_wait(a_full, ua & 1);
@@ -297,7 +350,10 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
 #pragma unroll
           for (int k = 0; k < kKBytes / 32; ++k)  // last step: aux slices, chunks 16-17 of A against chunks 18-19 of B
             mma_i8_elect(tm + buf * kTileN, make_desc(sa + k * 256), make_desc(sb + k * 256 + (k == 8 ? 256 : 0)), k > 0);
-          mma_commit_elect(b_empty + s);
+          if (PAIR)
+            mma_commit_pair_elect(b_empty + s);  // both CTAs' producers learn that this CTA is done with the stage
+          else
+            mma_commit_elect(b_empty + s);
           mma_commit_elect(t_full + buf);
         }
         mma_commit_elect(a_empty);
@@ -310,8 +366,8 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
     const int row = 32 * q + lane;                // row of the A tile
     int* col = s_col + g * 4 * 128;
     uint32_t tc = 0;  // tiles drained from this group's buffer
-    for (int u = blockIdx.x; u < nunits; u += gridDim.x) {
-      const Unit w = decode_unit(a, u);
+    for (int u = cid; u < nunits; u += nworkers) {
+      const Unit w = decode_unit<PAIR>(a, u, rank);
       if (!w.live) continue;
       const int qi = w.mt * kTileM + row;
       const bool active = qi < w.nq;
@@ -424,10 +480,18 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // nothing of the peer is in flight towards this CTA's shared memory any more
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
 }  // namespace
+
+// CTA pairs pay for the k-best-only search (map-to-frame: 0.950 -> 0.905 ms per 5000 x 1 M frame) when the query tiles pair
+// up without much waste - an odd tile count leaves one CTA of the last pair idle; with the reverse search, whose epilogue
+// is the bound, the coupled B ring costs 6 % (measured), so those launches stay single CTAs.
+bool mma_use_pairs(int mtiles, bool reverse) {
+  return !reverse && mtiles >= 2 && (mtiles % 2 == 0 || mtiles >= 9) && !getenv("ORBX_MMA_NO_PAIRS");
+}
 
 size_t mma_expanded_bytes(int rows_padded) { return (size_t)rows_padded / 8 * kGroupBytes; }
 
@@ -441,14 +505,25 @@ int launch_expand_desc(const uint8_t* desc, size_t desc_stride, const int* n_dev
 }
 
 int launch_hamming_mma(const MmaMatchArgs& a, int num_sms, cudaStream_t s) {
-  const int nunits = a.npairs * a.nsplits * a.mtiles;
-  if (a.rev) {
-    ORBX_CUDA(cudaFuncSetAttribute(hamming_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    hamming_mma_kernel<true><<<std::min(num_sms, nunits), kThreads, kSmemBytes, s>>>(a);
-  } else {
-    ORBX_CUDA(cudaFuncSetAttribute(hamming_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    hamming_mma_kernel<false><<<std::min(num_sms, nunits), kThreads, kSmemBytes, s>>>(a);
-  }
+  const bool pair = mma_use_pairs(a.mtiles, a.rev != nullptr) && num_sms >= 2;
+  const int nunits = a.npairs * a.nsplits * (pair ? (a.mtiles + 1) / 2 : a.mtiles);
+  if (nunits <= 0) return ORBX_OK;
+  void (*kern)(MmaMatchArgs) =
+      a.rev ? hamming_mma_kernel<true, false> : (pair ? hamming_mma_kernel<false, true> : hamming_mma_kernel<false, false>);
+  ORBX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pair ? 2 * std::min(num_sms / 2, nunits) : std::min(num_sms, nunits));
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pair ? 1 : 0;
+  ORBX_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
   ORBX_LAUNCH_CHECK();
   return ORBX_OK;
 }

@@ -28,5 +28,8 @@ size_t mma_expanded_bytes(int rows_padded);  // bytes of one expanded set of row
 int launch_expand_desc(const uint8_t* desc, size_t desc_stride, const int* n_dev, int n_fixed, int max_rows, int nsets,
                        int rows_padded, uint8_t* out, size_t out_stride, cudaStream_t s);
 int launch_hamming_mma(const MmaMatchArgs& a, int num_sms, cudaStream_t s);
+// true: the launch runs as CTA pairs that share their train tiles; a work unit then covers TWO query tiles and there are
+// num_sms / 2 workers (the caller's choice of nsplits goes by that)
+bool mma_use_pairs(int mtiles, bool reverse);
 
 }  // namespace orbx
