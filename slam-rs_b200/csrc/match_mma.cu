@@ -19,6 +19,8 @@
 //                      complete_tx), warp 1 = MMA issuer (one thread; 9 x tcgen05.mma 128x256x32 per tile into one of
 //                      two 256-column TMEM accumulators, tcgen05.commit -> mbarriers), warps 2-17 = epilogue: four
 //                      groups of four warps drain (buffer, column half) with tcgen05.ld while the next tile's MMA runs.
+//                      Without the reverse search the launch runs as clusters of two CTAs that take the two query
+//                      tiles of a pair and share every train tile (multicast bulk copy of half a tile each).
 //                      Forward best-2 per query row = max-reduction of the keys in registers (2.5 VIMNMX per column);
 //                      reverse best-1 per train row (cross-check) = CREDUX.MAX over the 32 rows of a warp, four
 //                      quarter results per column combined in shared memory, one RED.MIN.U64 per (unit, column).
