@@ -492,7 +492,8 @@ __global__ void __launch_bounds__(kThreads, 1) hamming_mma_kernel(MmaMatchArgs a
 // up without much waste - an odd tile count leaves one CTA of the last pair idle; with the reverse search, whose epilogue
 // is the bound, the coupled B ring costs 6 % (measured), so those launches stay single CTAs.
 bool mma_use_pairs(int mtiles, bool reverse) {
-  return !reverse && mtiles >= 2 && (mtiles % 2 == 0 || mtiles >= 9) && !getenv("ORBX_MMA_NO_PAIRS");
+  static const bool no_pairs = getenv("ORBX_MMA_NO_PAIRS") != nullptr;  // A/B switch for measurements
+  return !reverse && !no_pairs && mtiles >= 2 && (mtiles % 2 == 0 || mtiles >= 9);
 }
 
 size_t mma_expanded_bytes(int rows_padded) { return (size_t)rows_padded / 8 * kGroupBytes; }

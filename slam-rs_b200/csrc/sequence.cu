@@ -467,6 +467,7 @@ int orbx_sequence_run_host(orbx_sequence* s, const uint8_t* frames, int T, orbx_
   // 11.7 ms per pass in the steady state against 12.0 ms with four 250-frame stages alternating between two streams).
   // After a sync the GPU is idle and the next pass starts with the ramp again (orbx_sequence_sync clears `pipelining`).
   const bool pipelined = s->pipelining;
+  s->pipelining = false;  // set again when the whole pass has been queued: a call that fails half-way ends the pipelining
   const auto bounds = pipelined ? even_schedule(T, s->chunk) : chunk_schedule(T, s->host_chunk);
   const size_t nc = bounds.size();
   begin_pass(s);
