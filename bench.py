@@ -685,6 +685,9 @@ def run_ours(args, rank, world, local_rank):
             peak = 2.0 * peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0))
             ham.update({"kernel": "hamming_mma_kernel", "bound": "tensor", "achieved_tops": tops, "peak_tops": peak,
                         "frac": tops / peak, "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops_sustained (%s)" % peak_kind,
+                        "note": "stage time includes the int8 expansion and the merge / filter kernels; the kernel itself is bound "
+                                "by its epilogue (best-2 + reverse best-1 out of TMEM): ALU pipe 75 %, tensor pipe 41 % "
+                                "(profiles/r02_ncu_full_v3.csv, profiles/r02_matcher_experiments.md)",
                         "popc_equivalent": {"what": "the same pairs on the XOR+POPC kernel would need 5 POPC each",
                                             "tpopc_per_s": pairs_s * 5 / 1e12, "popc_peak_tpopc": popc / 1e12 if popc else None}})
         else:
